@@ -1,0 +1,151 @@
+"""Deterministic synthetic scenes and cameras.
+
+Replaces the reference's COLMAP / MatrixCity readers (scene/, OUT OF SCOPE) for
+tests and benchmarks; only the conventions are kept: ``viewmat`` is the
+row-major world-to-camera matrix (= ``camera.world_view_transform.T``,
+strategies/clm_offload/engine.py:44) and ``K`` comes from the field of view
+exactly as scene/cameras.py:110-126 builds it.
+
+Everything is numpy on the host; callers upload what they need.
+"""
+from dataclasses import dataclass
+import math
+
+import numpy as np
+
+
+@dataclass
+class SceneSpec:
+    name: str
+    n_gaussians: int
+    width: int
+    height: int
+    batch: int
+    shape: str  # "object" | "aerial"
+    fovx_deg: float
+    index: int  # config index -> seeds
+
+
+# BASELINE.json configs[0..4]
+CONFIGS = {
+    "c1_plumbing_100k": SceneSpec("c1_plumbing_100k", 100_000, 256, 256, 8, "object", 60.0, 0),
+    "c2_bicycle_6m": SceneSpec("c2_bicycle_6m", 6_000_000, 1237, 822, 4, "object", 60.0, 1),
+    "c3_rubble4k_28m": SceneSpec("c3_rubble4k_28m", 28_000_000, 3840, 2160, 4, "aerial", 50.0, 2),
+    "c4_bigcity_102m": SceneSpec("c4_bigcity_102m", 102_000_000, 1920, 1080, 64, "aerial", 50.0, 3),
+    "c5_stress_500m": SceneSpec("c5_stress_500m", 500_000_000, 1920, 1080, 64, "aerial", 50.0, 4),
+}
+
+
+def make_gaussians(spec: SceneSpec, n=None, chunk=4_000_000, sh_out=None):
+    """Returns dict of float32 arrays: xyz[N,3], log_scale[N,3], raw_quat[N,4],
+    opacity_logit[N,1], sh[N,48].  ``sh_out`` may be a preallocated (pinned) [N,48]
+    array that is filled in place (large scenes)."""
+    N = int(n if n is not None else spec.n_gaussians)
+    rng = np.random.default_rng(1234 + spec.index)
+    xyz = np.empty((N, 3), np.float32)
+    if spec.shape == "object":
+        # N(0, I) truncated to |x| < 3 (rejection, chunked)
+        filled = 0
+        while filled < N:
+            m = min(chunk, int((N - filled) * 1.05) + 16)
+            p = rng.standard_normal((m, 3), dtype=np.float32)
+            p = p[(p * p).sum(1) < 9.0]
+            k = min(len(p), N - filled)
+            xyz[filled:filled + k] = p[:k]
+            filled += k
+        spacing = (4.0 / 3.0 * math.pi * 27.0 / N) ** (1.0 / 3.0)
+        L = 3.0
+    else:
+        L = 0.5 * math.sqrt(N / 1e4)
+        for s in range(0, N, chunk):
+            e = min(N, s + chunk)
+            u = rng.random((e - s, 3), dtype=np.float32)
+            xyz[s:e, 0] = (2 * u[:, 0] - 1) * L
+            xyz[s:e, 1] = (2 * u[:, 1] - 1) * L
+            xyz[s:e, 2] = u[:, 2] * 0.1 * L
+        spacing = (2 * L * 2 * L * 0.1 * L / N) ** (1.0 / 3.0)
+    log_scale = np.empty((N, 3), np.float32)
+    raw_quat = np.empty((N, 4), np.float32)
+    opacity = np.empty((N, 1), np.float32)
+    sh = sh_out if sh_out is not None else np.empty((N, 48), np.float32)
+    mu = math.log(0.5 * spacing)
+    for s in range(0, N, chunk):
+        e = min(N, s + chunk)
+        log_scale[s:e] = mu + 0.4 * rng.standard_normal((e - s, 3), dtype=np.float32)
+        q = rng.standard_normal((e - s, 4), dtype=np.float32)
+        raw_quat[s:e] = q / np.linalg.norm(q, axis=1, keepdims=True)
+        opacity[s:e] = 1.5 * rng.standard_normal((e - s, 1), dtype=np.float32)
+        sh[s:e, :3] = 0.5 * rng.standard_normal((e - s, 3), dtype=np.float32)
+        sh[s:e, 3:] = 0.1 * rng.standard_normal((e - s, 45), dtype=np.float32)
+    return dict(xyz=xyz, log_scale=log_scale, raw_quat=raw_quat, opacity_logit=opacity, sh=sh,
+                extent=L, spacing=spacing)
+
+
+def look_at(eye, target, up=(0.0, 0.0, 1.0)):
+    """Row-major 4x4 world->camera, OpenCV axes (x right, y down, z forward)."""
+    eye = np.asarray(eye, np.float64)
+    fwd = np.asarray(target, np.float64) - eye
+    fwd /= np.linalg.norm(fwd)
+    right = np.cross(fwd, np.asarray(up, np.float64))
+    right /= np.linalg.norm(right)
+    down = np.cross(fwd, right)
+    R = np.stack([right, down, fwd])  # rows
+    V = np.eye(4)
+    V[:3, :3] = R
+    V[:3, 3] = -R @ eye
+    return V.astype(np.float32)
+
+
+def intrinsics(width, height, fovx_deg):
+    """scene/cameras.py:110-126 with FoVy chosen for square pixels."""
+    tanx = math.tan(math.radians(fovx_deg) * 0.5)
+    fx = width / (2 * tanx)
+    fy = fx
+    return np.array([[fx, 0, width / 2.0], [0, fy, height / 2.0], [0, 0, 1]], np.float32)
+
+
+def make_cameras(spec: SceneSpec, n_cameras, extent, seed_offset=0):
+    """Returns viewmats[n,4,4], Ks[n,3,3], campos[n,3] float32."""
+    rng = np.random.default_rng(4321 + spec.index + 1000 * seed_offset)
+    V, Kk, P = [], [], []
+    K = intrinsics(spec.width, spec.height, spec.fovx_deg)
+    for _ in range(n_cameras):
+        if spec.shape == "object":
+            ang = rng.uniform(0, 2 * math.pi)
+            eye = np.array([4 * math.cos(ang), 4 * math.sin(ang), rng.uniform(-0.5, 1.5)])
+            tgt = np.zeros(3)
+        else:
+            L = extent
+            eye = np.array([rng.uniform(-0.8 * L, 0.8 * L), rng.uniform(-0.8 * L, 0.8 * L),
+                            0.25 * L * rng.uniform(0.8, 1.2)])
+            yaw = rng.uniform(0, 2 * math.pi)
+            pitch = math.radians(45 + rng.uniform(-10, 10))
+            d = np.array([math.cos(yaw) * math.cos(pitch), math.sin(yaw) * math.cos(pitch), -math.sin(pitch)])
+            tgt = eye + d
+        V.append(look_at(eye, tgt))
+        Kk.append(K)
+        P.append(eye.astype(np.float32))
+    return np.stack(V), np.stack(Kk), np.stack(P)
+
+
+def make_gt_images(spec: SceneSpec, n_cameras, seed=999):
+    """uint8 [n,3,H,W] low-pass noise: bilinear upsample of 1/16-res uniform noise."""
+    rng = np.random.default_rng(seed)
+    H, W = spec.height, spec.width
+    h, w = max(2, H // 16), max(2, W // 16)
+    out = np.empty((n_cameras, 3, H, W), np.uint8)
+    ys = np.linspace(0, h - 1, H)
+    xs = np.linspace(0, w - 1, W)
+    y0 = np.floor(ys).astype(int).clip(0, h - 2)
+    x0 = np.floor(xs).astype(int).clip(0, w - 2)
+    fy = (ys - y0)[:, None].astype(np.float32)
+    fx = (xs - x0)[None, :].astype(np.float32)
+    for i in range(n_cameras):
+        lo = rng.random((3, h, w), dtype=np.float32)
+        a = lo[:, y0][:, :, x0]
+        b = lo[:, y0][:, :, x0 + 1]
+        c = lo[:, y0 + 1][:, :, x0]
+        d = lo[:, y0 + 1][:, :, x0 + 1]
+        img = (a * (1 - fx) + b * fx) * (1 - fy) + (c * (1 - fx) + d * fx) * fy
+        out[i] = (img * 255.0 + 0.5).astype(np.uint8)
+    return out
