@@ -1,0 +1,232 @@
+"""Thin tensor-level front-end over the C ABI (include/clmgs.h).
+
+Each function allocates its outputs with torch (device memory + the current
+stream are the only things torch provides here) and calls exactly one or two
+``clmgs_*`` entry points.  No math happens in python.
+"""
+import math
+
+import torch
+
+from . import _lib
+from ._lib import call
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _scratch(nbytes, device):
+    return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=device)
+
+
+_WORD_DTYPE = {1: torch.uint8, 2: torch.int16, 4: torch.int32, 8: torch.int64}
+
+
+def word_bytes_for(B):
+    return 1 if B <= 8 else 2 if B <= 16 else 4 if B <= 32 else 8
+
+
+def _f32c(t):
+    assert t.dtype == torch.float32, t.dtype
+    return t.contiguous()
+
+
+# --------------------------------------------------------------------------- S1
+def cull(means, scales, quats, viewmats, Ks, width, height, activated=True, eps2d=0.3,
+         near_plane=0.01, far_plane=1e10, radius_clip=0.0, packed_outputs=False):
+    """Frustum cull for B cameras.  Returns dict(bitmap, counts (list[int]), gaussian_ids
+    [nnz] i64 (camera-major, ascending), and with packed_outputs also camera_ids, radii,
+    means2d, depths, conics).  One host sync (reading the B counts)."""
+    means, scales, quats = _f32c(means), _f32c(scales), _f32c(quats)
+    viewmats, Ks = _f32c(viewmats), _f32c(Ks)
+    dev = means.device
+    N, B = means.shape[0], viewmats.shape[0]
+    wb = word_bytes_for(B)
+    bitmap = torch.empty(N, dtype=_WORD_DTYPE[wb], device=dev)
+    counts = torch.empty(B, dtype=torch.int64, device=dev)
+    sbytes = call("clmgs_cull_scratch_bytes", N, B)
+    scratch = _scratch(sbytes, dev)
+    args = (means, scales, quats, int(activated), N, viewmats, Ks, B, int(width), int(height),
+            float(eps2d), float(near_plane), float(far_plane), float(radius_clip))
+    call("clmgs_cull_count", *args, bitmap, wb, counts, scratch, scratch.numel(), _st())
+    counts_h = counts.tolist()  # host sync (the reference has the same one: packed_fwd.cu:236)
+    nnz = sum(counts_h)
+    gids = torch.empty(nnz, dtype=torch.int64, device=dev)
+    out = dict(bitmap=bitmap, counts=counts_h, counts_dev=counts, gaussian_ids=gids, word_bytes=wb)
+    cam = rad = m2 = dep = con = None
+    if packed_outputs:
+        cam = torch.empty(nnz, dtype=torch.int64, device=dev)
+        rad = torch.empty(nnz, dtype=torch.int32, device=dev)
+        m2 = torch.empty(nnz, 2, dtype=torch.float32, device=dev)
+        dep = torch.empty(nnz, dtype=torch.float32, device=dev)
+        con = torch.empty(nnz, 3, dtype=torch.float32, device=dev)
+        out.update(camera_ids=cam, radii=rad, means2d=m2, depths=dep, conics=con)
+    call("clmgs_cull_emit", *args, bitmap, wb, scratch, gids, cam, rad, m2, dep, con, _st())
+    return out
+
+
+# --------------------------------------------------------------------------- A4
+def gather_activate(xyz, log_scale, raw_quat, opacity_logit, ids):
+    n, dev = ids.shape[0], xyz.device
+    means = torch.empty(n, 3, device=dev)
+    scales = torch.empty(n, 3, device=dev)
+    quats = torch.empty(n, 4, device=dev)
+    opac = torch.empty(n, device=dev)
+    call("clmgs_gather_activate", _f32c(xyz), _f32c(log_scale), _f32c(raw_quat), _f32c(opacity_logit),
+         ids.contiguous(), n, means, scales, quats, opac, _st())
+    return means, scales, quats, opac
+
+
+def activate_bwd_scatter(log_scale, raw_quat, opacity_logit, ids, v_means, v_scales, v_quats,
+                         v_opacities, g_xyz, g_log_scale, g_raw_quat, g_opacity_logit):
+    call("clmgs_activate_bwd_scatter", log_scale, raw_quat, opacity_logit, ids, ids.shape[0],
+         _f32c(v_means), _f32c(v_scales), _f32c(v_quats), _f32c(v_opacities), g_xyz, g_log_scale,
+         g_raw_quat, g_opacity_logit, _st())
+
+
+# --------------------------------------------------------------------------- S3
+def projection_fwd(means, quats, scales, viewmats, Ks, width, height, eps2d=0.3, near_plane=0.01,
+                   far_plane=1e10, radius_clip=0.0, calc_compensations=False):
+    means, quats, scales = _f32c(means), _f32c(quats), _f32c(scales)
+    viewmats, Ks = _f32c(viewmats), _f32c(Ks)
+    dev = means.device
+    N, C = means.shape[0], viewmats.shape[0]
+    radii = torch.empty(C, N, dtype=torch.int32, device=dev)
+    means2d = torch.empty(C, N, 2, device=dev)
+    depths = torch.empty(C, N, device=dev)
+    conics = torch.empty(C, N, 3, device=dev)
+    comp = torch.empty(C, N, device=dev) if calc_compensations else None
+    call("clmgs_projection_fwd", C, N, means, quats, scales, viewmats, Ks, int(width), int(height),
+         float(eps2d), float(near_plane), float(far_plane), float(radius_clip), radii, means2d, depths,
+         conics, comp, _st())
+    return radii, means2d, depths, conics, comp
+
+
+def projection_bwd(means, quats, scales, viewmats, Ks, width, height, eps2d, radii, conics,
+                   v_means2d, v_depths, v_conics):
+    dev = means.device
+    N, C = means.shape[0], viewmats.shape[0]
+    v_means = torch.zeros(N, 3, device=dev)
+    v_quats = torch.zeros(N, 4, device=dev)
+    v_scales = torch.zeros(N, 3, device=dev)
+    call("clmgs_projection_bwd", C, N, _f32c(means), _f32c(quats), _f32c(scales), _f32c(viewmats),
+         _f32c(Ks), int(width), int(height), float(eps2d), radii.contiguous(), _f32c(conics),
+         _f32c(v_means2d), _f32c(v_depths), _f32c(v_conics), v_means, v_quats, v_scales, _st())
+    return v_means, v_quats, v_scales
+
+
+# --------------------------------------------------------------------------- SH
+def sh_fwd(degree, dirs, coeffs, masks=None):
+    dirs, coeffs = _f32c(dirs), _f32c(coeffs)
+    K = coeffs.shape[-2]
+    N = dirs.numel() // 3
+    colors = torch.zeros_like(dirs) if masks is not None else torch.empty_like(dirs)
+    m = None if masks is None else masks.contiguous().view(torch.uint8)
+    call("clmgs_sh_fwd", N, K, int(degree), dirs, coeffs, m, colors, _st())
+    return colors
+
+
+def sh_bwd(degree, dirs, coeffs, v_colors, v_coeffs=None, masks=None, compute_v_dirs=True):
+    """v_coeffs given -> accumulate in place (clm_kernels semantics); else fresh tensor."""
+    dirs, coeffs, v_colors = _f32c(dirs), _f32c(coeffs), _f32c(v_colors)
+    K = coeffs.shape[-2]
+    N = dirs.numel() // 3
+    accumulate = v_coeffs is not None
+    if v_coeffs is None:
+        v_coeffs = torch.zeros_like(coeffs)
+    assert v_coeffs.is_contiguous()
+    v_dirs = torch.empty_like(dirs) if compute_v_dirs else None
+    m = None if masks is None else masks.contiguous().view(torch.uint8)
+    call("clmgs_sh_bwd", N, K, int(degree), dirs, coeffs, m, v_colors, v_coeffs, int(accumulate), v_dirs, _st())
+    return v_coeffs, v_dirs
+
+
+# --------------------------------------------------------------------------- S4
+def isect_tiles(means2d, radii, depths, tile_size, tile_width, tile_height, sort=True,
+                n_cameras=None, camera_ids=None):
+    """-> tiles_per_gauss i32 (same shape as radii), isect_ids i64 [n], flatten_ids i32 [n].
+    One host sync to read n_isects (reference: isect_tiles.cu:166)."""
+    means2d, depths = _f32c(means2d), _f32c(depths)
+    radii = radii.contiguous()
+    dev = means2d.device
+    packed = camera_ids is not None
+    if packed:
+        C, N = int(n_cameras), radii.shape[0]
+        total = N
+    else:
+        C, N = radii.shape
+        total = C * N
+    tpg = torch.empty(radii.shape, dtype=torch.int32, device=dev)
+    cum = torch.empty(max(total, 1), dtype=torch.int64, device=dev)
+    sc = _scratch(call("clmgs_isect_count_scratch_bytes", total), dev)
+    call("clmgs_isect_count", total, means2d, radii, int(tile_size), int(tile_width), int(tile_height),
+         tpg, cum, sc, sc.numel(), _st())
+    n_isects = int(cum[total - 1].item()) if total > 0 else 0
+    ids = torch.empty(n_isects, dtype=torch.int64, device=dev)
+    flat = torch.empty(n_isects, dtype=torch.int32, device=dev)
+    sc2 = _scratch(call("clmgs_isect_sort_scratch_bytes", n_isects) if sort else 0, dev)
+    call("clmgs_isect_emit_sort", C, N, camera_ids, means2d, radii, depths, cum, int(tile_size),
+         int(tile_width), int(tile_height), n_isects, int(bool(sort)), ids, flat, sc2, sc2.numel(), _st())
+    return tpg, ids, flat
+
+
+def isect_offset_encode(isect_ids, n_cameras, tile_width, tile_height):
+    off = torch.empty(n_cameras, tile_height, tile_width, dtype=torch.int32, device=isect_ids.device)
+    call("clmgs_isect_offset_encode", isect_ids.shape[0], isect_ids.contiguous(), int(n_cameras),
+         int(tile_width), int(tile_height), off, _st())
+    return off
+
+
+# --------------------------------------------------------------------------- S5
+def rasterize_fwd(means2d, conics, colors, opacities, width, height, tile_size, isect_offsets,
+                  flatten_ids, backgrounds=None):
+    means2d, conics, colors, opacities = map(_f32c, (means2d, conics, colors, opacities))
+    dev = means2d.device
+    C, th, tw = isect_offsets.shape
+    N = opacities.shape[-1]
+    rc = torch.empty(C, height, width, 3, device=dev)
+    ra = torch.empty(C, height, width, 1, device=dev)
+    last = torch.empty(C, height, width, dtype=torch.int32, device=dev)
+    bg = None if backgrounds is None else _f32c(backgrounds)
+    call("clmgs_rasterize_fwd", C, N, flatten_ids.shape[0], means2d, conics, colors, opacities, bg,
+         int(width), int(height), int(tile_size), tw, th, isect_offsets.contiguous(),
+         flatten_ids.contiguous(), rc, ra, last, _st())
+    return rc, ra, last
+
+
+def rasterize_bwd(means2d, conics, colors, opacities, width, height, tile_size, isect_offsets,
+                  flatten_ids, render_alphas, last_ids, v_render_colors, v_render_alphas=None,
+                  backgrounds=None, absgrad=False):
+    means2d, conics, colors, opacities = map(_f32c, (means2d, conics, colors, opacities))
+    dev = means2d.device
+    C, th, tw = isect_offsets.shape
+    N = opacities.shape[-1]
+    v_means2d = torch.zeros_like(means2d)
+    v_conics = torch.zeros_like(conics)
+    v_colors = torch.zeros_like(colors)
+    v_opac = torch.zeros_like(opacities)
+    v_abs = torch.zeros_like(means2d) if absgrad else None
+    bg = None if backgrounds is None else _f32c(backgrounds)
+    vra = None if v_render_alphas is None else _f32c(v_render_alphas)
+    call("clmgs_rasterize_bwd", C, N, flatten_ids.shape[0], means2d, conics, colors, opacities, bg,
+         int(width), int(height), int(tile_size), tw, th, isect_offsets.contiguous(),
+         flatten_ids.contiguous(), _f32c(render_alphas), last_ids.contiguous(), _f32c(v_render_colors),
+         vra, v_abs, v_means2d, v_conics, v_colors, v_opac, _st())
+    return v_means2d, v_conics, v_colors, v_opac, v_abs
+
+
+# --------------------------------------------------------------------------- loss
+def loss_fwd_bwd(image, gt_u8, lambda_dssim=0.2, hwc=True):
+    """image [H,W,3] (hwc) or [3,H,W]; gt_u8 uint8 [3,H,W] -> (loss_vec[3] device: loss,l1,ssim; v_image)."""
+    image = _f32c(image)
+    if hwc:
+        H, W, _ = image.shape
+    else:
+        _, H, W = image.shape
+    out = torch.empty(3, device=image.device)
+    v = torch.empty_like(image)
+    sc = _scratch(call("clmgs_loss_scratch_bytes", H, W), image.device)
+    call("clmgs_loss_fwd_bwd", H, W, image, int(hwc), gt_u8.contiguous(), float(lambda_dssim), out, v, sc,
+         sc.numel(), _st())
+    return out, v

@@ -1,0 +1,548 @@
+// S1 frustum cull + compaction, A4 gather/activate, S3 dense projection,
+// S4 tile counting / key emission / offsets.  Compiled with -fmad=false (see
+// gs_math.cuh): these kernels make the integer decisions that must be
+// bit-exact against the oracle.
+#include "common.cuh"
+#include "gs_math.cuh"
+
+using namespace gsm;
+
+constexpr int kCullThreads = 256;
+constexpr int kMaxCams = 64;
+
+struct CullParams {
+    int width, height;
+    float eps2d, near_plane, far_plane, radius_clip;
+};
+
+// Shared-memory camera table: 16 floats per camera (R row-major, t, fx fy cx cy).
+__device__ __forceinline__ void stage_cameras(float *s_cam, const float *viewmats, const float *Ks, int B) {
+    for (int i = threadIdx.x; i < B * 16; i += blockDim.x) {
+        int c = i >> 4, k = i & 15;
+        float v;
+        if (k < 9) v = viewmats[c * 16 + (k / 3) * 4 + (k % 3)];
+        else if (k < 12) v = viewmats[c * 16 + (k - 9) * 4 + 3];
+        else if (k == 12) v = Ks[c * 9 + 0];
+        else if (k == 13) v = Ks[c * 9 + 4];
+        else if (k == 14) v = Ks[c * 9 + 2];
+        else v = Ks[c * 9 + 5];
+        s_cam[i] = v;
+    }
+}
+__device__ __forceinline__ void camera_from_smem(const float *s, Camera &cam) {
+#pragma unroll
+    for (int k = 0; k < 9; ++k) cam.R[k] = s[k];
+    cam.t[0] = s[9]; cam.t[1] = s[10]; cam.t[2] = s[11];
+    cam.fx = s[12]; cam.fy = s[13]; cam.cx = s[14]; cam.cy = s[15];
+}
+
+__device__ __forceinline__ void load_gaussian(const float *means, const float *scales, const float *quats,
+                                              int activated, int64_t i, float mean[3], float covar[9]) {
+    float s[3], q[4];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { mean[k] = __ldg(means + 3 * i + k); s[k] = __ldg(scales + 3 * i + k); }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) q[k] = __ldg(quats + 4 * i + k);
+    if (!activated) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) s[k] = det_expf(s[k]);
+        float qn[4];
+        normalize_quat(q, qn);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) q[k] = qn[k];
+    }
+    quat_scale_to_covar(q, s, covar);
+}
+
+// ---------------------------------------------------------------------------
+// S1.  One thread per Gaussian, all B cameras: xyz/scale/quat are read once
+// (40 B/Gaussian) instead of 2*B times as in the reference's two-pass kernel.
+// ---------------------------------------------------------------------------
+template <typename W>
+__global__ void __launch_bounds__(kCullThreads)
+cull_count_kernel(const float *__restrict__ means, const float *__restrict__ scales,
+                  const float *__restrict__ quats, int activated, int64_t N,
+                  const float *__restrict__ viewmats, const float *__restrict__ Ks, int B, CullParams p,
+                  W *__restrict__ bitmap, int32_t *__restrict__ block_counts /* [B][gridDim.x] */) {
+    __shared__ float s_cam[kMaxCams * 16];
+    __shared__ int s_cnt[kMaxCams];
+    stage_cameras(s_cam, viewmats, Ks, B);
+    if (threadIdx.x < kMaxCams) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    int64_t i = (int64_t)blockIdx.x * kCullThreads + threadIdx.x;
+    uint64_t word = 0;
+    if (i < N) {
+        float mean[3], covar[9];
+        load_gaussian(means, scales, quats, activated, i, mean, covar);
+        for (int c = 0; c < B; ++c) {
+            Camera cam;
+            camera_from_smem(s_cam + c * 16, cam);
+            Projected o;
+            bool ok = project_one<true>(mean, covar, cam, p.width, p.height, p.eps2d, p.near_plane,
+                                        p.far_plane, p.radius_clip, o);
+            word |= (uint64_t)ok << c;
+        }
+        bitmap[i] = (W)word;
+    }
+    // per-camera block totals: warp ballot + one shared atomic per warp
+    int lane = threadIdx.x & 31;
+    for (int c = 0; c < B; ++c) {
+        unsigned m = __ballot_sync(0xffffffffu, (word >> c) & 1);
+        if (lane == 0 && m) atomicAdd(&s_cnt[c], __popc(m));
+    }
+    __syncthreads();
+    if (threadIdx.x < B) block_counts[(int64_t)threadIdx.x * gridDim.x + blockIdx.x] = s_cnt[threadIdx.x];
+}
+
+// Block-wide exclusive scan of one value per thread (1024 threads); returns
+// the exclusive prefix, *total gets the block total.  s_warp: 33 entries.
+template <typename T>
+__device__ __forceinline__ T block_excl_scan_1024(T v, T *s_warp, T *total) {
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    T incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        T t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        T w = s_warp[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            T t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        s_warp[lane] = wi - w;
+        if (lane == 31) s_warp[32] = wi;
+    }
+    __syncthreads();
+    T excl = s_warp[warp] + (incl - v);
+    *total = s_warp[32];
+    __syncthreads();  // s_warp may be reused by the caller's next round
+    return excl;
+}
+
+// One block per camera: exclusive scan of its block counts in place; total -> counts[c].
+__global__ void __launch_bounds__(1024)
+cull_scan_kernel(int32_t *__restrict__ block_counts, int64_t nblocks, int64_t *__restrict__ counts_a,
+                 int64_t *__restrict__ counts_b) {
+    __shared__ int64_t s_warp[33];
+    int32_t *row = block_counts + (int64_t)blockIdx.x * nblocks;
+    int64_t carry = 0;
+    for (int64_t base = 0; base < nblocks; base += 1024) {
+        int64_t j = base + threadIdx.x;
+        int64_t v = j < nblocks ? row[j] : 0, total;
+        int64_t excl = block_excl_scan_1024<int64_t>(v, s_warp, &total);
+        if (j < nblocks) row[j] = (int32_t)(carry + excl);
+        carry += total;
+    }
+    if (threadIdx.x == 0) {
+        counts_a[blockIdx.x] = carry;
+        counts_b[blockIdx.x] = carry;
+    }
+}
+
+// Compaction from the bitmap: camera c's ascending ids land at
+// [sum(counts[<c]) + block offset + rank in block).
+template <typename W>
+__global__ void __launch_bounds__(kCullThreads)
+cull_emit_kernel(const float *__restrict__ means, const float *__restrict__ scales,
+                 const float *__restrict__ quats, int activated, int64_t N,
+                 const float *__restrict__ viewmats, const float *__restrict__ Ks, int B, CullParams p,
+                 const W *__restrict__ bitmap, const int32_t *__restrict__ block_offsets,
+                 const int64_t *__restrict__ counts, int64_t *__restrict__ gaussian_ids,
+                 int64_t *__restrict__ camera_ids, int32_t *__restrict__ radii, float *__restrict__ means2d,
+                 float *__restrict__ depths, float *__restrict__ conics) {
+    __shared__ float s_cam[kMaxCams * 16];
+    __shared__ int64_t s_base[kMaxCams];
+    __shared__ int s_wcnt[kMaxCams][kCullThreads / 32];
+    const bool extra = radii != nullptr;
+    if (extra) stage_cameras(s_cam, viewmats, Ks, B);
+    if (threadIdx.x == 0) {
+        int64_t acc = 0;
+        for (int c = 0; c < B; ++c) { s_base[c] = acc; acc += counts[c]; }
+    }
+    int64_t i = (int64_t)blockIdx.x * kCullThreads + threadIdx.x;
+    uint64_t word = i < N ? (uint64_t)bitmap[i] : 0;
+    int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int c = 0; c < B; ++c) {
+        unsigned m = __ballot_sync(0xffffffffu, (word >> c) & 1);
+        if (lane == 0) s_wcnt[c][warp] = __popc(m);
+    }
+    __syncthreads();
+    float mean[3], covar[9];
+    if (extra && word) load_gaussian(means, scales, quats, activated, i, mean, covar);
+    const unsigned lt_mask = (1u << lane) - 1u;
+    for (int c = 0; c < B; ++c) {
+        bool bit = (word >> c) & 1;
+        unsigned m = __ballot_sync(0xffffffffu, bit);
+        if (!bit) continue;
+        int r = __popc(m & lt_mask);
+        for (int w = 0; w < warp; ++w) r += s_wcnt[c][w];
+        int64_t pos = s_base[c] + block_offsets[(int64_t)c * gridDim.x + blockIdx.x] + r;
+        gaussian_ids[pos] = i;
+        if (camera_ids) camera_ids[pos] = c;
+        if (extra) {
+            Camera cam;
+            camera_from_smem(s_cam + c * 16, cam);
+            Projected o;
+            project_one<true>(mean, covar, cam, p.width, p.height, p.eps2d, p.near_plane, p.far_plane,
+                              p.radius_clip, o);
+            radii[pos] = (int32_t)o.radius;
+            means2d[2 * pos] = o.mean2d[0];
+            means2d[2 * pos + 1] = o.mean2d[1];
+            depths[pos] = o.depth;
+            conics[3 * pos] = o.conic[0];
+            conics[3 * pos + 1] = o.conic[1];
+            conics[3 * pos + 2] = o.conic[2];
+        }
+    }
+}
+
+// scratch layout: int64 counts[64] | int32 block_offsets[B][nblocks]
+constexpr size_t kCullHead = kMaxCams * sizeof(int64_t);
+
+CLMGS_EXPORT size_t clmgs_cull_scratch_bytes(int64_t N, int B) {
+    int64_t nblocks = ceil_div64(N > 0 ? N : 1, kCullThreads);
+    return kCullHead + (size_t)(nblocks * B) * sizeof(int32_t);
+}
+
+static int check_cull_args(int B, int word_bytes, int64_t N) {
+    CLMGS_REQUIRE(B >= 1 && B <= kMaxCams, "cull: B=%d must be in [1,64]", B);
+    CLMGS_REQUIRE(word_bytes == 1 || word_bytes == 2 || word_bytes == 4 || word_bytes == 8,
+                  "cull: word_bytes=%d must be 1,2,4,8", word_bytes);
+    CLMGS_REQUIRE(8 * word_bytes >= B, "cull: %d-byte bitmap words cannot hold %d cameras", word_bytes, B);
+    CLMGS_REQUIRE(N >= 0 && ceil_div64(N, kCullThreads) < ((int64_t)1 << 31), "cull: bad N");
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_cull_count(const float *means, const float *scales, const float *quats, int activated,
+                                  int64_t N, const float *viewmats, const float *Ks, int B, int width, int height,
+                                  float eps2d, float near_plane, float far_plane, float radius_clip, void *bitmap,
+                                  int word_bytes, int64_t *counts, void *scratch, size_t scratch_bytes,
+                                  void *stream) {
+    if (int rc = check_cull_args(B, word_bytes, N)) return rc;
+    cudaStream_t st = as_stream(stream);
+    if (scratch_bytes < clmgs_cull_scratch_bytes(N, B)) {
+        clmgs_set_error("cull: scratch too small (%zu < %zu)", scratch_bytes, clmgs_cull_scratch_bytes(N, B));
+        return CLMGS_ERR_SCRATCH;
+    }
+    int64_t *head = (int64_t *)scratch;
+    int32_t *blk = (int32_t *)((char *)scratch + kCullHead);
+    if (N == 0) {
+        CLMGS_CUDA(cudaMemsetAsync(counts, 0, sizeof(int64_t) * B, st));
+        CLMGS_CUDA(cudaMemsetAsync(head, 0, kCullHead, st));
+        return CLMGS_OK;
+    }
+    CullParams p{width, height, eps2d, near_plane, far_plane, radius_clip};
+    unsigned nblocks = (unsigned)ceil_div64(N, kCullThreads);
+#define LAUNCH(W)                                                                                         \
+    cull_count_kernel<W><<<nblocks, kCullThreads, 0, st>>>(means, scales, quats, activated, N, viewmats, \
+                                                          Ks, B, p, (W *)bitmap, blk)
+    switch (word_bytes) {
+        case 1: LAUNCH(uint8_t); break;
+        case 2: LAUNCH(uint16_t); break;
+        case 4: LAUNCH(uint32_t); break;
+        default: LAUNCH(uint64_t); break;
+    }
+#undef LAUNCH
+    CLMGS_LAUNCH_OK();
+    cull_scan_kernel<<<B, 1024, 0, st>>>(blk, (int64_t)nblocks, head, counts);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_cull_emit(const float *means, const float *scales, const float *quats, int activated,
+                                 int64_t N, const float *viewmats, const float *Ks, int B, int width, int height,
+                                 float eps2d, float near_plane, float far_plane, float radius_clip,
+                                 const void *bitmap, int word_bytes, const void *scratch, int64_t *gaussian_ids,
+                                 int64_t *camera_ids, int32_t *radii, float *means2d, float *depths, float *conics,
+                                 void *stream) {
+    if (int rc = check_cull_args(B, word_bytes, N)) return rc;
+    CLMGS_REQUIRE((radii == nullptr) == (means2d == nullptr) && (radii == nullptr) == (depths == nullptr) &&
+                      (radii == nullptr) == (conics == nullptr),
+                  "cull_emit: radii/means2d/depths/conics must be all NULL or all set");
+    if (N == 0) return CLMGS_OK;
+    CullParams p{width, height, eps2d, near_plane, far_plane, radius_clip};
+    cudaStream_t st = as_stream(stream);
+    unsigned nblocks = (unsigned)ceil_div64(N, kCullThreads);
+    const int64_t *head = (const int64_t *)scratch;
+    const int32_t *blk = (const int32_t *)((const char *)scratch + kCullHead);
+#define LAUNCH(W)                                                                                              \
+    cull_emit_kernel<W><<<nblocks, kCullThreads, 0, st>>>(means, scales, quats, activated, N, viewmats, Ks, B, \
+                                                         p, (const W *)bitmap, blk, head, gaussian_ids,       \
+                                                         camera_ids, radii, means2d, depths, conics)
+    switch (word_bytes) {
+        case 1: LAUNCH(uint8_t); break;
+        case 2: LAUNCH(uint16_t); break;
+        case 4: LAUNCH(uint32_t); break;
+        default: LAUNCH(uint64_t); break;
+    }
+#undef LAUNCH
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+// ---------------------------------------------------------------------------
+// A4.  Filter gather + activations (engine.py:650-666).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gather_activate_kernel(const float *__restrict__ xyz, const float *__restrict__ log_scale,
+                       const float *__restrict__ raw_quat, const float *__restrict__ opacity_logit,
+                       const int64_t *__restrict__ ids, int64_t n, float *__restrict__ means_out,
+                       float *__restrict__ scales_out, float *__restrict__ quats_out,
+                       float *__restrict__ opac_out) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    int64_t g = ids[r];
+    float q[4], qn[4];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        means_out[3 * r + k] = __ldg(xyz + 3 * g + k);
+        scales_out[3 * r + k] = det_expf(__ldg(log_scale + 3 * g + k));
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) q[k] = __ldg(raw_quat + 4 * g + k);
+    normalize_quat(q, qn);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) quats_out[4 * r + k] = qn[k];
+    opac_out[r] = det_sigmoidf(__ldg(opacity_logit + g));
+}
+
+CLMGS_EXPORT int clmgs_gather_activate(const float *xyz, const float *log_scale, const float *raw_quat,
+                                       const float *opacity_logit, const int64_t *ids, int64_t n,
+                                       float *means_out, float *scales_out, float *quats_out,
+                                       float *opacities_out, void *stream) {
+    if (n == 0) return CLMGS_OK;
+    gather_activate_kernel<<<(unsigned)ceil_div64(n, 256), 256, 0, as_stream(stream)>>>(
+        xyz, log_scale, raw_quat, opacity_logit, ids, n, means_out, scales_out, quats_out, opacities_out);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+// ---------------------------------------------------------------------------
+// S3.  Dense projection, one thread per (camera, Gaussian).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+projection_fwd_kernel(int C, int64_t N, const float *__restrict__ means, const float *__restrict__ quats,
+                      const float *__restrict__ scales, const float *__restrict__ viewmats,
+                      const float *__restrict__ Ks, CullParams p, int32_t *__restrict__ radii,
+                      float *__restrict__ means2d, float *__restrict__ depths, float *__restrict__ conics,
+                      float *__restrict__ compensations) {
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)C * N) return;
+    int c = (int)(idx / N);
+    int64_t i = idx % N;
+    Camera cam;
+    load_camera(viewmats + 16 * c, Ks + 9 * c, cam);
+    float mean[3], covar[9];
+    load_gaussian(means, scales, quats, 1, i, mean, covar);
+    Projected o;
+    bool ok = project_one<false>(mean, covar, cam, p.width, p.height, p.eps2d, p.near_plane, p.far_plane,
+                                 p.radius_clip, o);
+    if (!ok) {
+        radii[idx] = 0;
+        means2d[2 * idx] = 0.f; means2d[2 * idx + 1] = 0.f;
+        depths[idx] = 0.f;
+        conics[3 * idx] = 0.f; conics[3 * idx + 1] = 0.f; conics[3 * idx + 2] = 0.f;
+        if (compensations) compensations[idx] = 0.f;
+        return;
+    }
+    radii[idx] = (int32_t)o.radius;
+    means2d[2 * idx] = o.mean2d[0];
+    means2d[2 * idx + 1] = o.mean2d[1];
+    depths[idx] = o.depth;
+    conics[3 * idx] = o.conic[0];
+    conics[3 * idx + 1] = o.conic[1];
+    conics[3 * idx + 2] = o.conic[2];
+    if (compensations) compensations[idx] = o.compensation;
+}
+
+CLMGS_EXPORT int clmgs_projection_fwd(int C, int64_t N, const float *means, const float *quats,
+                                      const float *scales, const float *viewmats, const float *Ks, int width,
+                                      int height, float eps2d, float near_plane, float far_plane,
+                                      float radius_clip, int32_t *radii, float *means2d, float *depths,
+                                      float *conics, float *compensations, void *stream) {
+    CLMGS_REQUIRE(C >= 0 && N >= 0, "projection_fwd: negative size");
+    int64_t total = (int64_t)C * N;
+    if (total == 0) return CLMGS_OK;
+    CullParams p{width, height, eps2d, near_plane, far_plane, radius_clip};
+    projection_fwd_kernel<<<(unsigned)ceil_div64(total, 256), 256, 0, as_stream(stream)>>>(
+        C, N, means, quats, scales, viewmats, Ks, p, radii, means2d, depths, conics, compensations);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+// ---------------------------------------------------------------------------
+// S4.  Tile counting with an inclusive int64 prefix sum (three phases, 1024
+// elements per block), key emission, per-tile offsets.
+// ---------------------------------------------------------------------------
+constexpr int kScanThreads = 1024;
+
+__device__ __forceinline__ int tiles_of(const float *means2d, const int32_t *radii, int64_t idx, int tile_size,
+                                        int tw, int th) {
+    int r = radii[idx];
+    if (r <= 0) return 0;
+    int x0, y0, x1, y1;
+    tile_rect(means2d[2 * idx], means2d[2 * idx + 1], r, tile_size, tw, th, x0, y0, x1, y1);
+    return (y1 - y0) * (x1 - x0);
+}
+
+__global__ void __launch_bounds__(kScanThreads)
+isect_count_kernel(int64_t total, const float *__restrict__ means2d, const int32_t *__restrict__ radii,
+                   int tile_size, int tw, int th, int32_t *__restrict__ tiles_per_gauss,
+                   int64_t *__restrict__ block_sums) {
+    __shared__ int64_t s_warp[33];
+    int64_t idx = (int64_t)blockIdx.x * kScanThreads + threadIdx.x;
+    int64_t v = 0, tot;
+    if (idx < total) {
+        v = tiles_of(means2d, radii, idx, tile_size, tw, th);
+        tiles_per_gauss[idx] = (int32_t)v;
+    }
+    block_excl_scan_1024<int64_t>(v, s_warp, &tot);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(kScanThreads)
+scan_block_sums_kernel(int64_t *__restrict__ block_sums, int64_t nblocks) {
+    __shared__ int64_t s_warp[33];
+    int64_t carry = 0;
+    for (int64_t base = 0; base < nblocks; base += kScanThreads) {
+        int64_t j = base + threadIdx.x;
+        int64_t v = j < nblocks ? block_sums[j] : 0, tot;
+        int64_t excl = block_excl_scan_1024<int64_t>(v, s_warp, &tot);
+        if (j < nblocks) block_sums[j] = carry + excl;
+        carry += tot;
+    }
+}
+
+__global__ void __launch_bounds__(kScanThreads)
+isect_cumsum_kernel(int64_t total, const int32_t *__restrict__ tiles_per_gauss,
+                    const int64_t *__restrict__ block_sums, int64_t *__restrict__ cum_tiles) {
+    __shared__ int64_t s_warp[33];
+    int64_t idx = (int64_t)blockIdx.x * kScanThreads + threadIdx.x;
+    int64_t v = idx < total ? tiles_per_gauss[idx] : 0, tot;
+    int64_t excl = block_excl_scan_1024<int64_t>(v, s_warp, &tot);
+    if (idx < total) cum_tiles[idx] = block_sums[blockIdx.x] + excl + v;
+}
+
+CLMGS_EXPORT size_t clmgs_isect_count_scratch_bytes(int64_t total) {
+    return (size_t)(ceil_div64(total > 0 ? total : 1, kScanThreads)) * sizeof(int64_t);
+}
+
+CLMGS_EXPORT int clmgs_isect_count(int64_t total, const float *means2d, const int32_t *radii, int tile_size,
+                                   int tile_width, int tile_height, int32_t *tiles_per_gauss, int64_t *cum_tiles,
+                                   void *scratch, size_t scratch_bytes, void *stream) {
+    CLMGS_REQUIRE(total >= 0 && tile_size > 0, "isect_count: bad sizes");
+    if (total == 0) return CLMGS_OK;
+    if (scratch_bytes < clmgs_isect_count_scratch_bytes(total)) {
+        clmgs_set_error("isect_count: scratch too small");
+        return CLMGS_ERR_SCRATCH;
+    }
+    cudaStream_t st = as_stream(stream);
+    int64_t nblocks = ceil_div64(total, kScanThreads);
+    int64_t *bs = (int64_t *)scratch;
+    isect_count_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(total, means2d, radii, tile_size, tile_width,
+                                                                  tile_height, tiles_per_gauss, bs);
+    CLMGS_LAUNCH_OK();
+    scan_block_sums_kernel<<<1, kScanThreads, 0, st>>>(bs, nblocks);
+    CLMGS_LAUNCH_OK();
+    isect_cumsum_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(total, tiles_per_gauss, bs, cum_tiles);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+__global__ void __launch_bounds__(256)
+isect_emit_kernel(int64_t total, int64_t N, const int64_t *__restrict__ camera_ids,
+                  const float *__restrict__ means2d, const int32_t *__restrict__ radii,
+                  const float *__restrict__ depths, const int64_t *__restrict__ cum_tiles, int tile_size,
+                  int tw, int th, int tile_n_bits, int64_t *__restrict__ isect_ids,
+                  int32_t *__restrict__ flatten_ids) {
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    int r = radii[idx];
+    if (r <= 0) return;
+    int x0, y0, x1, y1;
+    tile_rect(means2d[2 * idx], means2d[2 * idx + 1], r, tile_size, tw, th, x0, y0, x1, y1);
+    int64_t cid = camera_ids ? camera_ids[idx] : idx / N;
+    int64_t cid_enc = cid << (32 + tile_n_bits);
+    int64_t depth_enc = (int64_t)__float_as_int(depths[idx]);  // sign-extending cast, as the reference
+    int64_t cur = idx == 0 ? 0 : cum_tiles[idx - 1];
+    for (int i = y0; i < y1; ++i)
+        for (int j = x0; j < x1; ++j) {
+            int64_t tile_id = (int64_t)i * tw + j;
+            isect_ids[cur] = cid_enc | (tile_id << 32) | depth_enc;
+            flatten_ids[cur] = (int32_t)idx;
+            ++cur;
+        }
+}
+
+int clmgs_radix_sort_pairs(int64_t n, int64_t *keys, int32_t *vals, int end_bit, void *scratch,
+                           size_t scratch_bytes, cudaStream_t st);  // sort.cu
+size_t clmgs_radix_sort_scratch(int64_t n);
+
+static int n_bits_of(int64_t v) {  // floor(log2(v)) + 1, CSRC/isect_tiles.cu:143-144
+    int b = 0;
+    while (((int64_t)1 << b) <= v) ++b;
+    return b;
+}
+
+CLMGS_EXPORT size_t clmgs_isect_sort_scratch_bytes(int64_t n_isects) { return clmgs_radix_sort_scratch(n_isects); }
+
+CLMGS_EXPORT int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_ids, const float *means2d,
+                                       const int32_t *radii, const float *depths, const int64_t *cum_tiles,
+                                       int tile_size, int tile_width, int tile_height, int64_t n_isects, int sort,
+                                       int64_t *isect_ids, int32_t *flatten_ids, void *scratch,
+                                       size_t scratch_bytes, void *stream) {
+    int64_t total = camera_ids ? N : (int64_t)C * N;
+    if (total == 0 || n_isects == 0) return CLMGS_OK;
+    CLMGS_REQUIRE(n_isects < ((int64_t)1 << 31), "isect: n_isects=%lld does not fit int32 offsets", (long long)n_isects);
+    int tile_n_bits = n_bits_of((int64_t)tile_width * tile_height);
+    int cam_n_bits = n_bits_of(C);
+    CLMGS_REQUIRE(tile_n_bits + cam_n_bits <= 32, "isect: too many tiles/cameras for a 64-bit key");
+    cudaStream_t st = as_stream(stream);
+    isect_emit_kernel<<<(unsigned)ceil_div64(total, 256), 256, 0, st>>>(total, N, camera_ids, means2d, radii, depths,
+                                                                       cum_tiles, tile_size, tile_width,
+                                                                       tile_height, tile_n_bits, isect_ids,
+                                                                       flatten_ids);
+    CLMGS_LAUNCH_OK();
+    if (sort)
+        return clmgs_radix_sort_pairs(n_isects, isect_ids, flatten_ids, 32 + tile_n_bits + cam_n_bits, scratch,
+                                      scratch_bytes, st);
+    return CLMGS_OK;
+}
+
+__global__ void __launch_bounds__(256)
+isect_offsets_kernel(int64_t n_isects, const int64_t *__restrict__ isect_ids, int64_t n_slots, int n_tiles,
+                     int tile_n_bits, int32_t *__restrict__ offsets) {
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n_isects) return;
+    int64_t hi = isect_ids[idx] >> 32;
+    int64_t cur = (hi >> tile_n_bits) * n_tiles + (hi & (((int64_t)1 << tile_n_bits) - 1));
+    int64_t prev = -1;
+    if (idx > 0) {
+        int64_t hp = isect_ids[idx - 1] >> 32;
+        prev = (hp >> tile_n_bits) * n_tiles + (hp & (((int64_t)1 << tile_n_bits) - 1));
+    }
+    for (int64_t t = prev + 1; t <= cur; ++t) offsets[t] = (int32_t)idx;  // first entry of every slot in (prev, cur]
+    if (idx == n_isects - 1)
+        for (int64_t t = cur + 1; t < n_slots; ++t) offsets[t] = (int32_t)n_isects;
+}
+
+CLMGS_EXPORT int clmgs_isect_offset_encode(int64_t n_isects, const int64_t *isect_ids, int C, int tile_width,
+                                           int tile_height, int32_t *offsets, void *stream) {
+    cudaStream_t st = as_stream(stream);
+    int n_tiles = tile_width * tile_height;
+    int64_t n_slots = (int64_t)C * n_tiles;
+    if (n_slots == 0) return CLMGS_OK;
+    if (n_isects == 0) {
+        CLMGS_CUDA(cudaMemsetAsync(offsets, 0, sizeof(int32_t) * n_slots, st));
+        return CLMGS_OK;
+    }
+    isect_offsets_kernel<<<(unsigned)ceil_div64(n_isects, 256), 256, 0, st>>>(n_isects, isect_ids, n_slots, n_tiles,
+                                                                             n_bits_of(n_tiles), offsets);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}

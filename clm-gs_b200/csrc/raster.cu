@@ -1,0 +1,300 @@
+// S5 alpha-composited rasterisation, forward and backward, 3 colour channels,
+// 16x16-pixel tiles (one CTA of 256 threads per tile, one pixel per thread).
+//
+// Semantics follow rasterize_to_pixels_{fwd,bwd}_kernel<3>
+// (CSRC/rasterize_to_pixels_fwd.cu:14-160, CSRC/rasterize_to_pixels_bwd.cu:14-249):
+// front-to-back compositing, alpha = min(0.999, o*exp(-sigma)), skip when
+// sigma < 0 or alpha < 1/255, exclusive termination at T*(1-alpha) <= 1e-4.
+//
+// Differences in how it is computed (B200-first):
+//  * a batch of 256 Gaussians is staged in shared memory as two float4 + one
+//    float per Gaussian INCLUDING its colour, so the inner loop touches no
+//    global memory (the reference fetches colours from global per hit);
+//  * backward: the 9 per-Gaussian partial gradients of a warp are reduced with
+//    a multi-value butterfly (14 shuffles instead of 45) and the 8 finished
+//    sums are added by 8 different lanes in parallel.
+#include "common.cuh"
+
+constexpr int kTile = 16;
+constexpr int kBlock = kTile * kTile;
+
+struct RasterArgs {
+    int C;
+    int64_t N;
+    int64_t n_isects;
+    int width, height, tile_width, tile_height;
+};
+
+__device__ __forceinline__ void tile_range(const RasterArgs &a, const int32_t *tile_offsets, int cam, int tile_id,
+                                           int &start, int &end) {
+    int64_t t = (int64_t)cam * a.tile_width * a.tile_height + tile_id;
+    start = tile_offsets[t];
+    end = (t == (int64_t)a.C * a.tile_width * a.tile_height - 1) ? (int)a.n_isects : tile_offsets[t + 1];
+}
+
+template <bool HAS_BG>
+__global__ void __launch_bounds__(kBlock)
+raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float *__restrict__ conics,
+                  const float *__restrict__ colors, const float *__restrict__ opacities,
+                  const float *__restrict__ backgrounds, const int32_t *__restrict__ tile_offsets,
+                  const int32_t *__restrict__ flatten_ids, float *__restrict__ render_colors,
+                  float *__restrict__ render_alphas, int32_t *__restrict__ last_ids) {
+    __shared__ float4 s_a[kBlock];  // x, y, conic.x, conic.y
+    __shared__ float4 s_b[kBlock];  // conic.z, opacity, r, g
+    __shared__ float s_c[kBlock];   // b
+    const int cam = blockIdx.z;
+    const int tile_id = blockIdx.y * a.tile_width + blockIdx.x;
+    const int i = blockIdx.y * kTile + threadIdx.y;
+    const int j = blockIdx.x * kTile + threadIdx.x;
+    const int tr = threadIdx.y * kTile + threadIdx.x;
+    const float px = (float)j + 0.5f, py = (float)i + 0.5f;
+    const bool inside = i < a.height && j < a.width;
+    bool done = !inside;
+    int start, end;
+    tile_range(a, tile_offsets, cam, tile_id, start, end);
+    const int num_batches = (end - start + kBlock - 1) / kBlock;
+
+    float T = 1.0f, r = 0.f, g = 0.f, b = 0.f;
+    int cur_idx = 0;
+    for (int bt = 0; bt < num_batches; ++bt) {
+        if (__syncthreads_count(done) >= kBlock) break;
+        const int batch_start = start + kBlock * bt;
+        const int idx = batch_start + tr;
+        if (idx < end) {
+            const int gid = flatten_ids[idx];
+            const float2 xy = means2d[gid];
+            const float *cn = conics + 3 * (int64_t)gid;
+            const float *cl = colors + 3 * (int64_t)gid;
+            s_a[tr] = make_float4(xy.x, xy.y, cn[0], cn[1]);
+            s_b[tr] = make_float4(cn[2], opacities[gid], cl[0], cl[1]);
+            s_c[tr] = cl[2];
+        }
+        __syncthreads();
+        const int batch_size = min(kBlock, end - batch_start);
+        for (int t = 0; t < batch_size && !done; ++t) {
+            const float4 A = s_a[t];
+            const float4 Bv = s_b[t];
+            const float dx = A.x - px, dy = A.y - py;
+            const float sigma = 0.5f * (A.z * dx * dx + Bv.x * dy * dy) + A.w * dx * dy;
+            const float alpha = fminf(0.999f, Bv.y * __expf(-sigma));
+            if (sigma < 0.f || alpha < 1.f / 255.f) continue;
+            const float next_T = T * (1.0f - alpha);
+            if (next_T <= 1e-4f) { done = true; break; }
+            const float vis = alpha * T;
+            r += Bv.z * vis; g += Bv.w * vis; b += s_c[t] * vis;
+            cur_idx = batch_start + t;
+            T = next_T;
+        }
+    }
+    if (inside) {
+        const int64_t pix = ((int64_t)cam * a.height + i) * a.width + j;
+        render_alphas[pix] = 1.0f - T;
+        if (HAS_BG) {
+            const float *bg = backgrounds + 3 * cam;
+            r += T * bg[0]; g += T * bg[1]; b += T * bg[2];
+        }
+        render_colors[3 * pix] = r; render_colors[3 * pix + 1] = g; render_colors[3 * pix + 2] = b;
+        last_ids[pix] = cur_idx;
+    }
+}
+
+CLMGS_EXPORT int clmgs_rasterize_fwd(int C, int64_t N, int64_t n_isects, const float *means2d, const float *conics,
+                                     const float *colors, const float *opacities, const float *backgrounds,
+                                     int width, int height, int tile_size, int tile_width, int tile_height,
+                                     const int32_t *tile_offsets, const int32_t *flatten_ids, float *render_colors,
+                                     float *render_alphas, int32_t *last_ids, void *stream) {
+    CLMGS_REQUIRE(tile_size == kTile, "rasterize: tile_size must be 16 (got %d)", tile_size);
+    CLMGS_REQUIRE(tile_width * kTile >= width && tile_height * kTile >= height,
+                  "rasterize: tile grid %dx%d does not cover %dx%d", tile_width, tile_height, width, height);
+    CLMGS_REQUIRE(n_isects < ((int64_t)1 << 31), "rasterize: n_isects too large");
+    if (C == 0 || width == 0 || height == 0) return CLMGS_OK;
+    RasterArgs a{C, N, n_isects, width, height, tile_width, tile_height};
+    dim3 grid(tile_width, tile_height, C), block(kTile, kTile, 1);
+    cudaStream_t st = as_stream(stream);
+    if (backgrounds)
+        raster_fwd_kernel<true><<<grid, block, 0, st>>>(a, (const float2 *)means2d, conics, colors, opacities,
+                                                        backgrounds, tile_offsets, flatten_ids, render_colors,
+                                                        render_alphas, last_ids);
+    else
+        raster_fwd_kernel<false><<<grid, block, 0, st>>>(a, (const float2 *)means2d, conics, colors, opacities,
+                                                         backgrounds, tile_offsets, flatten_ids, render_colors,
+                                                         render_alphas, last_ids);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Backward
+// ---------------------------------------------------------------------------
+// Butterfly reduction of 8 values across a warp in 9 shuffles.  On return,
+// lane L with (L & 3) == 0 holds the full warp sum of value index
+// ((L>>4)&1)*4 + ((L>>3)&1)*2 + ((L>>2)&1) in v[0].
+__device__ __forceinline__ float butterfly8(float v[8], int lane) {
+    const bool up16 = lane & 16;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        float send = up16 ? v[k] : v[k + 4];
+        float keep = up16 ? v[k + 4] : v[k];
+        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+    const bool up8 = lane & 8;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        float send = up8 ? v[k] : v[k + 2];
+        float keep = up8 ? v[k + 2] : v[k];
+        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    const bool up4 = lane & 4;
+    {
+        float send = up4 ? v[0] : v[1];
+        float keep = up4 ? v[1] : v[0];
+        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+    return v[0];
+}
+
+template <bool HAS_BG, bool ABSGRAD>
+__global__ void __launch_bounds__(kBlock)
+raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float *__restrict__ conics,
+                  const float *__restrict__ colors, const float *__restrict__ opacities,
+                  const float *__restrict__ backgrounds, const int32_t *__restrict__ tile_offsets,
+                  const int32_t *__restrict__ flatten_ids, const float *__restrict__ render_alphas,
+                  const int32_t *__restrict__ last_ids, const float *__restrict__ v_render_colors,
+                  const float *__restrict__ v_render_alphas, float *__restrict__ v_means2d_abs,
+                  float *__restrict__ v_means2d, float *__restrict__ v_conics, float *__restrict__ v_colors,
+                  float *__restrict__ v_opacities) {
+    __shared__ int s_id[kBlock];
+    __shared__ float4 s_a[kBlock];  // x, y, conic.x, conic.y
+    __shared__ float4 s_b[kBlock];  // conic.z, opacity, r, g
+    __shared__ float s_c[kBlock];   // b
+    const int cam = blockIdx.z;
+    const int tile_id = blockIdx.y * a.tile_width + blockIdx.x;
+    const int i = blockIdx.y * kTile + threadIdx.y;
+    const int j = blockIdx.x * kTile + threadIdx.x;
+    const int tr = threadIdx.y * kTile + threadIdx.x;
+    const int lane = tr & 31;
+    const float px = (float)j + 0.5f, py = (float)i + 0.5f;
+    const bool inside = i < a.height && j < a.width;
+    int start, end;
+    tile_range(a, tile_offsets, cam, tile_id, start, end);
+    const int num_batches = (end - start + kBlock - 1) / kBlock;
+
+    const int64_t pix = inside ? ((int64_t)cam * a.height + i) * a.width + j : 0;
+    const float T_final = inside ? 1.0f - render_alphas[pix] : 1.0f;
+    float T = T_final;
+    float buf_r = 0.f, buf_g = 0.f, buf_b = 0.f;
+    const int bin_final = inside ? last_ids[pix] : 0;
+    float vr = 0.f, vg = 0.f, vb = 0.f, va = 0.f;
+    if (inside) {
+        vr = v_render_colors[3 * pix]; vg = v_render_colors[3 * pix + 1]; vb = v_render_colors[3 * pix + 2];
+        if (v_render_alphas) va = v_render_alphas[pix];
+    }
+    float bg_dot = 0.f;
+    if (HAS_BG) {
+        const float *bg = backgrounds + 3 * cam;
+        bg_dot = bg[0] * vr + bg[1] * vg + bg[2] * vb;
+    }
+    int warp_bin_final = bin_final;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
+
+    for (int bt = 0; bt < num_batches; ++bt) {
+        __syncthreads();
+        const int batch_end = end - 1 - kBlock * bt;  // absolute index of the back-most entry of this batch
+        const int batch_size = min(kBlock, batch_end + 1 - start);
+        const int idx = batch_end - tr;
+        if (idx >= start) {
+            const int gid = flatten_ids[idx];
+            s_id[tr] = gid;
+            const float2 xy = means2d[gid];
+            const float *cn = conics + 3 * (int64_t)gid;
+            const float *cl = colors + 3 * (int64_t)gid;
+            s_a[tr] = make_float4(xy.x, xy.y, cn[0], cn[1]);
+            s_b[tr] = make_float4(cn[2], opacities[gid], cl[0], cl[1]);
+            s_c[tr] = cl[2];
+        }
+        __syncthreads();
+        for (int t = max(0, batch_end - warp_bin_final); t < batch_size; ++t) {
+            bool valid = inside && (batch_end - t <= bin_final);
+            float alpha = 0.f, opac = 0.f, vis = 0.f, dx = 0.f, dy = 0.f;
+            float4 A, Bv;
+            if (valid) {
+                A = s_a[t]; Bv = s_b[t];
+                opac = Bv.y;
+                dx = A.x - px; dy = A.y - py;
+                const float sigma = 0.5f * (A.z * dx * dx + Bv.x * dy * dy) + A.w * dx * dy;
+                vis = __expf(-sigma);
+                alpha = fminf(0.999f, opac * vis);
+                if (sigma < 0.f || alpha < 1.f / 255.f) valid = false;
+            }
+            if (!__any_sync(0xffffffffu, valid)) continue;
+            float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // rgb, conic xyz, xy
+            float v_opa = 0.f, v_ax = 0.f, v_ay = 0.f;
+            if (valid) {
+                const float cb = s_c[t];
+                const float ra = 1.0f / (1.0f - alpha);
+                T *= ra;
+                const float fac = alpha * T;
+                v[0] = fac * vr; v[1] = fac * vg; v[2] = fac * vb;
+                float v_alpha = (Bv.z * T - buf_r * ra) * vr + (Bv.w * T - buf_g * ra) * vg + (cb * T - buf_b * ra) * vb;
+                v_alpha += T_final * ra * va;
+                if (HAS_BG) v_alpha += -T_final * ra * bg_dot;
+                if (opac * vis <= 0.999f) {
+                    const float v_sigma = -opac * vis * v_alpha;
+                    v[3] = 0.5f * v_sigma * dx * dx;
+                    v[4] = v_sigma * dx * dy;
+                    v[5] = 0.5f * v_sigma * dy * dy;
+                    v[6] = v_sigma * (A.z * dx + A.w * dy);
+                    v[7] = v_sigma * (A.w * dx + Bv.x * dy);
+                    if (ABSGRAD) { v_ax = fabsf(v[6]); v_ay = fabsf(v[7]); }
+                    v_opa = vis * v_alpha;
+                }
+                buf_r += Bv.z * fac; buf_g += Bv.w * fac; buf_b += cb * fac;
+            }
+            const float red = butterfly8(v, lane);
+            v_opa = warp_sum(v_opa);
+            if (ABSGRAD) { v_ax = warp_sum(v_ax); v_ay = warp_sum(v_ay); }
+            const int64_t gid = s_id[t];
+            if ((lane & 3) == 0) {
+                const int k = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+                float *dst = k < 3 ? v_colors + 3 * gid + k : (k < 6 ? v_conics + 3 * gid + (k - 3) : v_means2d + 2 * gid + (k - 6));
+                atomicAdd(dst, red);
+            } else if (lane == 1) {
+                atomicAdd(v_opacities + gid, v_opa);
+            } else if (ABSGRAD && lane == 2) {
+                atomicAdd(v_means2d_abs + 2 * gid, v_ax);
+            } else if (ABSGRAD && lane == 3) {
+                atomicAdd(v_means2d_abs + 2 * gid + 1, v_ay);
+            }
+        }
+    }
+}
+
+CLMGS_EXPORT int clmgs_rasterize_bwd(int C, int64_t N, int64_t n_isects, const float *means2d, const float *conics,
+                                     const float *colors, const float *opacities, const float *backgrounds,
+                                     int width, int height, int tile_size, int tile_width, int tile_height,
+                                     const int32_t *tile_offsets, const int32_t *flatten_ids,
+                                     const float *render_alphas, const int32_t *last_ids,
+                                     const float *v_render_colors, const float *v_render_alphas,
+                                     float *v_means2d_abs, float *v_means2d, float *v_conics, float *v_colors,
+                                     float *v_opacities, void *stream) {
+    CLMGS_REQUIRE(tile_size == kTile, "rasterize: tile_size must be 16 (got %d)", tile_size);
+    CLMGS_REQUIRE(tile_width * kTile >= width && tile_height * kTile >= height,
+                  "rasterize: tile grid %dx%d does not cover %dx%d", tile_width, tile_height, width, height);
+    if (C == 0 || width == 0 || height == 0 || n_isects == 0) return CLMGS_OK;
+    RasterArgs a{C, N, n_isects, width, height, tile_width, tile_height};
+    dim3 grid(tile_width, tile_height, C), block(kTile, kTile, 1);
+    cudaStream_t st = as_stream(stream);
+#define LAUNCH(BG, AB)                                                                                          \
+    raster_bwd_kernel<BG, AB><<<grid, block, 0, st>>>(a, (const float2 *)means2d, conics, colors, opacities,     \
+                                                      backgrounds, tile_offsets, flatten_ids, render_alphas,     \
+                                                      last_ids, v_render_colors, v_render_alphas, v_means2d_abs, \
+                                                      v_means2d, v_conics, v_colors, v_opacities)
+    if (backgrounds) { if (v_means2d_abs) LAUNCH(true, true); else LAUNCH(true, false); }
+    else { if (v_means2d_abs) LAUNCH(false, true); else LAUNCH(false, false); }
+#undef LAUNCH
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}

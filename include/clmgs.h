@@ -1,0 +1,324 @@
+/*
+ * clmgs.h -- C ABI of libclmgs.so, the B200 (sm_100a) implementation of the
+ * CLM-GS per-camera-batch training hot path.
+ *
+ * This is the drop-in boundary: one entry point per native function the
+ * reference binds for this path through pybind11 (gsplat.csrc:
+ * submodules/gsplat/gsplat/cuda/csrc/ext.cpp:4-32; clm_kernels._C:
+ * submodules/clm_kernels/ext.cpp:7-23), plus the cpu-adam / fast-tsp calls of
+ * strategies/clm_offload/engine.py.  Paths below are relative to the reference
+ * root; CSRC = submodules/gsplat/gsplat/cuda/csrc, CK = submodules/clm_kernels.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types cross the boundary
+ *   - `d_` / unprefixed pointers are device memory, `h_` pointers are PINNED
+ *     host memory mapped into the device address space (UVA zero-copy), `host_`
+ *     pointers are ordinary host memory read by the CPU
+ *   - outputs are caller-allocated; functions that need temporary global memory
+ *     take (scratch, scratch_bytes) and have a *_scratch_bytes() query
+ *   - `stream` is a cudaStream_t passed as void*; every launch is asynchronous
+ *     on that stream and no entry point synchronises unless it says so
+ *   - return value: 0 = ok, negative = error; clmgs_last_error() gives the
+ *     message (thread-local).  No C++ exception crosses the boundary.
+ *   - all floating point is fp32; ids are int64 where the reference uses int64
+ *     (filters, camera_ids/gaussian_ids) and int32 where it uses int32.
+ */
+#ifndef CLMGS_H
+#define CLMGS_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CLMGS_OK 0
+#define CLMGS_ERR_INVALID (-1)
+#define CLMGS_ERR_CUDA (-2)
+#define CLMGS_ERR_SCRATCH (-3)
+
+const char *clmgs_last_error(void);
+/* ABI version of this header; bumped on any signature change. */
+int clmgs_abi_version(void);
+
+/* ---------------------------------------------------------------------------
+ * S1  Frustum cull + compaction.
+ * Replaces fully_fused_projection_packed_fwd_tensor
+ * (CSRC/fully_fused_projection_packed_fwd.cu:184-274, two projection passes +
+ * cumsum + .item()) as used by calculate_filters (strategies/base_engine.py:18-76).
+ *
+ * clmgs_cull_count: every Gaussian is projected ONCE for all B cameras
+ * (B <= 64); writes the visibility word of each Gaussian (bit c = camera c;
+ * word_bytes = 1,2,4,8 chosen by the caller with 8*word_bytes >= B), the
+ * per-camera totals counts[B] (int64) and the per-block partial counts in
+ * scratch.  If `activated` is 0 the inputs are the RAW model tensors
+ * (log-scale, unnormalised quaternion) and exp()/normalize() are fused in
+ * (strategies/base_gaussian_model.py:42-50); if 1 they are already activated,
+ * as the reference's python passes them.
+ *
+ * clmgs_cull_emit: from bitmap + scratch writes, for camera c, its ascending
+ * Gaussian ids at gaussian_ids[offset_c ...] with offset_c = sum(counts[<c]),
+ * i.e. exactly the flat (camera_ids, gaussian_ids) of the reference.  Optional
+ * outputs (may be NULL) reproduce the rest of the packed tuple: camera_ids,
+ * radii, means2d, depths, conics.
+ * ------------------------------------------------------------------------- */
+size_t clmgs_cull_scratch_bytes(int64_t N, int B);
+int clmgs_cull_count(const float *means, const float *scales, const float *quats, int activated,
+                     int64_t N, const float *viewmats, const float *Ks, int B, int width,
+                     int height, float eps2d, float near_plane, float far_plane,
+                     float radius_clip, void *bitmap, int word_bytes, int64_t *counts,
+                     void *scratch, size_t scratch_bytes, void *stream);
+int clmgs_cull_emit(const float *means, const float *scales, const float *quats, int activated,
+                    int64_t N, const float *viewmats, const float *Ks, int B, int width,
+                    int height, float eps2d, float near_plane, float far_plane,
+                    float radius_clip, const void *bitmap, int word_bytes, const void *scratch,
+                    int64_t *gaussian_ids, int64_t *camera_ids, int32_t *radii, float *means2d,
+                    float *depths, float *conics, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * A4  Filter gather + activations (strategies/clm_offload/engine.py:650-666,
+ * strategies/base_gaussian_model.py:42-50) and its backward + scatter-add into
+ * the dense gradient tensors (engine.py:725-742).
+ * ------------------------------------------------------------------------- */
+int clmgs_gather_activate(const float *xyz, const float *log_scale, const float *raw_quat,
+                          const float *opacity_logit, const int64_t *ids, int64_t n,
+                          float *means_out, float *scales_out, float *quats_out,
+                          float *opacities_out, void *stream);
+/* v_* are gradients w.r.t. the ACTIVATED filtered values; g_* are the dense
+ * [N,*] accumulators (+=).  Re-reads the raw parameters to differentiate
+ * exp / normalize / sigmoid. */
+int clmgs_activate_bwd_scatter(const float *log_scale, const float *raw_quat,
+                               const float *opacity_logit, const int64_t *ids, int64_t n,
+                               const float *v_means, const float *v_scales, const float *v_quats,
+                               const float *v_opacities, float *g_xyz, float *g_log_scale,
+                               float *g_raw_quat, float *g_opacity_logit, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * S3  Dense projection.  fully_fused_projection_fwd_tensor / _bwd_tensor
+ * (CSRC/fully_fused_projection_fwd.cu:132-181, CSRC/fully_fused_projection_bwd.cu:188-283).
+ * Shapes: means [N,3], quats [N,4] wxyz, scales [N,3], viewmats [C,4,4]
+ * row-major world->camera, Ks [C,3,3]; outputs radii [C,N] i32, means2d
+ * [C,N,2], depths [C,N], conics [C,N,3], compensations [C,N] or NULL.
+ * Unlike the reference (torch::empty) culled rows are written as zeros.
+ * bwd accumulates (+=) into v_means/v_quats/v_scales, which the caller zeroes.
+ * ------------------------------------------------------------------------- */
+int clmgs_projection_fwd(int C, int64_t N, const float *means, const float *quats,
+                         const float *scales, const float *viewmats, const float *Ks, int width,
+                         int height, float eps2d, float near_plane, float far_plane,
+                         float radius_clip, int32_t *radii, float *means2d, float *depths,
+                         float *conics, float *compensations, void *stream);
+int clmgs_projection_bwd(int C, int64_t N, const float *means, const float *quats,
+                         const float *scales, const float *viewmats, const float *Ks, int width,
+                         int height, float eps2d, const int32_t *radii, const float *conics,
+                         const float *v_means2d, const float *v_depths, const float *v_conics,
+                         float *v_means, float *v_quats, float *v_scales, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * Spherical harmonics.  compute_sh_fwd_tensor (CSRC/compute_sh_fwd.cu:31-58)
+ * and compute_sh_bwd_inplace_tensor (CK/compute_sh_bwd.cu:309-344).
+ * dirs [N,3], coeffs [N,K,3], masks [N] (uint8/bool) or NULL, colors [N,3].
+ * bwd: v_coeffs [N,K,3]; accumulate != 0 gives the clm `+=` behaviour,
+ * 0 gives gsplat's overwrite (bases above the degree are written as 0).
+ * v_dirs [N,3] may be NULL.
+ * ------------------------------------------------------------------------- */
+int clmgs_sh_fwd(int64_t N, int K, int degree, const float *dirs, const float *coeffs,
+                 const uint8_t *masks, float *colors, void *stream);
+int clmgs_sh_bwd(int64_t N, int K, int degree, const float *dirs, const float *coeffs,
+                 const uint8_t *masks, const float *v_colors, float *v_coeffs, int accumulate,
+                 float *v_dirs, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * S4  Tile intersection, sort, offsets.  isect_tiles_tensor
+ * (CSRC/isect_tiles.cu:100-232) and isect_offset_encode_tensor (:280-301).
+ * Dense layout only ([C,N]); packed inputs are handled by passing camera_ids
+ * (int64 [nnz]) with C = n_cameras and N = nnz.
+ *
+ * clmgs_isect_count: tiles_per_gauss [C*N] i32, cum_tiles [C*N] i64 (inclusive
+ * prefix sum, == torch.cumsum in the reference), n_isects = cum_tiles[last]
+ * (device scalar, also returned in *d_n_isects if non-NULL).
+ * clmgs_isect_emit_sort: writes isect_ids [n_isects] i64 and flatten_ids
+ * [n_isects] i32; if `sort`, they are sorted by the low
+ * 32+tile_n_bits+cam_n_bits key bits with a stable LSD radix sort
+ * (cub::DeviceRadixSort semantics, CSRC/isect_tiles.cu:196-203).
+ * ------------------------------------------------------------------------- */
+size_t clmgs_isect_count_scratch_bytes(int64_t total);
+int clmgs_isect_count(int64_t total, const float *means2d, const int32_t *radii, int tile_size,
+                      int tile_width, int tile_height, int32_t *tiles_per_gauss,
+                      int64_t *cum_tiles, void *scratch, size_t scratch_bytes, void *stream);
+size_t clmgs_isect_sort_scratch_bytes(int64_t n_isects);
+int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_ids, const float *means2d,
+                          const int32_t *radii, const float *depths, const int64_t *cum_tiles,
+                          int tile_size, int tile_width, int tile_height, int64_t n_isects,
+                          int sort, int64_t *isect_ids, int32_t *flatten_ids, void *scratch,
+                          size_t scratch_bytes, void *stream);
+int clmgs_isect_offset_encode(int64_t n_isects, const int64_t *isect_ids, int C, int tile_width,
+                              int tile_height, int32_t *offsets, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * S5  Rasterise.  rasterize_to_pixels_fwd_tensor (CSRC/rasterize_to_pixels_fwd.cu:236-267)
+ * and rasterize_to_pixels_bwd_tensor (CSRC/rasterize_to_pixels_bwd.cu:347-381),
+ * 3 colour channels (CLM uses CDIM=3, engine.py:106-117), tile_size 16.
+ * means2d [C,N,2], conics [C,N,3], colors [C,N,3], opacities [C,N],
+ * backgrounds [C,3] or NULL, tile_offsets [C,th,tw] i32, flatten_ids i32.
+ * Outputs: render_colors [C,H,W,3], render_alphas [C,H,W,1], last_ids [C,H,W].
+ * bwd accumulates (+=) into v_means2d, v_conics, v_colors, v_opacities (and
+ * v_means2d_abs if non-NULL), which the caller zeroes.  v_render_alphas may be
+ * NULL (== zeros, as in the CLM loss).
+ * ------------------------------------------------------------------------- */
+int clmgs_rasterize_fwd(int C, int64_t N, int64_t n_isects, const float *means2d,
+                        const float *conics, const float *colors, const float *opacities,
+                        const float *backgrounds, int width, int height, int tile_size,
+                        int tile_width, int tile_height, const int32_t *tile_offsets,
+                        const int32_t *flatten_ids, float *render_colors, float *render_alphas,
+                        int32_t *last_ids, void *stream);
+int clmgs_rasterize_bwd(int C, int64_t N, int64_t n_isects, const float *means2d,
+                        const float *conics, const float *colors, const float *opacities,
+                        const float *backgrounds, int width, int height, int tile_size,
+                        int tile_width, int tile_height, const int32_t *tile_offsets,
+                        const int32_t *flatten_ids, const float *render_alphas,
+                        const int32_t *last_ids, const float *v_render_colors,
+                        const float *v_render_alphas, float *v_means2d_abs, float *v_means2d,
+                        float *v_conics, float *v_colors, float *v_opacities, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * A9  Loss.  fusedssim + fusedssim_backward (CK/ssim.cu:368-444) fused with
+ * loss_combined (strategies/base_engine.py:79-94, a torch.compile/Triton
+ * kernel in the reference):  loss = (1-l)*mean|I-GT| + l*(1-mean ssim_map).
+ * image is [H,W,3] (the rasteriser's layout, hwc=1) or [3,H,W] (hwc=0); gt_u8
+ * is uint8 [3,H,W] (train.py:311).  Writes loss_out[0..2] = {loss, l1, ssim}
+ * (device) and v_image = d loss / d image in the image's own layout.
+ * scratch: clmgs_loss_scratch_bytes(H,W).
+ * ------------------------------------------------------------------------- */
+size_t clmgs_loss_scratch_bytes(int height, int width);
+int clmgs_loss_fwd_bwd(int height, int width, const float *image, int hwc, const uint8_t *gt_u8,
+                       float lambda_dssim, float *loss_out, float *v_image, void *scratch,
+                       size_t scratch_bytes, void *stream);
+/* Plain fused SSIM map mean (clm_kernels.fused_ssim forward, CK/clm_kernels/__init__.py:54-61)
+ * on float [B,CH,H,W] inputs, for drop-in use; ssim_out is one float; v_img1
+ * (optional) receives d mean(ssim_map) / d img1 (fusedssim_backward with
+ * dL_dmap = 1/numel).  scratch: clmgs_loss_scratch_bytes(B*CH*H/3 + 1, W). */
+int clmgs_fused_ssim(int B, int CH, int height, int width, const float *img1, const float *img2,
+                     float *ssim_out, float *v_img1, void *scratch, size_t scratch_bytes,
+                     void *stream);
+
+/* ---------------------------------------------------------------------------
+ * S2 / S6  Offloaded SH rows.  48 floats = 192 B per row.
+ * send_shs2gpu_stream (CK/clm_kernels.cu:26-48), send_shs2gpu_stream_retention
+ * (:92-126), send_shs2cpu_grad_buffer_stream (:150-175),
+ * send_shs2cpu_grad_buffer_stream_retention (:230-268), set_signal (:280-289).
+ * The grid/block arguments of the reference are dropped: the library sizes its
+ * own launches.
+ * ------------------------------------------------------------------------- */
+int clmgs_rows_gather_i64(float *d_rows, const float *h_rows, const int64_t *ids, int64_t n,
+                          void *stream);
+int clmgs_rows_gather_retention(float *d_rows, const float *h_rows, const float *d_prev_rows,
+                                const int32_t *host_ids, const int32_t *prev_src_rows,
+                                const int32_t *dst_rows_from_host,
+                                const int32_t *dst_rows_from_prev, int64_t n_host,
+                                int64_t n_prev, void *stream);
+int clmgs_rows_scatter_grad_i64(const float *d_grad, float *h_grad, const int64_t *ids,
+                                int64_t n, int accum, void *stream);
+int clmgs_rows_scatter_grad_retention(const float *d_grad, float *h_grad, float *d_next_grad,
+                                      const int32_t *host_ids, const int32_t *next_dst_rows,
+                                      const int32_t *src_rows_to_host,
+                                      const int32_t *src_rows_to_next, int64_t n_host,
+                                      int64_t n_next, int accum, void *stream);
+int clmgs_set_signal(int32_t *h_flags, int index, int value, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * A2  Camera ordering / retention bookkeeping bitmaps.
+ * scatter_to_bit (CK/clm_kernels.cu:362-421), extract_ffs (:291-360),
+ * compute_cnt_h (:423-627).  word_bytes in {1,2,4,8}.
+ * clmgs_compute_cnt_d writes cnt_d[k] = |F_k & F_{k+1}| for k < bsz-1 directly
+ * (int32 [bsz-1], zeroed inside) instead of the reference's (bsz-1, 16384)
+ * per-thread partials + torch.sum.
+ * clmgs_bitmap_permute re-encodes a cull bitmap (bit c = input camera c) into
+ * the ordered convention of engine.py:151-153,199-201: camera order[i] -> bit
+ * bsz-1-i, replacing zero_() + bsz scatter_to_bit launches.
+ * ------------------------------------------------------------------------- */
+int clmgs_scatter_to_bit(void *bitmap, int word_bytes, const int64_t *ids, int64_t n, int bit,
+                         void *stream);
+int clmgs_extract_ffs(const void *bitmap, int word_bytes, uint8_t *out, int64_t N, void *stream);
+int clmgs_compute_cnt_d(const void *bitmap, int word_bytes, int bsz, int64_t N, int32_t *cnt_d,
+                        void *stream);
+int clmgs_bitmap_permute(const void *bitmap_in, void *bitmap_out, int word_bytes, int bsz,
+                         const int32_t *order /* host, [bsz] */, int64_t N, void *stream);
+/* Sampled pairwise XOR distance matrix of engine.py:159-175: dist[i*bsz+j] =
+ * #samples where cameras i and j differ (int32 [bsz*bsz], zeroed inside). */
+int clmgs_bitmap_distance(const void *bitmap, int word_bytes, int bsz, const int64_t *sample_ids,
+                          int64_t n_samples, int32_t *dist, void *stream);
+/* Groups Gaussian ids by ffs value (the torch.sort + unique_consecutive +
+ * split of engine.py:203-213): out_ids [N] int32 grouped by key 0..bsz, with
+ * group_counts [bsz+1] int64; ids ascending inside each group (stable).
+ * scratch: clmgs_group_by_ffs_scratch_bytes(N). */
+size_t clmgs_group_by_ffs_scratch_bytes(int64_t N);
+int clmgs_group_by_ffs(const uint8_t *ffs, int64_t N, int bsz, int32_t *out_ids,
+                       int64_t *group_counts, void *scratch, size_t scratch_bytes, void *stream);
+/* Retention without index lists (new design; replaces the nonzero_static /
+ * gather / scatter_ glue of engine.py:519-641 and :767-803 plus the two
+ * transfer launches).  `bitmap` is the ORDERED bitmap (camera at position k of
+ * the processing order <-> bit bsz-1-k, engine.py:151-153); ids_this/ids_next
+ * are the ascending filters of positions k and k+1.
+ *
+ * clmgs_rows_prefetch_next: for every row r' of the next camera, copies its
+ * 192-B SH row either device->device from the current camera's buffer (the
+ * Gaussian is also visible now: rank found by binary search in ids_this) or
+ * from the pinned host table with 16-byte zero-copy loads.  src_map[r'] gets
+ * the source row in the current buffer, or -1 for rows that came from host.
+ *
+ * clmgs_rows_grad_handoff: after the backward of camera k: next_grad[r'] =
+ * grad_this[src_map[r']] (retained rows) or 0 (rows new to the GPU); rows of
+ * camera k that camera k+1 does not see go to the pinned gradient table
+ * (h_grad[id] += or =).  ids_next == NULL (n_next == 0) flushes every row
+ * (last camera, engine.py:812-822). */
+int clmgs_rows_prefetch_next(float *d_next_rows, const float *h_rows, const float *d_this_rows,
+                             const int64_t *ids_this, int64_t n_this, const int64_t *ids_next,
+                             int64_t n_next, const void *bitmap, int word_bytes, int bit_this,
+                             int32_t *src_map, void *stream);
+int clmgs_rows_grad_handoff(const float *d_grad_this, float *d_next_grad, float *h_grad,
+                            const int64_t *ids_this, int64_t n_this, int64_t n_next,
+                            const int32_t *src_map, const void *bitmap, int word_bytes,
+                            int bit_next, int accum, void *stream);
+
+/* ---------------------------------------------------------------------------
+ * A16  GPU Adam.  selective_adam_update (CK/adam.cu:43-78; masked, no bias
+ * correction) and the dense torch.optim.Adam(fused=True) rule with bias
+ * correction (optimizer.py:127-129).  grad_scale multiplies the gradient
+ * first (the `param.grad /= bsz` of engine.py:870-872, fused).
+ * ------------------------------------------------------------------------- */
+int clmgs_selective_adam(float *param, const float *grad, float *exp_avg, float *exp_avg_sq,
+                         const uint8_t *mask, float lr, float b1, float b2, float eps,
+                         float grad_scale, int64_t N, int M, void *stream);
+int clmgs_adam_dense(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, float lr,
+                     float b1, float b2, float eps, float grad_scale, int64_t step, int64_t n,
+                     void *stream);
+
+/* ---------------------------------------------------------------------------
+ * A15  Host Adam for the offloaded rows (HOST code, runs on the CPU by design:
+ * the reference's cpu-adam, submodule TarzanZhao/cpu-adam @ f169c36, source
+ * not in the mount; call sites optimizer.py:130-142, engine.py:301-335).
+ * Blocking; releases nothing itself -- call it from a thread that does not
+ * hold the GIL (ctypes does that).  For m in 0..bsz: waits (spins with pause)
+ * until h_signal[m-1] != 0 for m >= 1, then updates rows
+ * host_rows[row_offsets[m] .. row_offsets[m+1]) of the pinned [N,48] tensors.
+ * Group 0 (rows untouched this batch) is skipped when sparse_adam != 0.
+ * Gradients are multiplied by `scale`, and zeroed in place afterwards
+ * (the reference's version=3).  n_threads <= 0 picks hardware concurrency.
+ * ------------------------------------------------------------------------- */
+int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, float *host_exp_avg,
+                                       float *host_exp_avg_sq, int cols, const float *col_lr,
+                                       const int32_t *host_rows, const int64_t *row_offsets,
+                                       int bsz, const volatile int32_t *h_signal, float b1,
+                                       float b2, float eps, int64_t step, float scale,
+                                       int sparse_adam, int n_threads);
+
+/* fast_tsp.find_tour(dist, 0.001) (engine.py:179; submodule TarzanZhao/fast-tsp
+ * @ 069eb3d, source not in the mount): deterministic greedy + 2-opt/Or-opt
+ * open... closed tour over n <= 64 cameras, int32 dist [n*n]; writes tour[n]. */
+int clmgs_tsp_tour(const int32_t *host_dist, int n, int32_t *host_tour);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CLMGS_H */
