@@ -230,3 +230,124 @@ def loss_fwd_bwd(image, gt_u8, lambda_dssim=0.2, hwc=True):
     call("clmgs_loss_fwd_bwd", H, W, image, int(hwc), gt_u8.contiguous(), float(lambda_dssim), out, v, sc,
          sc.numel(), _st())
     return out, v
+
+
+def fused_ssim_fwd_bwd(img1, img2, want_grad=True):
+    """clm_kernels.fused_ssim on float [B,CH,H,W]: -> (ssim scalar tensor, d mean/d img1 or None)."""
+    img1, img2 = _f32c(img1), _f32c(img2)
+    B, CH, H, W = img1.shape
+    out = torch.empty(1, device=img1.device)
+    v = torch.empty_like(img1) if want_grad else None
+    sc = _scratch(256 + (B * CH * 3 * H * W * 4 if want_grad else 0), img1.device)
+    call("clmgs_fused_ssim", B, CH, H, W, img1, img2, out, v, sc, sc.numel(), _st())
+    return out[0], v
+
+
+# --------------------------------------------------------------------------- S2 / S6 rows
+def rows_gather(d_rows, h_rows, ids):
+    call("clmgs_rows_gather_i64", d_rows, h_rows, ids.contiguous(), ids.shape[0], _st())
+
+
+def rows_gather_retention(d_rows, h_rows, d_prev, host_ids, prev_src_rows, dst_from_host, dst_from_prev):
+    call("clmgs_rows_gather_retention", d_rows, h_rows, d_prev, host_ids, prev_src_rows, dst_from_host,
+         dst_from_prev, host_ids.shape[0], prev_src_rows.shape[0], _st())
+
+
+def rows_scatter_grad(d_grad, h_grad, ids, accum):
+    call("clmgs_rows_scatter_grad_i64", d_grad, h_grad, ids.contiguous(), ids.shape[0], int(accum), _st())
+
+
+def rows_scatter_grad_retention(d_grad, h_grad, d_next_grad, host_ids, next_dst_rows, src_to_host, src_to_next,
+                                accum):
+    call("clmgs_rows_scatter_grad_retention", d_grad, h_grad, d_next_grad, host_ids, next_dst_rows, src_to_host,
+         src_to_next, host_ids.shape[0], next_dst_rows.shape[0], int(accum), _st())
+
+
+def set_signal(h_flags, index, value):
+    call("clmgs_set_signal", h_flags, int(index), int(value), _st())
+
+
+def rows_prefetch_next(d_next, h_rows, d_this, ids_this, ids_next, bitmap, bit_this):
+    n_next = ids_next.shape[0]
+    src_map = torch.empty(max(n_next, 1), dtype=torch.int32, device=d_next.device)
+    call("clmgs_rows_prefetch_next", d_next, h_rows, d_this, ids_this, 0 if ids_this is None else ids_this.shape[0],
+         ids_next, n_next, bitmap, bitmap.element_size(), int(bit_this), src_map, _st())
+    return src_map
+
+
+def rows_grad_handoff(d_grad, d_next_grad, h_grad, ids_this, n_next, src_map, bitmap, bit_next, accum=True):
+    call("clmgs_rows_grad_handoff", d_grad, d_next_grad, h_grad, ids_this, ids_this.shape[0], int(n_next), src_map,
+         bitmap, bitmap.element_size(), int(bit_next), int(accum), _st())
+
+
+# --------------------------------------------------------------------------- A2 bitmaps
+def scatter_to_bit(bitmap, ids, bit):
+    call("clmgs_scatter_to_bit", bitmap, bitmap.element_size(), ids.contiguous(), ids.shape[0], int(bit), _st())
+
+
+def extract_ffs(bitmap, out=None):
+    if out is None:
+        out = torch.empty(bitmap.shape[0], dtype=torch.uint8, device=bitmap.device)
+    call("clmgs_extract_ffs", bitmap, bitmap.element_size(), out, bitmap.shape[0], _st())
+    return out
+
+
+def compute_cnt_d(bitmap, bsz):
+    cnt = torch.empty(max(bsz - 1, 1), dtype=torch.int32, device=bitmap.device)
+    call("clmgs_compute_cnt_d", bitmap, bitmap.element_size(), int(bsz), bitmap.shape[0], cnt, _st())
+    return cnt[: bsz - 1]
+
+
+def bitmap_permute(bitmap, bsz, order):
+    import numpy as np
+    out = torch.empty_like(bitmap)
+    order = np.ascontiguousarray(order, dtype=np.int32)
+    call("clmgs_bitmap_permute", bitmap, out, bitmap.element_size(), int(bsz), order, bitmap.shape[0], _st())
+    return out
+
+
+def bitmap_distance(bitmap, bsz, sample_ids):
+    buf = torch.empty(2 * bsz * bsz, dtype=torch.int32, device=bitmap.device)
+    call("clmgs_bitmap_distance", bitmap, bitmap.element_size(), int(bsz), sample_ids.contiguous(),
+         sample_ids.shape[0], buf, _st())
+    return buf[: bsz * bsz].view(bsz, bsz)
+
+
+def group_by_ffs(ffs, bsz):
+    N, dev = ffs.shape[0], ffs.device
+    out_ids = torch.empty(N, dtype=torch.int32, device=dev)
+    counts = torch.empty(bsz + 1, dtype=torch.int64, device=dev)
+    sc = _scratch(call("clmgs_group_by_ffs_scratch_bytes", N), dev)
+    call("clmgs_group_by_ffs", ffs, N, int(bsz), out_ids, counts, sc, sc.numel(), _st())
+    return out_ids, counts
+
+
+# --------------------------------------------------------------------------- A16 / A15 optimisers
+def selective_adam(param, grad, exp_avg, exp_avg_sq, mask, lr, b1, b2, eps, grad_scale=1.0):
+    N = mask.shape[0]
+    M = param.numel() // N
+    m = mask if mask.dtype == torch.uint8 else mask.view(torch.uint8)
+    call("clmgs_selective_adam", param, grad, exp_avg, exp_avg_sq, m, float(lr), float(b1), float(b2), float(eps),
+         float(grad_scale), N, M, _st())
+
+
+def adam_dense(param, grad, exp_avg, exp_avg_sq, lr, b1, b2, eps, step, grad_scale=1.0):
+    call("clmgs_adam_dense", param, grad, exp_avg, exp_avg_sq, float(lr), float(b1), float(b2), float(eps),
+         float(grad_scale), int(step), param.numel(), _st())
+
+
+def cpu_adam_batched_sparse_step(param, grad, exp_avg, exp_avg_sq, col_lr, rows, row_offsets, bsz, signal, b1, b2,
+                                 eps, step, scale, sparse_adam, n_threads=0):
+    """All arguments are HOST tensors/arrays (pinned where the GPU also touches them).  Blocking."""
+    call("clmgs_cpu_adam_batched_sparse_step", param, grad, exp_avg, exp_avg_sq, int(param.shape[1]), col_lr, rows,
+         row_offsets, int(bsz), signal, float(b1), float(b2), float(eps), int(step), float(scale), int(sparse_adam),
+         int(n_threads))
+
+
+def tsp_tour(dist):
+    import numpy as np
+    d = np.ascontiguousarray(dist, dtype=np.int32)
+    n = d.shape[0]
+    tour = np.empty(n, np.int32)
+    call("clmgs_tsp_tour", d, n, tour)
+    return tour.tolist()

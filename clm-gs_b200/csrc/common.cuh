@@ -32,7 +32,7 @@ void clmgs_set_error(const char *fmt, ...);
 #define CLMGS_LAUNCH_OK() CLMGS_CUDA(cudaGetLastError())
 
 static inline cudaStream_t as_stream(void *s) { return (cudaStream_t)s; }
-static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+__host__ __device__ static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 constexpr int kNumSMs = 148;  // B200
 

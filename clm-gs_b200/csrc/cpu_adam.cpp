@@ -1,0 +1,165 @@
+// A15 host-side Adam for the offloaded SH rows, and the camera-order TSP
+// heuristic.  HOST code by design (north star: "host-resident optimizer state
+// keeps the reference's cpu-adam as part of the design").  The reference's
+// implementations (submodules cpu-adam @ f169c36 and fast-tsp @ 069eb3d) are
+// not in the mount; semantics come from the call sites
+// (optimizer.py:130-142, engine.py:301-335, engine.py:179) -- parity unpinned.
+#include <immintrin.h>
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#include <algorithm>
+#include <thread>
+#include <vector>
+
+#include "../../include/clmgs.h"
+
+void clmgs_set_error(const char *fmt, ...);
+#define CLMGS_EXPORT extern "C" __attribute__((visibility("default")))
+
+namespace {
+
+struct AdamConst {
+    float b1, b2, eps, scale, inv_bc1, bc2_rsqrt;
+};
+
+// one row of `cols` floats; cols % 8 == 0 fast path (48 = 6 x __m256)
+inline void adam_row(float *p, float *g, float *m, float *v, const float *col_lr, int cols, const AdamConst &c) {
+    int k = 0;
+    const __m256 b1 = _mm256_set1_ps(c.b1), omb1 = _mm256_set1_ps(1.0f - c.b1);
+    const __m256 b2 = _mm256_set1_ps(c.b2), omb2 = _mm256_set1_ps(1.0f - c.b2);
+    const __m256 eps = _mm256_set1_ps(c.eps), sc = _mm256_set1_ps(c.scale);
+    const __m256 ibc1 = _mm256_set1_ps(-c.inv_bc1), bc2r = _mm256_set1_ps(c.bc2_rsqrt);
+    for (; k + 8 <= cols; k += 8) {
+        __m256 gg = _mm256_mul_ps(_mm256_loadu_ps(g + k), sc);
+        __m256 mm = _mm256_add_ps(_mm256_mul_ps(b1, _mm256_loadu_ps(m + k)), _mm256_mul_ps(omb1, gg));
+        __m256 vv = _mm256_add_ps(_mm256_mul_ps(b2, _mm256_loadu_ps(v + k)), _mm256_mul_ps(omb2, _mm256_mul_ps(gg, gg)));
+        __m256 denom = _mm256_add_ps(_mm256_mul_ps(_mm256_sqrt_ps(vv), bc2r), eps);
+        __m256 step = _mm256_mul_ps(_mm256_mul_ps(_mm256_loadu_ps(col_lr + k), ibc1), _mm256_div_ps(mm, denom));
+        _mm256_storeu_ps(p + k, _mm256_add_ps(_mm256_loadu_ps(p + k), step));
+        _mm256_storeu_ps(m + k, mm);
+        _mm256_storeu_ps(v + k, vv);
+        _mm256_storeu_ps(g + k, _mm256_setzero_ps());  // version 3: zero the consumed gradient in place
+    }
+    for (; k < cols; ++k) {
+        float gg = g[k] * c.scale;
+        float mm = c.b1 * m[k] + (1.0f - c.b1) * gg;
+        float vv = c.b2 * v[k] + (1.0f - c.b2) * gg * gg;
+        float denom = sqrtf(vv) * c.bc2_rsqrt + c.eps;
+        p[k] += -(col_lr[k] * c.inv_bc1) * (mm / denom);
+        m[k] = mm; v[k] = vv; g[k] = 0.f;
+    }
+}
+
+inline void wait_flag(const volatile int32_t *flag) {
+    int spins = 0;
+    while (*flag == 0) {
+        _mm_pause();
+        if (++spins > 2000) { std::this_thread::yield(); spins = 0; }
+    }
+    __atomic_thread_fence(__ATOMIC_ACQUIRE);
+}
+
+}  // namespace
+
+CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, float *host_exp_avg,
+                                                    float *host_exp_avg_sq, int cols, const float *col_lr,
+                                                    const int32_t *host_rows, const int64_t *row_offsets, int bsz,
+                                                    const volatile int32_t *h_signal, float b1, float b2, float eps,
+                                                    int64_t step, float scale, int sparse_adam, int n_threads) {
+    if (cols <= 0 || bsz < 0 || step < 1) {
+        clmgs_set_error("cpu_adam: bad arguments (cols=%d bsz=%d step=%lld)", cols, bsz, (long long)step);
+        return CLMGS_ERR_INVALID;
+    }
+    if (n_threads <= 0) n_threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    n_threads = std::min(n_threads, 256);
+    AdamConst c;
+    c.b1 = b1; c.b2 = b2; c.eps = eps; c.scale = scale;
+    c.inv_bc1 = (float)(1.0 / (1.0 - pow((double)b1, (double)step)));
+    c.bc2_rsqrt = (float)(1.0 / sqrt(1.0 - pow((double)b2, (double)step)));
+    auto worker = [&](int tid) {
+        for (int m = 0; m <= bsz; ++m) {
+            if (m == 0 && sparse_adam) continue;        // untouched rows: no update at all
+            if (m >= 1 && h_signal) wait_flag(h_signal + (m - 1));  // gradients of camera m-1 have landed
+            const int64_t lo = row_offsets[m], hi = row_offsets[m + 1], n = hi - lo;
+            const int64_t a = lo + n * tid / n_threads, b = lo + n * (tid + 1) / n_threads;
+            for (int64_t r = a; r < b; ++r) {
+                const int64_t base = (int64_t)host_rows[r] * cols;
+                if (r + 4 < b) {
+                    const int64_t nb = (int64_t)host_rows[r + 4] * cols;
+                    _mm_prefetch((const char *)(host_param + nb), _MM_HINT_T0);
+                    _mm_prefetch((const char *)(host_grad + nb), _MM_HINT_T0);
+                    _mm_prefetch((const char *)(host_exp_avg + nb), _MM_HINT_T0);
+                    _mm_prefetch((const char *)(host_exp_avg_sq + nb), _MM_HINT_T0);
+                }
+                adam_row(host_param + base, host_grad + base, host_exp_avg + base, host_exp_avg_sq + base, col_lr,
+                         cols, c);
+            }
+        }
+    };
+    if (n_threads == 1) { worker(0); return CLMGS_OK; }
+    std::vector<std::thread> th;
+    th.reserve(n_threads);
+    for (int t = 0; t < n_threads; ++t) th.emplace_back(worker, t);
+    for (auto &t : th) t.join();
+    return CLMGS_OK;
+}
+
+// Deterministic TSP heuristic: nearest-neighbour tour from node 0, improved by
+// 2-opt and Or-opt passes until no move helps (n <= 64, so this is microseconds).
+CLMGS_EXPORT int clmgs_tsp_tour(const int32_t *host_dist, int n, int32_t *host_tour) {
+    if (n <= 0 || n > 4096) { clmgs_set_error("tsp: bad n=%d", n); return CLMGS_ERR_INVALID; }
+    auto D = [&](int a, int b) { return (int64_t)host_dist[a * n + b]; };
+    std::vector<int> tour(n);
+    std::vector<char> used(n, 0);
+    tour[0] = 0; used[0] = 1;
+    for (int i = 1; i < n; ++i) {
+        int best = -1;
+        for (int j = 0; j < n; ++j)
+            if (!used[j] && (best < 0 || D(tour[i - 1], j) < D(tour[i - 1], best))) best = j;
+        tour[i] = best; used[best] = 1;
+    }
+    if (n > 3) {
+        bool improved = true;
+        int rounds = 0;
+        while (improved && rounds++ < 100) {
+            improved = false;
+            for (int i = 0; i < n - 1; ++i)           // 2-opt on the closed tour
+                for (int j = i + 2; j < n; ++j) {
+                    if (i == 0 && j == n - 1) continue;
+                    int a = tour[i], b = tour[i + 1], c = tour[j], d = tour[(j + 1) % n];
+                    if (D(a, c) + D(b, d) < D(a, b) + D(c, d)) {
+                        std::reverse(tour.begin() + i + 1, tour.begin() + j + 1);
+                        improved = true;
+                    }
+                }
+            for (int i = 0; i < n; ++i) {             // Or-opt: move one city elsewhere
+                int prev = tour[(i + n - 1) % n], cur = tour[i], next = tour[(i + 1) % n];
+                int64_t gain = D(prev, cur) + D(cur, next) - D(prev, next);
+                if (gain <= 0) continue;
+                for (int j = 0; j < n; ++j) {
+                    if (j == i || (j + 1) % n == i) continue;
+                    int a = tour[j], b = tour[(j + 1) % n];
+                    if (D(a, cur) + D(cur, b) - D(a, b) < gain) {
+                        std::vector<int> t2;
+                        t2.reserve(n);
+                        for (int k = 0; k < n; ++k) {
+                            if (k == i) continue;
+                            t2.push_back(tour[k]);
+                            if (k == j) t2.push_back(cur);
+                        }
+                        tour.swap(t2);
+                        improved = true;
+                        break;
+                    }
+                }
+            }
+        }
+        // rotate so that the tour starts at camera 0 (as a fixed, reproducible anchor)
+        auto it = std::find(tour.begin(), tour.end(), 0);
+        std::rotate(tour.begin(), it, tour.end());
+    }
+    for (int i = 0; i < n; ++i) host_tour[i] = tour[i];
+    return CLMGS_OK;
+}

@@ -1,0 +1,277 @@
+// S2 / S6: movement of the offloaded 48-float (192 B) SH rows between pinned
+// host memory and HBM, with cross-camera retention.
+//
+// Reference: CK/clm_kernels.cu:5-289 moves every float with its own 4-byte
+// zero-copy access from only 32 CTAs.  Here a row is 12 x 16-byte accesses by
+// 12 consecutive lanes (a row of a pinned [N,48] fp32 table is 64-B aligned, so
+// float4 is always legal), the grid is sized to keep all 148 SMs issuing, and
+// each thread keeps UNROLL independent loads in flight -- what a PCIe-latency
+// bound transfer needs.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kRowF4 = 12;       // float4 per row
+constexpr int kThreads = 256;
+constexpr int kUnroll = 4;
+
+__device__ __forceinline__ float4 ld_stream(const float4 *p) {
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+
+inline unsigned grid_for(int64_t n_rows) {
+    int64_t work = ceil_div64(n_rows * kRowF4, (int64_t)kThreads * kUnroll);
+    int64_t cap = (int64_t)kNumSMs * 8;
+    return (unsigned)(work < 1 ? 1 : (work > cap ? cap : work));
+}
+
+// dst[dst_row(r)] = src[src_row(r)] for r in [0,n); row maps are functors.
+template <typename SrcMap, typename DstMap>
+__global__ void __launch_bounds__(kThreads)
+copy_rows_kernel(float4 *__restrict__ dst, const float4 *__restrict__ src, int64_t n, SrcMap smap, DstMap dmap) {
+    const int64_t total = n * kRowF4;
+    const int64_t stride = (int64_t)gridDim.x * kThreads;
+    for (int64_t e0 = (int64_t)blockIdx.x * kThreads + threadIdx.x; e0 < total; e0 += stride * kUnroll) {
+        float4 v[kUnroll];
+        int64_t d[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            int64_t e = e0 + u * stride;
+            d[u] = -1;
+            if (e < total) {
+                int64_t r = e / kRowF4;
+                int c = (int)(e - r * kRowF4);
+                v[u] = ld_stream(src + smap(r) * kRowF4 + c);
+                d[u] = dmap(r) * kRowF4 + c;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+            if (d[u] >= 0) dst[d[u]] = v[u];
+    }
+}
+
+template <typename SrcMap, typename DstMap>
+__global__ void __launch_bounds__(kThreads)
+accum_rows_kernel(float4 *__restrict__ dst, const float4 *__restrict__ src, int64_t n, SrcMap smap, DstMap dmap) {
+    const int64_t total = n * kRowF4;
+    const int64_t stride = (int64_t)gridDim.x * kThreads;
+    for (int64_t e0 = (int64_t)blockIdx.x * kThreads + threadIdx.x; e0 < total; e0 += stride * kUnroll) {
+        float4 v[kUnroll], o[kUnroll];
+        int64_t d[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            int64_t e = e0 + u * stride;
+            d[u] = -1;
+            if (e < total) {
+                int64_t r = e / kRowF4;
+                int c = (int)(e - r * kRowF4);
+                d[u] = dmap(r) * kRowF4 + c;
+                v[u] = ld_stream(src + smap(r) * kRowF4 + c);
+                o[u] = dst[d[u]];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+            if (d[u] >= 0) dst[d[u]] = make_float4(o[u].x + v[u].x, o[u].y + v[u].y, o[u].z + v[u].z, o[u].w + v[u].w);
+    }
+}
+
+struct Identity { __device__ int64_t operator()(int64_t r) const { return r; } };
+struct Map64 { const int64_t *p; __device__ int64_t operator()(int64_t r) const { return p[r]; } };
+struct Map32 { const int32_t *p; __device__ int64_t operator()(int64_t r) const { return p[r]; } };
+
+template <typename W>
+__device__ __forceinline__ bool test_bit(const void *bitmap, int64_t i, int bit) {
+    return (((const W *)bitmap)[i] >> bit) & 1;
+}
+__device__ __forceinline__ bool test_bit_any(const void *bitmap, int wb, int64_t i, int bit) {
+    switch (wb) {
+        case 1: return test_bit<uint8_t>(bitmap, i, bit);
+        case 2: return test_bit<uint16_t>(bitmap, i, bit);
+        case 4: return test_bit<uint32_t>(bitmap, i, bit);
+        default: return test_bit<uint64_t>(bitmap, i, bit);
+    }
+}
+
+// position of `id` in the ascending array ids[0..n) (it is known to be present)
+__device__ __forceinline__ int32_t rank_of(const int64_t *__restrict__ ids, int64_t n, int64_t id) {
+    int64_t lo = 0, hi = n - 1;
+    while (lo < hi) {
+        int64_t mid = (lo + hi) >> 1;
+        if (__ldg(ids + mid) < id) lo = mid + 1; else hi = mid;
+    }
+    return (int32_t)lo;
+}
+
+// One 16-lane group per destination row; lane 0 classifies and searches.
+__global__ void __launch_bounds__(kThreads)
+prefetch_next_kernel(float4 *__restrict__ d_next, const float4 *__restrict__ h_rows,
+                     const float4 *__restrict__ d_this, const int64_t *__restrict__ ids_this, int64_t n_this,
+                     const int64_t *__restrict__ ids_next, int64_t n_next, const void *__restrict__ bitmap, int wb,
+                     int bit_this, int32_t *__restrict__ src_map) {
+    const int sub = threadIdx.x & 15;
+    const int64_t groups = ((int64_t)gridDim.x * kThreads) >> 4;
+    for (int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4; r < n_next; r += groups) {
+        int64_t id = 0;
+        int32_t src = -1;
+        if (sub == 0) {
+            id = ids_next[r];
+            if (n_this > 0 && test_bit_any(bitmap, wb, id, bit_this)) src = rank_of(ids_this, n_this, id);
+            src_map[r] = src;
+        }
+        const unsigned gmask = 0xffffu << (threadIdx.x & 16);
+        id = __shfl_sync(gmask, id, 0, 16);
+        src = __shfl_sync(gmask, src, 0, 16);
+        if (sub < kRowF4) {
+            const float4 *s = src >= 0 ? d_this + (int64_t)src * kRowF4 + sub : h_rows + id * kRowF4 + sub;
+            d_next[r * kRowF4 + sub] = ld_stream(s);
+        }
+    }
+}
+
+// Part A: next_grad rows (retained or zero).  Part B: flush rows camera k+1 does not see.
+__global__ void __launch_bounds__(kThreads)
+grad_handoff_kernel(const float4 *__restrict__ d_grad, float4 *__restrict__ d_next_grad, float4 *__restrict__ h_grad,
+                    const int64_t *__restrict__ ids_this, int64_t n_this, int64_t n_next,
+                    const int32_t *__restrict__ src_map, const void *__restrict__ bitmap, int wb, int bit_next,
+                    int accum) {
+    const int sub = threadIdx.x & 15;
+    const int64_t groups = ((int64_t)gridDim.x * kThreads) >> 4;
+    const int64_t g0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4;
+    const unsigned gmask = 0xffffu << (threadIdx.x & 16);
+    for (int64_t r = g0; r < n_next; r += groups) {
+        int32_t src = sub == 0 ? src_map[r] : 0;
+        src = __shfl_sync(gmask, src, 0, 16);
+        if (sub < kRowF4)
+            d_next_grad[r * kRowF4 + sub] = src >= 0 ? d_grad[(int64_t)src * kRowF4 + sub] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (int64_t r = g0; r < n_this; r += groups) {
+        int64_t id = -1;
+        if (sub == 0) {
+            id = ids_this[r];
+            if (n_next > 0 && test_bit_any(bitmap, wb, id, bit_next)) id = -1;  // retained on the GPU
+        }
+        id = __shfl_sync(gmask, id, 0, 16);
+        if (id >= 0 && sub < kRowF4) {
+            float4 v = d_grad[r * kRowF4 + sub];
+            float4 *dst = h_grad + id * kRowF4 + sub;
+            if (accum) { float4 o = *dst; v = make_float4(o.x + v.x, o.y + v.y, o.z + v.z, o.w + v.w); }
+            *dst = v;
+        }
+    }
+}
+
+__global__ void set_signal_kernel(volatile int32_t *flags, int index, int value) {
+    __threadfence_system();  // everything this stream wrote to host memory is visible first
+    flags[index] = value;
+    __threadfence_system();
+}
+
+int check_align(const void *p, const char *what) {
+    CLMGS_REQUIRE((((uintptr_t)p) & 15) == 0, "%s must be 16-byte aligned", what);
+    return CLMGS_OK;
+}
+
+}  // namespace
+
+#define F4(p) reinterpret_cast<float4 *>(p)
+#define CF4(p) reinterpret_cast<const float4 *>(p)
+
+CLMGS_EXPORT int clmgs_rows_gather_i64(float *d_rows, const float *h_rows, const int64_t *ids, int64_t n,
+                                       void *stream) {
+    if (n == 0) return CLMGS_OK;
+    if (int rc = check_align(d_rows, "d_rows")) return rc;
+    if (int rc = check_align(h_rows, "h_rows")) return rc;
+    copy_rows_kernel<<<grid_for(n), kThreads, 0, as_stream(stream)>>>(F4(d_rows), CF4(h_rows), n, Map64{ids}, Identity{});
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_rows_gather_retention(float *d_rows, const float *h_rows, const float *d_prev_rows,
+                                             const int32_t *host_ids, const int32_t *prev_src_rows,
+                                             const int32_t *dst_rows_from_host, const int32_t *dst_rows_from_prev,
+                                             int64_t n_host, int64_t n_prev, void *stream) {
+    if (int rc = check_align(d_rows, "d_rows")) return rc;
+    cudaStream_t st = as_stream(stream);
+    if (n_host > 0) {
+        copy_rows_kernel<<<grid_for(n_host), kThreads, 0, st>>>(F4(d_rows), CF4(h_rows), n_host, Map32{host_ids},
+                                                               Map32{dst_rows_from_host});
+        CLMGS_LAUNCH_OK();
+    }
+    if (n_prev > 0) {
+        copy_rows_kernel<<<grid_for(n_prev), kThreads, 0, st>>>(F4(d_rows), CF4(d_prev_rows), n_prev,
+                                                               Map32{prev_src_rows}, Map32{dst_rows_from_prev});
+        CLMGS_LAUNCH_OK();
+    }
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_rows_scatter_grad_i64(const float *d_grad, float *h_grad, const int64_t *ids, int64_t n,
+                                             int accum, void *stream) {
+    if (n == 0) return CLMGS_OK;
+    if (int rc = check_align(h_grad, "h_grad")) return rc;
+    cudaStream_t st = as_stream(stream);
+    if (accum) accum_rows_kernel<<<grid_for(n), kThreads, 0, st>>>(F4(h_grad), CF4(d_grad), n, Identity{}, Map64{ids});
+    else copy_rows_kernel<<<grid_for(n), kThreads, 0, st>>>(F4(h_grad), CF4(d_grad), n, Identity{}, Map64{ids});
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_rows_scatter_grad_retention(const float *d_grad, float *h_grad, float *d_next_grad,
+                                                   const int32_t *host_ids, const int32_t *next_dst_rows,
+                                                   const int32_t *src_rows_to_host, const int32_t *src_rows_to_next,
+                                                   int64_t n_host, int64_t n_next, int accum, void *stream) {
+    cudaStream_t st = as_stream(stream);
+    if (n_host > 0) {
+        if (accum) accum_rows_kernel<<<grid_for(n_host), kThreads, 0, st>>>(F4(h_grad), CF4(d_grad), n_host, Map32{src_rows_to_host}, Map32{host_ids});
+        else copy_rows_kernel<<<grid_for(n_host), kThreads, 0, st>>>(F4(h_grad), CF4(d_grad), n_host, Map32{src_rows_to_host}, Map32{host_ids});
+        CLMGS_LAUNCH_OK();
+    }
+    if (n_next > 0) {
+        if (accum) accum_rows_kernel<<<grid_for(n_next), kThreads, 0, st>>>(F4(d_next_grad), CF4(d_grad), n_next, Map32{src_rows_to_next}, Map32{next_dst_rows});
+        else copy_rows_kernel<<<grid_for(n_next), kThreads, 0, st>>>(F4(d_next_grad), CF4(d_grad), n_next, Map32{src_rows_to_next}, Map32{next_dst_rows});
+        CLMGS_LAUNCH_OK();
+    }
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_set_signal(int32_t *h_flags, int index, int value, void *stream) {
+    set_signal_kernel<<<1, 1, 0, as_stream(stream)>>>(h_flags, index, value);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_rows_prefetch_next(float *d_next_rows, const float *h_rows, const float *d_this_rows,
+                                          const int64_t *ids_this, int64_t n_this, const int64_t *ids_next,
+                                          int64_t n_next, const void *bitmap, int word_bytes, int bit_this,
+                                          int32_t *src_map, void *stream) {
+    if (n_next == 0) return CLMGS_OK;
+    CLMGS_REQUIRE(word_bytes == 1 || word_bytes == 2 || word_bytes == 4 || word_bytes == 8, "bad word_bytes");
+    int64_t blocks = ceil_div64(n_next * 16, kThreads);
+    int64_t cap = (int64_t)kNumSMs * 8;
+    prefetch_next_kernel<<<(unsigned)(blocks > cap ? cap : blocks), kThreads, 0, as_stream(stream)>>>(
+        F4(d_next_rows), CF4(h_rows), CF4(d_this_rows), ids_this, n_this, ids_next, n_next, bitmap, word_bytes,
+        bit_this, src_map);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_rows_grad_handoff(const float *d_grad_this, float *d_next_grad, float *h_grad,
+                                         const int64_t *ids_this, int64_t n_this, int64_t n_next,
+                                         const int32_t *src_map, const void *bitmap, int word_bytes, int bit_next,
+                                         int accum, void *stream) {
+    int64_t n = n_this > n_next ? n_this : n_next;
+    if (n == 0) return CLMGS_OK;
+    CLMGS_REQUIRE(word_bytes == 1 || word_bytes == 2 || word_bytes == 4 || word_bytes == 8, "bad word_bytes");
+    int64_t blocks = ceil_div64(n * 16, kThreads);
+    int64_t cap = (int64_t)kNumSMs * 8;
+    grad_handoff_kernel<<<(unsigned)(blocks > cap ? cap : blocks), kThreads, 0, as_stream(stream)>>>(
+        CF4(d_grad_this), F4(d_next_grad), F4(h_grad), ids_this, n_this, n_next, src_map, bitmap, word_bytes,
+        bit_next, accum);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}

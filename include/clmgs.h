@@ -245,7 +245,9 @@ int clmgs_compute_cnt_d(const void *bitmap, int word_bytes, int bsz, int64_t N, 
 int clmgs_bitmap_permute(const void *bitmap_in, void *bitmap_out, int word_bytes, int bsz,
                          const int32_t *order /* host, [bsz] */, int64_t N, void *stream);
 /* Sampled pairwise XOR distance matrix of engine.py:159-175: dist[i*bsz+j] =
- * #samples where cameras i and j differ (int32 [bsz*bsz], zeroed inside). */
+ * #samples where cameras i and j differ.  Here bit c of a word = camera c.
+ * dist must hold 2*bsz*bsz int32: the first bsz*bsz are the matrix, the rest
+ * is working space (co-visibility counts).  Zeroed inside. */
 int clmgs_bitmap_distance(const void *bitmap, int word_bytes, int bsz, const int64_t *sample_ids,
                           int64_t n_samples, int32_t *dist, void *stream);
 /* Groups Gaussian ids by ffs value (the torch.sort + unique_consecutive +

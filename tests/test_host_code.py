@@ -1,0 +1,100 @@
+"""CPU-side product code (no GPU needed): the C ABI loads and exports every
+declared symbol, host Adam and the TSP heuristic work, layout rules hold."""
+import os
+import re
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+import oracle
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_abi_exports_every_declared_symbol():
+    from clmgs import _lib
+    L = _lib.lib()
+    assert len(L.protos) >= 38
+    assert L.missing_symbols() == []
+    assert L.call("clmgs_abi_version") == 1
+    out = subprocess.check_output(["nm", "-D", "--defined-only", _lib.LIB_PATH], text=True)
+    exported = set(re.findall(r"\b(clmgs_\w+)\b", out))
+    assert set(L.protos) <= exported
+
+
+def test_abi_reports_errors_without_a_gpu():
+    from clmgs import _lib
+    import pytest
+    with pytest.raises(_lib.ClmgsError, match="degree"):
+        _lib.call("clmgs_sh_fwd", 10, 16, 7, None, None, None, None, None)
+    with pytest.raises(_lib.ClmgsError, match="tile_size"):
+        _lib.call("clmgs_rasterize_fwd", 1, 1, 0, None, None, None, None, None, 16, 16, 8, 1, 1, None, None, None,
+                  None, None, None)
+
+
+def test_product_never_touches_the_oracle():
+    bad = []
+    for dp, _, fs in os.walk(os.path.join(ROOT, "clm-gs_b200")):
+        if "build" in dp.split(os.sep):
+            continue
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                s = open(os.path.join(dp, f), errors="ignore").read()
+                if re.search(r"import oracle|from oracle|clmgs_oracle|oracle/", s):
+                    bad.append(os.path.join(dp, f))
+    assert not bad, bad
+
+
+def test_cpu_adam_matches_oracle_and_waits_for_signals():
+    from clmgs import ops
+    rng = np.random.default_rng(0)
+    N, bsz = 5000, 4
+    p = rng.standard_normal((N, 48)).astype(np.float32)
+    g = rng.standard_normal((N, 48)).astype(np.float32)
+    m = np.zeros_like(p); v = np.zeros_like(p)
+    col_lr = np.array([2.5e-3] * 3 + [2.5e-3 / 20] * 45, np.float32)
+    key = rng.integers(0, bsz + 1, N)
+    rows = np.argsort(key, kind="stable").astype(np.int32)
+    offs = np.concatenate([[0], np.cumsum(np.bincount(key, minlength=bsz + 1))]).astype(np.int64)
+    for sparse in (0, 1):
+        pr, gr, mr, vr = p.copy(), g.copy(), m.copy(), v.copy()
+        sel = rows[offs[1]:] if sparse else rows
+        oracle.cpu_adam_rows(pr, gr, mr, vr, sel, col_lr, 0.9 ** 4, 0.999 ** 4, 1e-15 / 2, 2, 0.25)
+        pp, gg, mm, vv = p.copy(), g.copy(), m.copy(), v.copy()
+        signal = np.zeros(bsz, np.int32)
+
+        def fire():
+            for k in range(bsz):
+                time.sleep(0.02)
+                signal[k] = 1
+
+        th = threading.Thread(target=fire); th.start()
+        t0 = time.time()
+        ops.cpu_adam_batched_sparse_step(pp, gg, mm, vv, col_lr, rows, offs, bsz, signal, 0.9 ** 4, 0.999 ** 4,
+                                         1e-15 / 2, 2, 0.25, sparse, n_threads=3)
+        dt = time.time() - t0
+        th.join()
+        assert dt > 0.06, "did not wait for the per-camera signals"
+        np.testing.assert_allclose(pp, pr, rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(mm, mr, rtol=1e-5, atol=1e-8)
+        np.testing.assert_allclose(vv, vr, rtol=1e-5, atol=1e-10)
+        assert not gg[sel].any()
+        if sparse:
+            untouched = rows[: offs[1]]
+            assert (pp[untouched] == p[untouched]).all() and (gg[untouched] == g[untouched]).all()
+
+
+def test_tsp_tour_is_a_permutation_and_not_worse_than_identity():
+    from clmgs import ops
+    rng = np.random.default_rng(0)
+    for n in (4, 8, 16, 64):
+        pts = rng.random((n, 2))
+        d = (np.linalg.norm(pts[:, None] - pts[None], axis=-1) * 1000).astype(np.int32)
+        tour = ops.tsp_tour(d)
+        assert sorted(tour) == list(range(n)) and tour[0] == 0
+        cost = lambda t: sum(d[t[i], t[(i + 1) % n]] for i in range(n))
+        assert cost(tour) <= cost(list(range(n)))
+    assert ops.tsp_tour(np.zeros((1, 1), np.int32)) == [0]
