@@ -1,0 +1,325 @@
+"""Host orchestration of one CLM-offload training batch on B200 kernels.
+
+Keeps the contract of ``clm_offload_train_one_batch`` (strategies/clm_offload/engine.py:338-347,925):
+same arguments, returns ``(losses, ordered_cams, sparsity)``, same side effects on the model
+(GPU-resident attributes + their Adam state, pinned SH table + host Adam state, pinned gradient
+table left zeroed).  What changed underneath:
+
+  reference                                             here
+  --------------------------------------------------   ----------------------------------------------
+  packed projection x2 + cumsum + unique_consecutive   clmgs_cull_count/_emit: one projection pass for all
+                                                       cameras, bitmap + ballot compaction
+  bsz scatter_to_bit + randperm + (B,B,n) XOR tensor   bitmap comes from the cull; sampled distance kernel
+  torch.sort(N bytes) + unique_consecutive + split      counting sort by last-use key (group_by_ffs)
+  ~8 torch ops + 2 nonzero_static per camera            clmgs_rows_prefetch_next / _grad_handoff (no lists)
+  4 gathers + 3 activations + autograd                  clmgs_gather_activate / clmgs_activate_bwd_scatter
+  autograd graph per camera                             explicit forward + backward kernel calls
+  fused_ssim + torch.compile'd L1                       clmgs_loss_fwd_bwd (writes v_render_colors directly)
+
+Streams: compute = torch's current stream, SH-row traffic on ``comm_stream`` with events, host Adam
+on a python thread that drops the GIL inside the C call -- the reference's three-way overlap
+(engine.py:423-437, 464-641, 767-826).
+"""
+import math
+import threading
+
+import numpy as np
+import torch
+
+from . import ops
+
+TILE_SIZE = 16  # strategies/base_engine.py:15
+
+
+class StageTimer:
+    """CUDA-event stage timing on the stream each stage is launched on."""
+
+    def __init__(self, enabled=False):
+        self.enabled = enabled
+        self.pairs = []
+        self.totals = {}
+        self.counts = {}
+
+    class _Ctx:
+        def __init__(self, owner, name, stream):
+            self.o, self.name, self.stream = owner, name, stream
+
+        def __enter__(self):
+            if self.o.enabled:
+                self.s = torch.cuda.Event(enable_timing=True)
+                self.e = torch.cuda.Event(enable_timing=True)
+                self.s.record(self.stream or torch.cuda.current_stream())
+            return self
+
+        def __exit__(self, *a):
+            if self.o.enabled:
+                self.e.record(self.stream or torch.cuda.current_stream())
+                self.o.pairs.append((self.name, self.s, self.e))
+
+    def __call__(self, name, stream=None):
+        return StageTimer._Ctx(self, name, stream)
+
+    def collect(self):
+        """Call after a device synchronize."""
+        for name, s, e in self.pairs:
+            self.totals[name] = self.totals.get(name, 0.0) + s.elapsed_time(e)
+            self.counts[name] = self.counts.get(name, 0) + 1
+        self.pairs = []
+
+
+_NULL_TIMER = StageTimer(False)
+
+
+def calculate_filters(batched_cameras, gaussians, timer=_NULL_TIMER):
+    """strategies/base_engine.py:18-76.  Returns (filters, cull) where filters[c] is the ascending
+    int64 id list of camera c (views into one flat tensor) and cull carries the visibility bitmap."""
+    args = gaussians.args
+    viewmats = torch.stack([c.viewmat for c in batched_cameras])
+    Ks = torch.stack([c.create_k_on_gpu() for c in batched_cameras])
+    W, H = batched_cameras[0].image_width, batched_cameras[0].image_height
+    with timer("cull"):
+        cull = ops.cull(gaussians._xyz, gaussians._scaling, gaussians._rotation, viewmats, Ks, W, H,
+                        activated=False, radius_clip=args.radius_clip)
+    assert all(c > 0 for c in cull["counts"]), \
+        "every camera must see at least one Gaussian (strategies/base_engine.py:65-67)"
+    filters = list(torch.split(cull["gaussian_ids"], cull["counts"]))
+    return filters, cull
+
+
+def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, timer=_NULL_TIMER):
+    """engine.py:135-298: camera order (TSP over sampled visibility distance), ordered bitmap,
+    per-Gaussian last-use groups for the host Adam."""
+    bitmap = cull["bitmap"]
+    dev = bitmap.device
+    with timer("order"):
+        n_sampled = max(1, n_gaussians // (bsz * bsz) if bsz >= 32 else n_gaussians // 32)
+        stride = max(1, n_gaussians // n_sampled)
+        off = int(torch.randint(0, stride, (1,), generator=perm_generator).item()) if perm_generator is not None else 0
+        sample_ids = torch.arange(n_sampled, device=dev, dtype=torch.int64) * stride + off
+        sample_ids.clamp_(max=n_gaussians - 1)
+        dist = ops.bitmap_distance(bitmap, bsz, sample_ids).cpu().numpy()  # D2H sync (reference: .tolist())
+        ordered_cams = ops.tsp_tour(dist) if bsz > 1 else [0]
+        if args.reorder_by_min_sparsity_at_end and bsz > 1:
+            lens = [filters[c].shape[0] for c in ordered_cams]
+            mi = bsz - 1
+            for k in range(bsz - 1):
+                if lens[k] < lens[mi]:
+                    mi = k
+            ordered_cams = ordered_cams[mi + 1:] + ordered_cams[:mi + 1]
+        filters = [filters[i] for i in ordered_cams]
+        sparsity = [f.shape[0] / float(n_gaussians) for f in filters]
+        ordered_bitmap = ops.bitmap_permute(bitmap, bsz, ordered_cams)
+        ffs = ops.extract_ffs(ordered_bitmap)
+        rows_dev, counts = ops.group_by_ffs(ffs, bsz)
+        rows_host = torch.empty(n_gaussians, dtype=torch.int32).pin_memory()
+        rows_host.copy_(rows_dev, non_blocking=True)
+        counts_h = counts.cpu().numpy()  # sync: also completes the rows copy above (same stream)
+    offs = np.concatenate([[0], np.cumsum(counts_h)]).astype(np.int64)
+    # group m of the host Adam = rows whose last user is camera m-1 <-> ffs key bsz+1-m (engine.py:213)
+    keys = [0] + [bsz + 1 - m for m in range(1, bsz + 1)]
+    row_begin = np.ascontiguousarray(offs[keys], dtype=np.int64)
+    row_end = np.ascontiguousarray(offs[[k + 1 for k in keys]], dtype=np.int64)
+    return dict(ordered_cams=ordered_cams, filters=filters, sparsity=sparsity, ordered_bitmap=ordered_bitmap,
+                visibility=ffs, rows_host=rows_host, row_begin=row_begin, row_end=row_end)
+
+
+def forward_one_camera(gaussians, camera, ids, shs, background, timer=_NULL_TIMER):
+    """pipeline_forward_one_step_shs_inplace (engine.py:30-127) without autograd.  Returns a dict
+    with everything the backward needs."""
+    W, H = camera.image_width, camera.image_height
+    tw, th = math.ceil(W / float(TILE_SIZE)), math.ceil(H / float(TILE_SIZE))
+    with timer("gather_activate"):
+        means, scales, quats, opac = ops.gather_activate(gaussians._xyz, gaussians._scaling, gaussians._rotation,
+                                                         gaussians._opacity, ids)
+    with timer("projection_fwd"):
+        radii, means2d, depths, conics, _ = ops.projection_fwd(means, quats, scales, camera.viewmat[None],
+                                                               camera.K[None], W, H)
+    with timer("sh_fwd"):
+        colors = ops.sh_colors_fwd(gaussians.active_sh_degree, means, camera.campos, shs)
+    with timer("isect_sort"):
+        _, isect_ids, flatten_ids = ops.isect_tiles(means2d, radii, depths, TILE_SIZE, tw, th)
+        offsets = ops.isect_offset_encode(isect_ids, 1, tw, th)
+    bg = None if background is None else background.reshape(1, 3)
+    with timer("raster_fwd"):
+        rc, ra, last = ops.rasterize_fwd(means2d, conics, colors[None], opac[None], W, H, TILE_SIZE, offsets,
+                                         flatten_ids, bg)
+    return dict(means=means, scales=scales, quats=quats, opac=opac, radii=radii, means2d=means2d, conics=conics,
+                colors=colors, offsets=offsets, flatten_ids=flatten_ids, render=rc, alphas=ra, last=last, bg=bg,
+                n_isects=flatten_ids.shape[0])
+
+
+def backward_one_camera(gaussians, camera, ids, shs, shs_grad, fw, v_render, grads, timer=_NULL_TIMER):
+    """loss.backward() + spherical_harmonics_bwd_inplace + scatter_add_ (engine.py:703-742)."""
+    W, H = camera.image_width, camera.image_height
+    with timer("raster_bwd"):
+        v_means2d, v_conics, v_colors, v_opac, _ = ops.rasterize_bwd(
+            fw["means2d"], fw["conics"], fw["colors"][None], fw["opac"][None], W, H, TILE_SIZE, fw["offsets"],
+            fw["flatten_ids"], fw["alphas"], fw["last"], v_render, None, fw["bg"])
+    with timer("projection_bwd"):
+        v_means, v_quats, v_scales = ops.projection_bwd(fw["means"], fw["quats"], fw["scales"], camera.viewmat[None],
+                                                        camera.K[None], W, H, 0.3, fw["radii"], fw["conics"],
+                                                        v_means2d, None, v_conics)
+    with timer("sh_bwd"):
+        ops.sh_colors_bwd(gaussians.active_sh_degree, fw["means"], camera.campos, shs, v_colors[0], shs_grad, v_means)
+    with timer("activate_bwd_scatter"):
+        ops.activate_bwd_scatter(gaussians._scaling, gaussians._rotation, gaussians._opacity, ids, v_means, v_scales,
+                                 v_quats, v_opac[0], grads["xyz"], grads["scaling"], grads["rotation"],
+                                 grads["opacity"])
+    return v_means2d
+
+
+def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_grad_buffer, background, pipe_args,
+                                comm_stream, perm_generator, timer=None):
+    """One optimiser step over ``len(batched_cameras)`` cameras.  See the module docstring."""
+    timer = timer or _NULL_TIMER
+    args = gaussians.args
+    bsz = len(batched_cameras)
+    N = gaussians.n_gaussians
+    dev = gaussians._xyz.device
+    compute = torch.cuda.current_stream()
+    h_params = gaussians._parameters
+    h_grad = parameters_grad_buffer[:N]
+
+    # ---- stage 1: visibility + order ------------------------------------------------------------
+    with torch.no_grad():
+        filters, cull = calculate_filters(batched_cameras, gaussians, timer)
+        oc = order_calculation(filters, cull, N, bsz, perm_generator, args, timer)
+    ordered_cams, filters, sparsity = oc["ordered_cams"], oc["filters"], oc["sparsity"]
+    cams = [batched_cameras[i] for i in ordered_cams]
+    bitmap = oc["ordered_bitmap"]
+
+    # ---- stage 2: host Adam thread --------------------------------------------------------------
+    if not hasattr(gaussians, "signal_tensor_pinned") or gaussians.signal_tensor_pinned.shape[0] != bsz:
+        gaussians.signal_tensor_pinned = torch.zeros(bsz, dtype=torch.int32).pin_memory()
+    else:
+        gaussians.signal_tensor_pinned.zero_()
+    signal = gaussians.signal_tensor_pinned
+    cpu_adam = gaussians.optimizer.cpu_adam
+    worker_err = []
+
+    def cpuadam_thread():
+        try:
+            cpu_adam.batched_sparse_step(h_grad, bsz, oc["rows_host"], oc["row_begin"], oc["row_end"], signal,
+                                         1.0 / bsz, args.sparse_adam)
+        except Exception as e:  # surfaced after join
+            worker_err.append(e)
+
+    worker = threading.Thread(target=cpuadam_thread, daemon=True)
+    worker.start()
+    try:
+        return _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_grad, background, comm_stream,
+                              signal, timer, worker, worker_err)
+    except BaseException:
+        # never leave the host-Adam thread spinning on flags that will not come
+        torch.cuda.synchronize()
+        signal.fill_(1)
+        worker.join()
+        raise
+
+
+def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_grad, background, comm_stream, signal,
+                   timer, worker, worker_err):
+    args = gaussians.args
+    bsz = len(batched_cameras)
+    N = gaussians.n_gaussians
+    dev = gaussians._xyz.device
+    compute = torch.cuda.current_stream()
+    ordered_cams, sparsity = oc["ordered_cams"], oc["sparsity"]
+    cams = [batched_cameras[i] for i in ordered_cams]
+    bitmap = oc["ordered_bitmap"]
+
+    # ---- stage 3: state ---------------------------------------------------------------------------
+    grads = dict(xyz=torch.zeros_like(gaussians._xyz), opacity=torch.zeros_like(gaussians._opacity),
+                 scaling=torch.zeros_like(gaussians._scaling), rotation=torch.zeros_like(gaussians._rotation))
+    start_evt = torch.cuda.Event()
+    start_evt.record(compute)
+    comm_stream.wait_event(start_evt)  # filters / bitmap are ready for the copy stream
+    losses, keep = [], [cull, oc]
+    shs = shs_grad = shs_next = shs_grad_next = src_map = None
+    rows_ready = grad_ready = None
+
+    with torch.no_grad():
+        for k in range(bsz):
+            ids = filters[k]
+            n_k = ids.shape[0]
+            # -- 4.1 / 4.2: SH rows of this camera, prefetch of the next (copy stream) -------------
+            with torch.cuda.stream(comm_stream):
+                if k == 0:
+                    shs = torch.empty(n_k, 48, device=dev)
+                    shs_grad = torch.zeros(n_k, 48, device=dev)
+                    with timer("rows_load_first", comm_stream):
+                        ops.rows_gather(shs, h_params, ids)
+                    rows_ready = torch.cuda.Event()
+                    rows_ready.record(comm_stream)
+                    grad_ready = rows_ready
+                cur_rows_ready, cur_grad_ready = rows_ready, grad_ready
+                if k < bsz - 1:
+                    ids_next = filters[k + 1]
+                    shs_next = torch.empty(ids_next.shape[0], 48, device=dev)
+                    with timer("rows_prefetch", comm_stream):
+                        src_map = ops.rows_prefetch_next(shs_next, h_params, shs, ids, ids_next, bitmap,
+                                                         bsz - 1 - k)
+                    rows_ready = torch.cuda.Event()
+                    rows_ready.record(comm_stream)
+            for t in (shs, shs_grad):
+                t.record_stream(compute)
+
+            # -- 4.3: forward ---------------------------------------------------------------------
+            compute.wait_event(cur_rows_ready)
+            cam = cams[k]
+            fw = forward_one_camera(gaussians, cam, ids, shs, background, timer)
+            with timer("loss"):
+                loss_vec, v_render = ops.loss_fwd_bwd(fw["render"][0], cam.original_image, args.lambda_dssim,
+                                                      hwc=True)
+            losses.append(loss_vec[0])
+
+            # -- 4.4 / 4.5: backward ----------------------------------------------------------------
+            compute.wait_event(cur_grad_ready)
+            backward_one_camera(gaussians, cam, ids, shs, shs_grad, fw, v_render[None], grads, timer)
+            bwd_done = torch.cuda.Event()
+            bwd_done.record(compute)
+
+            # -- 4.6: gradient hand-off + signal (copy stream) -----------------------------------------
+            with torch.cuda.stream(comm_stream):
+                comm_stream.wait_event(bwd_done)
+                if k < bsz - 1:
+                    shs_grad_next = torch.empty_like(shs_next)
+                    with timer("grad_handoff", comm_stream):
+                        ops.rows_grad_handoff(shs_grad, shs_grad_next, h_grad, ids, shs_next.shape[0], src_map,
+                                              bitmap, bsz - 1 - (k + 1), accum=True)
+                    grad_ready = torch.cuda.Event()
+                    grad_ready.record(comm_stream)
+                else:
+                    with timer("grad_handoff", comm_stream):
+                        ops.rows_grad_handoff(shs_grad, None, h_grad, ids, 0, None, bitmap, 0, accum=True)
+                ops.set_signal(signal, k, 1)
+            keep.append((shs, shs_grad, fw, v_render, src_map))
+            if k < bsz - 1:
+                shs, shs_grad = shs_next, shs_grad_next
+
+        # ---- stage 5: GPU Adam (grads / bsz fused as grad_scale) ------------------------------------
+        with timer("gpu_adam"):
+            gaussians.optimizer.gpu_adam.step(grads, visibility=oc["visibility"] if args.sparse_adam else None,
+                                              grad_scale=1.0 / bsz)
+
+    worker.join()
+    if worker_err:
+        raise worker_err[0]
+    torch.cuda.synchronize()
+    if timer.enabled:
+        timer.collect()
+    gaussians.last_batch_stats = dict(n_visible=[f.shape[0] for f in filters],
+                                      n_isects=[kk[2]["n_isects"] for kk in keep[2:]])
+    return losses, ordered_cams, sparsity
+
+
+@torch.no_grad()
+def clm_offload_eval_one_cam(camera, gaussians, background, scene=None):
+    """engine.py:928-979, with the SH rows fetched by the zero-copy gather kernel instead of a
+    CPU-side torch.gather + .to('cuda').  Returns the [3,H,W] image."""
+    filters, _ = calculate_filters([camera], gaussians)
+    ids = filters[0]
+    shs = torch.empty(ids.shape[0], 48, device=ids.device)
+    ops.rows_gather(shs, gaussians._parameters, ids)
+    fw = forward_one_camera(gaussians, camera, ids, shs, background)
+    return fw["render"][0].permute(2, 0, 1).contiguous()

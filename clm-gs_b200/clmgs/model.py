@@ -1,0 +1,218 @@
+"""State the hot path touches: the split GPU / pinned-host Gaussian model and
+its optimiser hyper-parameters.
+
+Mirrors ``GaussianModelCLMOffload`` (strategies/clm_offload/gaussian_model.py:18,
+tensors :88-111, pinned buffers :33-44) and ``training_setup`` (:122-234) /
+``UnifiedAdam`` (optimizer.py:91-184) as far as one training iteration needs
+them.  Densification, ply/pt IO and the COLMAP readers are out of scope
+(SURVEY.md 2.1 rows 3, 15).
+
+Layout
+  GPU   _xyz [N,3], _opacity [N,1] (logit), _scaling [N,3] (log), _rotation [N,4] (raw wxyz)
+        + Adam moments for each (44 B + 88 B per Gaussian)
+  host  _parameters [N,48] = cat(f_dc[N,3], f_rest[N,45]) viewed as [16 bases][3 rgb]
+        (engine.py:71), parameters_grad_buffer [N,48], exp_avg / exp_avg_sq [N,48];
+        all pinned and mapped into the GPU's address space (768 B per Gaussian)
+"""
+from dataclasses import dataclass, field
+import math
+import os
+
+import numpy as np
+import torch
+
+from . import ops
+
+
+@dataclass
+class TrainArgs:
+    """The handful of reference flags the hot path reads (arguments/__init__.py:84-100,182-229)."""
+    bsz: int = 4
+    sparse_adam: bool = False
+    reorder_by_min_sparsity_at_end: bool = True
+    radius_clip: float = 0.0
+    sh_degree: int = 3
+    lr_scale_mode: str = "sqrt"
+    position_lr_init: float = 0.00016
+    position_lr_final: float = 0.0000016
+    position_lr_delay_mult: float = 0.01
+    position_lr_max_steps: int = 30_000
+    feature_lr: float = 0.0025
+    opacity_lr: float = 0.05
+    scaling_lr: float = 0.005
+    rotation_lr: float = 0.001
+    lambda_dssim: float = 0.2
+    spatial_lr_scale: float = 1.0
+    cpu_adam_threads: int = 0  # 0 = all hardware threads
+
+
+class _Group(dict):
+    pass
+
+
+class GpuAdam:
+    """Dense (torch fused-Adam rule, bias-corrected) or selective (masked, no bias
+    correction) Adam over the four GPU-resident tensors -- optimizer.py:47-88,124-129."""
+
+    def __init__(self, groups, sparse):
+        self.param_groups = groups
+        self.sparse = sparse
+        self.state = {}
+        self.step_count = 0
+        for g in groups:
+            p = g["params"][0]
+            self.state[g["name"]] = dict(exp_avg=torch.zeros_like(p), exp_avg_sq=torch.zeros_like(p))
+
+    @torch.no_grad()
+    def step(self, grads, visibility=None, grad_scale=1.0):
+        """grads: dict name -> dense grad tensor.  visibility: uint8/bool [N] (selective only)."""
+        self.step_count += 1
+        for g in self.param_groups:
+            p, st = g["params"][0], self.state[g["name"]]
+            b1, b2 = g["betas"]
+            if self.sparse:
+                ops.selective_adam(p, grads[g["name"]], st["exp_avg"], st["exp_avg_sq"], visibility, g["lr"], b1, b2,
+                                   g["eps"], grad_scale)
+            else:
+                ops.adam_dense(p, grads[g["name"]], st["exp_avg"], st["exp_avg_sq"], g["lr"], b1, b2, g["eps"],
+                               self.step_count, grad_scale)
+
+
+class CpuAdam:
+    """Host Adam over the pinned [N,48] SH table (the reference's cpu_adam.FusedCPUAdam,
+    optimizer.py:130-142): per-column learning rates, bias correction on."""
+
+    def __init__(self, param, columns_sizes, columns_lr, betas, eps, n_threads=0):
+        self.param = param
+        self.columns_lr = np.repeat(np.asarray(columns_lr, np.float32), columns_sizes).astype(np.float32)
+        self.betas = list(betas)
+        self.eps = eps
+        self.exp_avg = _pinned_zeros(param.shape)
+        self.exp_avg_sq = _pinned_zeros(param.shape)
+        self.step_count = 0
+        self.n_threads = n_threads
+
+    def batched_sparse_step(self, grad, batch_size, rows, row_begin, row_end, signal_tensor_pinned, scale,
+                            sparse_adam):
+        """engine.py:320-327.  Blocking; run it on a worker thread (ctypes drops the GIL)."""
+        self.step_count += 1
+        ops.cpu_adam_batched_sparse_step(self.param, grad, self.exp_avg, self.exp_avg_sq, self.columns_lr, rows,
+                                         row_begin, row_end, batch_size, signal_tensor_pinned, self.betas[0],
+                                         self.betas[1], self.eps, self.step_count, scale, sparse_adam, self.n_threads)
+
+
+class UnifiedAdam:
+    def __init__(self, gpu_adam, cpu_adam):
+        self.gpu_adam, self.cpu_adam = gpu_adam, cpu_adam
+
+
+def _pinned_zeros(shape):
+    t = torch.zeros(shape, dtype=torch.float32)
+    return t.pin_memory() if torch.cuda.is_available() else t
+
+
+def _pinned_empty(shape):
+    t = torch.empty(shape, dtype=torch.float32)
+    return t.pin_memory() if torch.cuda.is_available() else t
+
+
+def get_expon_lr_func(lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, max_steps=1000000):
+    """utils/general_utils.py get_expon_lr_func (log-linear interpolation with optional delay)."""
+
+    def helper(step):
+        if step < 0 or (lr_init == 0.0 and lr_final == 0.0):
+            return 0.0
+        if lr_delay_steps > 0:
+            delay_rate = lr_delay_mult + (1 - lr_delay_mult) * math.sin(0.5 * math.pi * min(max(step / lr_delay_steps, 0), 1))
+        else:
+            delay_rate = 1.0
+        t = min(max(step / max_steps, 0), 1)
+        return delay_rate * math.exp(math.log(lr_init) * (1 - t) + math.log(lr_final) * t)
+
+    return helper
+
+
+class GaussianModelCLMOffload:
+    def __init__(self, sh_degree=3, device="cuda:0"):
+        self.max_sh_degree = sh_degree
+        self.active_sh_degree = sh_degree
+        self.device = device
+        self.optimizer = None
+        self.args = None
+
+    # -- construction ----------------------------------------------------------------
+    def create_from_arrays(self, xyz, log_scale, raw_quat, opacity_logit, sh, capacity=None):
+        """sh may already be a pinned [capacity,48] torch tensor (large scenes) or a numpy array."""
+        dev = self.device
+        N = xyz.shape[0]
+        self._xyz = torch.from_numpy(np.ascontiguousarray(xyz)).to(dev)
+        self._opacity = torch.from_numpy(np.ascontiguousarray(opacity_logit).reshape(N, 1)).to(dev)
+        self._scaling = torch.from_numpy(np.ascontiguousarray(log_scale)).to(dev)
+        self._rotation = torch.from_numpy(np.ascontiguousarray(raw_quat)).to(dev)
+        if isinstance(sh, torch.Tensor):
+            self.parameters_buffer = sh
+        else:
+            self.parameters_buffer = _pinned_empty((capacity or N, 48))
+            self.parameters_buffer[:N].copy_(torch.from_numpy(np.ascontiguousarray(sh)))
+        self._parameters = self.parameters_buffer[:N]
+        self.parameters_grad_buffer = _pinned_zeros(tuple(self.parameters_buffer.shape))
+        return self
+
+    @property
+    def n_gaussians(self):
+        return self._xyz.shape[0]
+
+    def all_parameters(self):
+        return [self._xyz, self._opacity, self._scaling, self._rotation, self._parameters]
+
+    # -- optimiser (GM:122-234) --------------------------------------------------------
+    def training_setup(self, args: TrainArgs):
+        self.args = args
+        bsz = args.bsz
+        groups = [
+            _Group(name="xyz", params=[self._xyz], lr=args.position_lr_init * args.spatial_lr_scale),
+            _Group(name="opacity", params=[self._opacity], lr=args.opacity_lr),
+            _Group(name="scaling", params=[self._scaling], lr=args.scaling_lr),
+            _Group(name="rotation", params=[self._rotation], lr=args.rotation_lr),
+        ]
+        columns_lr = np.array([args.feature_lr, args.feature_lr / 20.0], np.float64)
+        betas, eps = [0.9, 0.999], 1e-15
+        assert args.lr_scale_mode == "sqrt", "overlapped host Adam only supports sqrt lr scaling (engine.py:861)"
+        lr_scale = math.sqrt(bsz)
+        for g in groups:
+            g["lr"] *= lr_scale
+            g["eps"] = eps / lr_scale
+            g["betas"] = [b ** bsz for b in betas]
+        cpu = CpuAdam(self._parameters, [3, 45], columns_lr * lr_scale, [b ** bsz for b in betas], eps / lr_scale,
+                      args.cpu_adam_threads)
+        self.optimizer = UnifiedAdam(GpuAdam(groups, args.sparse_adam), cpu)
+        self.xyz_scheduler_args = get_expon_lr_func(
+            lr_init=args.position_lr_init * args.spatial_lr_scale * lr_scale,
+            lr_final=args.position_lr_final * args.spatial_lr_scale * lr_scale,
+            lr_delay_mult=args.position_lr_delay_mult, max_steps=args.position_lr_max_steps)
+        return self
+
+    def update_learning_rate(self, iteration):
+        for g in self.optimizer.gpu_adam.param_groups:
+            if g["name"] == "xyz":
+                g["lr"] = self.xyz_scheduler_args(iteration)
+                return g["lr"]
+
+
+class Camera:
+    """Fields of scene/cameras.py the hot path reads."""
+
+    def __init__(self, viewmat, K, gt_image_u8, device="cuda:0", uid=0):
+        vm = torch.as_tensor(viewmat, dtype=torch.float32)
+        self.world_view_transform = vm.t().contiguous().to(device)  # transposed w2c, as the reference stores it
+        self.viewmat = vm.contiguous().to(device)
+        self.K = torch.as_tensor(K, dtype=torch.float32).contiguous().to(device)
+        c2w = torch.linalg.inv(vm.double()).float()
+        self.camtoworlds = c2w.unsqueeze(0).contiguous().to(device)
+        self.campos = c2w[:3, 3].contiguous().to(device)
+        self.original_image = torch.as_tensor(gt_image_u8).contiguous().to(device)  # uint8 [3,H,W]
+        self.image_height, self.image_width = int(self.original_image.shape[1]), int(self.original_image.shape[2])
+        self.uid = uid
+
+    def create_k_on_gpu(self):
+        return self.K

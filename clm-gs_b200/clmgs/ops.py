@@ -112,7 +112,8 @@ def projection_bwd(means, quats, scales, viewmats, Ks, width, height, eps2d, rad
     v_scales = torch.zeros(N, 3, device=dev)
     call("clmgs_projection_bwd", C, N, _f32c(means), _f32c(quats), _f32c(scales), _f32c(viewmats),
          _f32c(Ks), int(width), int(height), float(eps2d), radii.contiguous(), _f32c(conics),
-         _f32c(v_means2d), _f32c(v_depths), _f32c(v_conics), v_means, v_quats, v_scales, _st())
+         _f32c(v_means2d), None if v_depths is None else _f32c(v_depths), _f32c(v_conics), v_means, v_quats,
+         v_scales, _st())
     return v_means, v_quats, v_scales
 
 
@@ -336,12 +337,28 @@ def adam_dense(param, grad, exp_avg, exp_avg_sq, lr, b1, b2, eps, step, grad_sca
          float(grad_scale), int(step), param.numel(), _st())
 
 
-def cpu_adam_batched_sparse_step(param, grad, exp_avg, exp_avg_sq, col_lr, rows, row_offsets, bsz, signal, b1, b2,
-                                 eps, step, scale, sparse_adam, n_threads=0):
-    """All arguments are HOST tensors/arrays (pinned where the GPU also touches them).  Blocking."""
+def cpu_adam_batched_sparse_step(param, grad, exp_avg, exp_avg_sq, col_lr, rows, row_begin, row_end, bsz, signal,
+                                 b1, b2, eps, step, scale, sparse_adam, n_threads=0):
+    """All arguments are HOST tensors/arrays (pinned where the GPU also touches them).  Blocking.
+    Group m (m = 0..bsz) = rows[row_begin[m]:row_end[m]]."""
     call("clmgs_cpu_adam_batched_sparse_step", param, grad, exp_avg, exp_avg_sq, int(param.shape[1]), col_lr, rows,
-         row_offsets, int(bsz), signal, float(b1), float(b2), float(eps), int(step), float(scale), int(sparse_adam),
-         int(n_threads))
+         row_begin, row_end, int(bsz), signal, float(b1), float(b2), float(eps), int(step), float(scale),
+         int(sparse_adam), int(n_threads))
+
+
+def sh_colors_fwd(degree, means, campos, coeffs):
+    """Engine-fused: colours = clamp_min(SH(means - campos) + 0.5, 0).  coeffs [n,48] or [n,K,3]."""
+    n = means.shape[0]
+    K = coeffs.numel() // (3 * n) if n else 16
+    colors = torch.empty(n, 3, device=means.device)
+    call("clmgs_sh_colors_fwd", n, K, int(degree), means, campos, coeffs, colors, _st())
+    return colors
+
+
+def sh_colors_bwd(degree, means, campos, coeffs, v_colors, v_coeffs, v_means):
+    n = means.shape[0]
+    K = coeffs.numel() // (3 * n) if n else 16
+    call("clmgs_sh_colors_bwd", n, K, int(degree), means, campos, coeffs, _f32c(v_colors), v_coeffs, v_means, _st())
 
 
 def tsp_tour(dist):

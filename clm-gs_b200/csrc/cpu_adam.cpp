@@ -65,7 +65,7 @@ inline void wait_flag(const volatile int32_t *flag) {
 
 CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, float *host_exp_avg,
                                                     float *host_exp_avg_sq, int cols, const float *col_lr,
-                                                    const int32_t *host_rows, const int64_t *row_offsets, int bsz,
+                                                    const int32_t *host_rows, const int64_t *row_begin, const int64_t *row_end, int bsz,
                                                     const volatile int32_t *h_signal, float b1, float b2, float eps,
                                                     int64_t step, float scale, int sparse_adam, int n_threads) {
     if (cols <= 0 || bsz < 0 || step < 1) {
@@ -82,7 +82,7 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
         for (int m = 0; m <= bsz; ++m) {
             if (m == 0 && sparse_adam) continue;        // untouched rows: no update at all
             if (m >= 1 && h_signal) wait_flag(h_signal + (m - 1));  // gradients of camera m-1 have landed
-            const int64_t lo = row_offsets[m], hi = row_offsets[m + 1], n = hi - lo;
+            const int64_t lo = row_begin[m], hi = row_end[m], n = hi - lo;
             const int64_t a = lo + n * tid / n_threads, b = lo + n * (tid + 1) / n_threads;
             for (int64_t r = a; r < b; ++r) {
                 const int64_t base = (int64_t)host_rows[r] * cols;

@@ -122,7 +122,7 @@ projection_bwd_kernel(int C, int64_t N, const float *__restrict__ means, const f
     if (y * rz <= lim_y && y * rz >= -lim_y) v_mc[1] += -fy * rz2 * vJ12;
     else v_mc[2] += -fy * rz3 * vJ12 * ty;
     v_mc[2] += -fx * rz2 * vJ00 - fy * rz2 * vJ11 + 2.f * fx * tx * rz3 * vJ02 + 2.f * fy * ty * rz3 * vJ12;
-    v_mc[2] += v_depths[idx];
+    if (v_depths) v_mc[2] += v_depths[idx];
 
     // world->camera VJPs (CSRC/utils.cuh:241-280)
     float v_mean[3];

@@ -127,9 +127,10 @@ __device__ __forceinline__ void stage_rows(float *s, int stride, const float *g,
     }
 }
 
+template <bool ENGINE>
 __global__ void __launch_bounds__(kShRows)
-sh_fwd_kernel(int64_t N, int K, int degree, const float *__restrict__ dirs, const float *__restrict__ coeffs,
-              const uint8_t *__restrict__ masks, float *__restrict__ colors) {
+sh_fwd_kernel(int64_t N, int K, int degree, const float *__restrict__ dirs, const float *__restrict__ campos,
+              const float *__restrict__ coeffs, const uint8_t *__restrict__ masks, float *__restrict__ colors) {
     extern __shared__ float s_rows[];
     const int row_len = K * 3, stride = row_len | 1;
     int64_t base = (int64_t)blockIdx.x * kShRows;
@@ -142,6 +143,7 @@ sh_fwd_kernel(int64_t N, int K, int degree, const float *__restrict__ dirs, cons
     float x = 0.f, y = 0.f, z = 0.f;
     if (degree >= 1) {
         float dx = dirs[3 * i], dy = dirs[3 * i + 1], dz = dirs[3 * i + 2];
+        if (ENGINE) { dx -= campos[0]; dy -= campos[1]; dz -= campos[2]; }
         float inorm = rsqrtf(dx * dx + dy * dy + dz * dz);
         x = dx * inorm; y = dy * inorm; z = dz * inorm;
     }
@@ -158,6 +160,7 @@ sh_fwd_kernel(int64_t N, int K, int degree, const float *__restrict__ dirs, cons
             bl += b[k] * row[3 * k + 2];
         }
     }
+    if (ENGINE) { r = fmaxf(r + 0.5f, 0.f); g = fmaxf(g + 0.5f, 0.f); bl = fmaxf(bl + 0.5f, 0.f); }
     colors[3 * i] = r; colors[3 * i + 1] = g; colors[3 * i + 2] = bl;
 }
 
@@ -167,18 +170,32 @@ CLMGS_EXPORT int clmgs_sh_fwd(int64_t N, int K, int degree, const float *dirs, c
     CLMGS_REQUIRE(K >= (degree + 1) * (degree + 1) && K <= 25, "sh_fwd: K=%d too small for degree %d (or > 25)", K, degree);
     if (N == 0) return CLMGS_OK;
     size_t smem = (size_t)kShRows * ((K * 3) | 1) * sizeof(float);
-    sh_fwd_kernel<<<(unsigned)ceil_div64(N, kShRows), kShRows, smem, as_stream(stream)>>>(N, K, degree, dirs, coeffs,
-                                                                                         masks, colors);
+    sh_fwd_kernel<false><<<(unsigned)ceil_div64(N, kShRows), kShRows, smem, as_stream(stream)>>>(
+        N, K, degree, dirs, nullptr, coeffs, masks, colors);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_sh_colors_fwd(int64_t N, int K, int degree, const float *means, const float *campos,
+                                     const float *coeffs, float *colors, void *stream) {
+    CLMGS_REQUIRE(degree >= 0 && degree <= 4, "sh_colors_fwd: degree %d not in [0,4]", degree);
+    CLMGS_REQUIRE(K >= (degree + 1) * (degree + 1) && K <= 25, "sh_colors_fwd: K=%d too small for degree %d (or > 25)", K, degree);
+    if (N == 0) return CLMGS_OK;
+    size_t smem = (size_t)kShRows * ((K * 3) | 1) * sizeof(float);
+    sh_fwd_kernel<true><<<(unsigned)ceil_div64(N, kShRows), kShRows, smem, as_stream(stream)>>>(
+        N, K, degree, means, campos, coeffs, nullptr, colors);
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }
 
 // Backward: rows of coeffs AND of v_coeffs go through shared memory so that
 // both the read and the read-modify-write of the 192-B rows are coalesced.
+template <bool ENGINE>
 __global__ void __launch_bounds__(kShRows)
-sh_bwd_kernel(int64_t N, int K, int degree, const float *__restrict__ dirs, const float *__restrict__ coeffs,
-              const uint8_t *__restrict__ masks, const float *__restrict__ v_colors, float *__restrict__ v_coeffs,
-              int accumulate, float *__restrict__ v_dirs) {
+sh_bwd_kernel(int64_t N, int K, int degree, const float *__restrict__ dirs, const float *__restrict__ campos,
+              const float *__restrict__ coeffs, const uint8_t *__restrict__ masks,
+              const float *__restrict__ v_colors, float *__restrict__ v_coeffs, int accumulate,
+              float *__restrict__ v_dirs) {
     extern __shared__ float s_rows[];
     const int row_len = K * 3, stride = row_len | 1;
     int64_t base = (int64_t)blockIdx.x * kShRows;
@@ -195,12 +212,22 @@ sh_bwd_kernel(int64_t N, int K, int degree, const float *__restrict__ dirs, cons
             float x = 0.f, y = 0.f, z = 0.f, inorm = 0.f;
             if (degree >= 1) {
                 float dx = dirs[3 * i], dy = dirs[3 * i + 1], dz = dirs[3 * i + 2];
+                if (ENGINE) { dx -= campos[0]; dy -= campos[1]; dz -= campos[2]; }
                 inorm = rsqrtf(dx * dx + dy * dy + dz * dz);
                 x = dx * inorm; y = dy * inorm; z = dz * inorm;
             }
             float b[25], bx[25], by[25], bz[25];
             sh_basis_grad(degree, x, y, z, b, bx, by, bz);
             float vr = v_colors[3 * i], vg = v_colors[3 * i + 1], vb = v_colors[3 * i + 2];
+            if (ENGINE) {  // gradient of clamp_min(c + 0.5, 0): passes where c + 0.5 >= 0
+                float cr = 0.f, cg = 0.f, cb = 0.f;
+#pragma unroll
+                for (int k = 0; k < 25; ++k)
+                    if (k < nb) { cr += b[k] * row[3 * k]; cg += b[k] * row[3 * k + 1]; cb += b[k] * row[3 * k + 2]; }
+                if (cr + 0.5f < 0.f) vr = 0.f;
+                if (cg + 0.5f < 0.f) vg = 0.f;
+                if (cb + 0.5f < 0.f) vb = 0.f;
+            }
             float vx = 0.f, vy = 0.f, vz = 0.f;
 #pragma unroll
             for (int k = 0; k < 25; ++k) {
@@ -218,16 +245,23 @@ sh_bwd_kernel(int64_t N, int K, int degree, const float *__restrict__ dirs, cons
             if (v_dirs) {
                 if (degree >= 1) {
                     float dot = vx * x + vy * y + vz * z;
-                    v_dirs[3 * i] = (vx - dot * x) * inorm;
-                    v_dirs[3 * i + 1] = (vy - dot * y) * inorm;
-                    v_dirs[3 * i + 2] = (vz - dot * z) * inorm;
+                    if (ENGINE) {  // dirs = means - campos: v_means += v_dirs
+                        v_dirs[3 * i] += (vx - dot * x) * inorm;
+                        v_dirs[3 * i + 1] += (vy - dot * y) * inorm;
+                        v_dirs[3 * i + 2] += (vz - dot * z) * inorm;
+                    } else {
+                        v_dirs[3 * i] = (vx - dot * x) * inorm;
+                        v_dirs[3 * i + 1] = (vy - dot * y) * inorm;
+                        v_dirs[3 * i + 2] = (vz - dot * z) * inorm;
+                    }
+                } else if (ENGINE) {
                 } else {
                     v_dirs[3 * i] = v_dirs[3 * i + 1] = v_dirs[3 * i + 2] = 0.f;
                 }
             }
         } else {
             for (int k = 0; k < row_len; ++k) row[k] = 0.f;
-            if (v_dirs) v_dirs[3 * i] = v_dirs[3 * i + 1] = v_dirs[3 * i + 2] = 0.f;
+            if (v_dirs && !ENGINE) v_dirs[3 * i] = v_dirs[3 * i + 1] = v_dirs[3 * i + 2] = 0.f;
         }
     }
     __syncthreads();
@@ -249,8 +283,21 @@ CLMGS_EXPORT int clmgs_sh_bwd(int64_t N, int K, int degree, const float *dirs, c
     CLMGS_REQUIRE(K >= (degree + 1) * (degree + 1) && K <= 25, "sh_bwd: K=%d too small for degree %d (or > 25)", K, degree);
     if (N == 0) return CLMGS_OK;
     size_t smem = (size_t)kShRows * ((K * 3) | 1) * sizeof(float);
-    sh_bwd_kernel<<<(unsigned)ceil_div64(N, kShRows), kShRows, smem, as_stream(stream)>>>(
-        N, K, degree, dirs, coeffs, masks, v_colors, v_coeffs, accumulate, v_dirs);
+    sh_bwd_kernel<false><<<(unsigned)ceil_div64(N, kShRows), kShRows, smem, as_stream(stream)>>>(
+        N, K, degree, dirs, nullptr, coeffs, masks, v_colors, v_coeffs, accumulate, v_dirs);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_sh_colors_bwd(int64_t N, int K, int degree, const float *means, const float *campos,
+                                     const float *coeffs, const float *v_colors, float *v_coeffs, float *v_means,
+                                     void *stream) {
+    CLMGS_REQUIRE(degree >= 0 && degree <= 4, "sh_colors_bwd: degree %d not in [0,4]", degree);
+    CLMGS_REQUIRE(K >= (degree + 1) * (degree + 1) && K <= 25, "sh_colors_bwd: K=%d too small for degree %d (or > 25)", K, degree);
+    if (N == 0) return CLMGS_OK;
+    size_t smem = (size_t)kShRows * ((K * 3) | 1) * sizeof(float);
+    sh_bwd_kernel<true><<<(unsigned)ceil_div64(N, kShRows), kShRows, smem, as_stream(stream)>>>(
+        N, K, degree, means, campos, coeffs, nullptr, v_colors, v_coeffs, 1, v_means);
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }

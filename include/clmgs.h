@@ -101,7 +101,8 @@ int clmgs_activate_bwd_scatter(const float *log_scale, const float *raw_quat,
  * row-major world->camera, Ks [C,3,3]; outputs radii [C,N] i32, means2d
  * [C,N,2], depths [C,N], conics [C,N,3], compensations [C,N] or NULL.
  * Unlike the reference (torch::empty) culled rows are written as zeros.
- * bwd accumulates (+=) into v_means/v_quats/v_scales, which the caller zeroes.
+ * bwd accumulates (+=) into v_means/v_quats/v_scales, which the caller zeroes;
+ * v_depths may be NULL (== zeros, as in the CLM loss).
  * ------------------------------------------------------------------------- */
 int clmgs_projection_fwd(int C, int64_t N, const float *means, const float *quats,
                          const float *scales, const float *viewmats, const float *Ks, int width,
@@ -127,6 +128,17 @@ int clmgs_sh_fwd(int64_t N, int K, int degree, const float *dirs, const float *c
 int clmgs_sh_bwd(int64_t N, int K, int degree, const float *dirs, const float *coeffs,
                  const uint8_t *masks, const float *v_colors, float *v_coeffs, int accumulate,
                  float *v_dirs, void *stream);
+
+/* Engine-fused colour stage (engine.py:67-78 forward, :709-716 backward):
+ * dirs = means - campos is formed on the fly, the forward applies
+ * clamp_min(c + 0.5, 0), the backward re-derives the clamp mask (c + 0.5 >= 0,
+ * torch.clamp_min's rule) instead of keeping an autograd graph, accumulates
+ * (+=) into the retained SH gradient rows and adds v_dirs into v_means (+=). */
+int clmgs_sh_colors_fwd(int64_t N, int K, int degree, const float *means, const float *campos,
+                        const float *coeffs, float *colors, void *stream);
+int clmgs_sh_colors_bwd(int64_t N, int K, int degree, const float *means, const float *campos,
+                        const float *coeffs, const float *v_colors, float *v_coeffs,
+                        float *v_means, void *stream);
 
 /* ---------------------------------------------------------------------------
  * S4  Tile intersection, sort, offsets.  isect_tiles_tensor
@@ -303,15 +315,17 @@ int clmgs_adam_dense(float *param, const float *grad, float *exp_avg, float *exp
  * Blocking; releases nothing itself -- call it from a thread that does not
  * hold the GIL (ctypes does that).  For m in 0..bsz: waits (spins with pause)
  * until h_signal[m-1] != 0 for m >= 1, then updates rows
- * host_rows[row_offsets[m] .. row_offsets[m+1]) of the pinned [N,48] tensors.
+ * host_rows[row_begin[m] .. row_end[m]) of the pinned [N,48] tensors (group m
+ * = rows whose last user is camera m-1; group 0 = untouched rows).
  * Group 0 (rows untouched this batch) is skipped when sparse_adam != 0.
  * Gradients are multiplied by `scale`, and zeroed in place afterwards
  * (the reference's version=3).  n_threads <= 0 picks hardware concurrency.
  * ------------------------------------------------------------------------- */
 int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, float *host_exp_avg,
                                        float *host_exp_avg_sq, int cols, const float *col_lr,
-                                       const int32_t *host_rows, const int64_t *row_offsets,
-                                       int bsz, const volatile int32_t *h_signal, float b1,
+                                       const int32_t *host_rows, const int64_t *row_begin,
+                                       const int64_t *row_end, int bsz,
+                                       const volatile int32_t *h_signal, float b1,
                                        float b2, float eps, int64_t step, float scale,
                                        int sparse_adam, int n_threads);
 

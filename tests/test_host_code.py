@@ -73,7 +73,7 @@ def test_cpu_adam_matches_oracle_and_waits_for_signals():
 
         th = threading.Thread(target=fire); th.start()
         t0 = time.time()
-        ops.cpu_adam_batched_sparse_step(pp, gg, mm, vv, col_lr, rows, offs, bsz, signal, 0.9 ** 4, 0.999 ** 4,
+        ops.cpu_adam_batched_sparse_step(pp, gg, mm, vv, col_lr, rows, offs[:-1].copy(), offs[1:].copy(), bsz, signal, 0.9 ** 4, 0.999 ** 4,
                                          1e-15 / 2, 2, 0.25, sparse, n_threads=3)
         dt = time.time() - t0
         th.join()
