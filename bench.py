@@ -1,0 +1,392 @@
+"""bench.py -- one CLM-offload training iteration per "step" on synthetic scenes.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config NAME]
+
+Metric (BASELINE.json): train iters/sec (one iteration = one optimiser step over a batch of
+cameras: cull -> order -> per camera {SH gather, project, SH colour, tile sort, rasterise, loss,
+backward, gradient offload} -> GPU Adam + host Adam).  Default workload = BASELINE.json
+configs[1]: 6M Gaussians, 1237x822, batch 4, on 1 B200.
+
+`value`  : iterations/s with the camera batches (matrices + uint8 GT images) already in HBM.
+`e2e`    : same loop, but every step first copies its camera batch from pinned host memory and
+           ends with a device->host read of the losses (the caller-visible API cost).
+`--impl reference`: the reference's CPU path (oracle port: C restatement of gsplat's kernels +
+           cpu-adam, all host threads) on a bounded sample of the same workload, extrapolated.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "clm-gs_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "train_iters_per_sec"
+UNIT = "iter/s"
+
+
+# ------------------------------------------------------------------------------------------
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm_gbs=float(d["hbm_gbs"]), source="measured (MEASURED_PEAKS.json)",
+                    sm_max_mhz=float(d.get("sm_max_mhz", 1965.0)))
+    return dict(hbm_gbs=6650.0, source="fallback (B200_PROFILING.md)", sm_max_mhz=1965.0)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+# kernels launched per C-ABI call (static table; the radix sort is CUB: 1 histogram + 1 scan-free
+# onesweep pass per 8 key bits for 46-bit keys -> 7 launches, + 2 copy-back memcpys not counted)
+LAUNCHES = dict(clmgs_cull_count=2, clmgs_cull_emit=1, clmgs_gather_activate=1, clmgs_projection_fwd=1,
+                clmgs_sh_colors_fwd=1, clmgs_isect_count=3, clmgs_isect_emit_sort=8, clmgs_isect_offset_encode=1,
+                clmgs_rasterize_fwd=1, clmgs_loss_fwd_bwd=3, clmgs_rasterize_bwd=1, clmgs_projection_bwd=1,
+                clmgs_sh_colors_bwd=1, clmgs_activate_bwd_scatter=1, clmgs_rows_gather_i64=1,
+                clmgs_rows_prefetch_next=1, clmgs_rows_grad_handoff=1, clmgs_set_signal=1,
+                clmgs_bitmap_distance=2, clmgs_bitmap_permute=1, clmgs_extract_ffs=1, clmgs_group_by_ffs=3,
+                clmgs_selective_adam=1, clmgs_adam_dense=1)
+
+
+def count_launches(lib):
+    """Wrap _Lib.call to count kernel launches of OUR library."""
+    counter = dict(n=0, calls=0)
+    orig = lib.call
+
+    def call(name, *a):
+        k = LAUNCHES.get(name, 0)
+        counter["n"] += k
+        counter["calls"] += 1 if k else 0
+        return orig(name, *a)
+
+    lib.call = call
+    from clmgs import _lib, ops
+    _lib.call = call
+    ops.call = call
+    return counter
+
+
+# ------------------------------------------------------------------------------------------
+def make_host_batches(spec, g, n_batches, bsz):
+    from clmgs import scene as S
+    V, K, P = S.make_cameras(spec, n_batches * bsz, g["extent"])
+    n_img = min(n_batches * bsz, 16)  # distinct GT images; reused cyclically (content does not affect cost)
+    gts = S.make_gt_images(spec, n_img)
+    return V, K, P, gts
+
+
+def algorithmic_bytes(stats, N, B, W, H):
+    """SURVEY.md 8d per-unit figures x units of this batch (see DESIGN.md 'Roofline arithmetic')."""
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    nv, ni = stats["n_visible"], stats["n_isects"]
+    per_cam = lambda f: [f(n, i) for n, i in zip(nv, ni)]
+    return dict(
+        cull=40 * N + 8 * sum(nv) + N * (1 if B <= 8 else 2 if B <= 16 else 4 if B <= 32 else 8),
+        gather_activate=sum(88 * n + 8 * n for n in nv),
+        projection_fwd=sum((40 + 28) * n for n in nv),
+        sh_fwd=sum((192 + 12 + 12) * n for n in nv),
+        isect_sort=sum(36 * i + 4 * tiles + 16 * n for n, i in zip(nv, ni)),
+        projection_bwd=sum((40 + 12 + 20 + 40) * n for n in nv),
+        sh_bwd=sum((192 + 384 + 12 + 12 + 24) * n for n in nv),
+        activate_bwd_scatter=sum((44 + 40 + 88 + 8) * n for n in nv),
+        loss=(3 * 4 + 3 * 1 + 3 * 4) * W * H * B,
+        gpu_adam=308 * N,
+        rows_load_first=192 * nv[0],
+    )
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+
+    from clmgs import _lib, engine, model, scene as S
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local_rank)
+    dev = "cuda:%d" % local_rank
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+    assert a.gpus == world, "--gpus %d but WORLD_SIZE=%d (launch with torch.distributed.run)" % (a.gpus, world)
+
+    spec = S.CONFIGS[a.config]
+    N = a.n_gaussians or spec.n_gaussians
+    bsz = a.bsz or spec.batch
+    spec = S.SceneSpec(spec.name, N, spec.width, spec.height, bsz, spec.shape, spec.fovx_deg, spec.index)
+    W, H = spec.width, spec.height
+    t0 = time.time()
+    # weak scaling over cameras: every rank trains its own replica on its own camera batches
+    # (multi-GPU sharded state: see DESIGN.md "Multi-GPU"; round 1 = replicas, no data-path collective)
+    sh_host = torch.empty(N, 48, dtype=torch.float32).pin_memory()
+    g = S.make_gaussians(spec, sh_out=sh_host.numpy())
+    args = model.TrainArgs(bsz=bsz, sparse_adam=a.sparse_adam, cpu_adam_threads=a.cpu_threads)
+    gm = model.GaussianModelCLMOffload(3, dev).create_from_arrays(g["xyz"], g["log_scale"], g["raw_quat"],
+                                                                 g["opacity_logit"], sh_host).training_setup(args)
+    n_batches = a.warmup + a.steps
+    spec_r = S.SceneSpec(spec.name, N, W, H, bsz, spec.shape, spec.fovx_deg, spec.index + 100 * rank)
+    V, K, P, gts = make_host_batches(spec_r, g, n_batches, bsz)
+    gts_pinned = torch.from_numpy(gts).pin_memory()
+    V_p, K_p = torch.from_numpy(V).pin_memory(), torch.from_numpy(K).pin_memory()
+    setup_s = time.time() - t0
+    comm = torch.cuda.Stream(priority=-1)
+    gen = torch.Generator().manual_seed(1234)
+    counter = count_launches(_lib.lib())
+
+    def cams_resident(b):
+        return [model.Camera(V[b * bsz + i], K[b * bsz + i], gts[(b * bsz + i) % len(gts)], dev, uid=b * bsz + i)
+                for i in range(bsz)]
+
+    def step_e2e(b):
+        """host camera batch -> device, iteration, losses -> host."""
+        cams = []
+        for i in range(bsz):
+            j = b * bsz + i
+            img = gts_pinned[j % len(gts)].to(dev, non_blocking=True)
+            cams.append(model.Camera(V_p[j], K_p[j], img, dev, uid=j))
+        losses, order, sp = engine.clm_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None,
+                                                               comm, gen)
+        return torch.stack(losses).cpu()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, first_batch, nsteps, timer=None):
+        barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_wall = time.time()
+        s.record()
+        for b in range(first_batch, first_batch + nsteps):
+            fn(b)
+        e.record()
+        barrier()
+        ms = s.elapsed_time(e)
+        wall = (time.time() - t_wall) * 1e3
+        ms = max(ms, wall) if abs(wall - ms) > 0.05 * wall else ms  # the step ends with a host join
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    # ---- value: camera batches resident in HBM ----------------------------------------------
+    resident = [cams_resident(b) for b in range(n_batches)]
+    timer = engine.StageTimer(False)
+
+    def step_resident(b):
+        engine.clm_offload_train_one_batch(gm, None, resident[b], gm.parameters_grad_buffer, None, None, comm, gen,
+                                           timer=timer)
+
+    for b in range(a.warmup):
+        step_resident(b)
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    counter["n"] = 0
+    ms_total = timed(step_resident, a.warmup, a.steps)
+    launches = counter["n"]
+    clk = clocks.stop()
+    ms_per_step = ms_total / a.steps
+    value = world * 1000.0 / ms_per_step  # whole-job iterations/s (weak scaling: one iteration per rank per step)
+
+    # ---- per-stage device times (separate pass: event pairs around every stage) -----------------
+    timer = engine.StageTimer(True)
+    nprof = min(a.steps, 3)
+    timed(step_resident, a.warmup, nprof)
+    stats = gm.last_batch_stats
+    stage_ms = {k: v / nprof for k, v in timer.totals.items()}
+    host_ms = dict(cpu_adam_thread_ms=round(stats.get("cpu_adam_thread_ms", 0.0), 2),
+                   cpu_adam_trailing_ms=round(stats.get("cpu_adam_trailing_ms", 0.0), 2))
+    timer = engine.StageTimer(False)
+
+    # ---- e2e: host buffers in, losses out ----------------------------------------------------------
+    step_e2e(0)
+    ms_e2e = timed(step_e2e, a.warmup, a.steps) / a.steps
+    h2d = bsz * (3 * H * W + 16 * 4 + 9 * 4)
+    d2h = bsz * 4
+
+    peaks = load_peaks()
+    out = None
+    if rank == 0:
+        ab = algorithmic_bytes(stats, N, bsz, W, H)
+        stages = {}
+        for k, ms in sorted(stage_ms.items(), key=lambda kv: -kv[1]):
+            ent = dict(ms_per_step=round(ms, 3))
+            if k in ab:
+                gbs = ab[k] / (ms * 1e-3) / 1e9
+                ent.update(algorithmic_mb=round(ab[k] / 1e6, 1), gb_s=round(gbs, 1), frac_of_hbm=round(gbs / peaks["hbm_gbs"], 3))
+            stages[k] = ent
+        # dominant HBM-bound kernel for the `roofline` object = the costliest stage that is one
+        # memory-bound kernel of ours
+        hbm_stages = [k for k in stage_ms if k in ("sh_bwd", "sh_fwd", "cull", "projection_fwd", "projection_bwd",
+                                                  "gather_activate", "activate_bwd_scatter", "gpu_adam")]
+        top = max(hbm_stages, key=lambda k: stage_ms[k])
+        n_launch = dict(cull=1, gpu_adam=4).get(top, bsz)
+        dur = stage_ms[top] / n_launch * 1e-3
+        achieved = ab[top] / n_launch / dur / 1e9
+        out = dict(metric=METRIC, value=round(value, 4), unit=UNIT, n_gpus=world, steps=a.steps, warmup=a.warmup,
+                   ms_per_step=round(ms_per_step, 3), higher_is_better=True, scaling="weak", vs_baseline=None,
+                   dtype="f32", data="synthetic",
+                   config=dict(workload="%s: %d Gaussians, %dx%d, batch %d cameras/iteration, SH degree 3, "
+                               "clm_offload (48-float SH rows + Adam state in pinned host memory)" % (spec.name, N, W, H, bsz),
+                               parallelism="replica per GPU (camera batches data-parallel, weak)" if world > 1 else "1 GPU",
+                               l2="inputs larger than L2 (Gaussian tables %.0f MB >> 126 MB); no explicit flush" % (N * 44 / 1e6),
+                               sparse_adam=bool(a.sparse_adam), cpu_adam_threads=a.cpu_threads or os.cpu_count(),
+                               visible_per_camera=stats["n_visible"], isects_per_camera=stats["n_isects"],
+                               setup_s=round(setup_s, 1)),
+                   e2e=dict(value=round(world * 1000.0 / ms_e2e, 4), unit=UNIT, h2d_bytes_per_step=h2d,
+                            d2h_bytes_per_step=d2h, ms_per_step=round(ms_e2e, 3)),
+                   gpu_launches=launches, clocks=clk,
+                   roofline=dict(bound="hbm", kernel=top, achieved=round(achieved, 1), peak=peaks["hbm_gbs"], unit="GB/s",
+                                 frac=round(achieved / peaks["hbm_gbs"], 4), traffic=None, peak_source=peaks["source"],
+                                 algorithmic_bytes_per_launch=int(ab[top] / n_launch),
+                                 launch_ms=round(dur * 1e3, 4)),
+                   stages=stages, host=host_ms)
+        if not a.no_cpu_baseline and world == 1:
+            out["cpu_baseline"] = cpu_baseline(a, spec, N, bsz, budget_s=a.cpu_budget)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
+
+
+# ------------------------------------------------------------------------------------------
+def cpu_baseline(a, spec, N, bsz, budget_s=20.0, steps=1):
+    """The reference's CPU path restated (oracle port) on a bounded sample, all host threads.
+    Sample: the first n_s Gaussians of the scene (ids are i.i.d., so a prefix is a uniform
+    subsample) and ONE camera of the batch at full resolution; extrapolated linearly in
+    (cameras x Gaussians) to the full workload."""
+    import oracle
+    from oracle import train_step as TS
+    from clmgs import model, scene as S
+
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    n_s = min(N, a.cpu_sample_gaussians)
+    W, H = spec.width, spec.height
+    sspec = S.SceneSpec(spec.name, N, W, H, 1, spec.shape, spec.fovx_deg, spec.index)
+    g_full_spacing = S.make_gaussians(S.SceneSpec(spec.name, N, W, H, 1, spec.shape, spec.fovx_deg, spec.index), n=n_s)
+    # same per-Gaussian statistics as the full scene: spacing (hence scale) must come from N, not n_s
+    spacing_full = (4.0 / 3.0 * np.pi * 27.0 / N) ** (1 / 3.0) if spec.shape == "object" else None
+    g = g_full_spacing
+    V, K, P = S.make_cameras(sspec, 1, g["extent"])
+    gts = S.make_gt_images(sspec, 1)
+    args = model.TrainArgs(bsz=1, sparse_adam=a.sparse_adam)
+    st = TS.new_state(g)
+    times = []
+    for _ in range(steps):
+        t0 = time.time()
+        TS.train_one_batch(st, V, K, P, gts, W, H, args, [0])
+        times.append(time.time() - t0)
+    t = float(np.median(times))
+    full_s = t * bsz * (N / float(n_s))
+    return dict(value=round(1.0 / full_s, 6), unit=UNIT, cores=cores, kind="port",
+                sample="oracle port (C restatement of gsplat kernels + cpu-adam, OpenMP where the loop is parallel), "
+                       "1 of %d cameras x first %d of %d Gaussians at %dx%d: %.2f s measured, extrapolated x%d x%.0f"
+                       % (bsz, n_s, N, W, H, t, bsz, N / float(n_s)),
+                sample_seconds=round(t, 3))
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    from clmgs import scene as S
+    spec = S.CONFIGS[a.config]
+    N = a.n_gaussians or spec.n_gaussians
+    bsz = a.bsz or spec.batch
+    # warm-up + steps, each a bounded sample
+    vals = []
+    for i in range(a.warmup + a.steps):
+        cb = cpu_baseline(a, spec, N, bsz)
+        if i >= a.warmup:
+            vals.append(cb)
+    v = float(np.median([c["value"] for c in vals]))
+    cb = vals[-1]
+    cb["value"] = v
+    return dict(impl="reference", metric=METRIC, value=v, unit=UNIT, n_gpus=a.gpus, steps=a.steps, warmup=a.warmup,
+                ms_per_step=round(1000.0 / v, 1), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
+                data="synthetic",
+                config=dict(workload="%s: %d Gaussians, %dx%d, batch %d (CPU, bounded sample extrapolated)"
+                            % (spec.name, N, spec.width, spec.height, bsz)),
+                cpu_baseline=cb, e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="c2_bicycle_6m")
+    ap.add_argument("--n-gaussians", type=int, default=0, help="override the config's Gaussian count (debug)")
+    ap.add_argument("--bsz", type=int, default=0)
+    ap.add_argument("--sparse-adam", action="store_true")
+    ap.add_argument("--cpu-threads", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=20.0)
+    ap.add_argument("--cpu-sample-gaussians", type=int, default=100_000)
+    a = ap.parse_args()
+    a.warmup = max(a.warmup, 0)
+    out = run_reference(a) if a.impl == "reference" else run_ours(a)
+    if out is not None:
+        print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

@@ -197,18 +197,25 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     cpu_adam = gaussians.optimizer.cpu_adam
     worker_err = []
 
+    worker_times = {}
+
     def cpuadam_thread():
+        import time as _t
+        t0 = _t.perf_counter()
         try:
             cpu_adam.batched_sparse_step(h_grad, bsz, oc["rows_host"], oc["row_begin"], oc["row_end"], signal,
                                          1.0 / bsz, args.sparse_adam)
         except Exception as e:  # surfaced after join
             worker_err.append(e)
+        worker_times["cpu_adam_thread_ms"] = (_t.perf_counter() - t0) * 1e3
 
     worker = threading.Thread(target=cpuadam_thread, daemon=True)
     worker.start()
     try:
-        return _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_grad, background, comm_stream,
-                              signal, timer, worker, worker_err)
+        out = _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_grad, background, comm_stream,
+                             signal, timer, worker, worker_err)
+        gaussians.last_batch_stats.update(worker_times)
+        return out
     except BaseException:
         # never leave the host-Adam thread spinning on flags that will not come
         torch.cuda.synchronize()
@@ -286,12 +293,12 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
                     shs_grad_next = torch.empty_like(shs_next)
                     with timer("grad_handoff", comm_stream):
                         ops.rows_grad_handoff(shs_grad, shs_grad_next, h_grad, ids, shs_next.shape[0], src_map,
-                                              bitmap, bsz - 1 - (k + 1), accum=True)
+                                              bitmap, bsz - 1 - k, bsz - 1 - (k + 1), accum=2)
                     grad_ready = torch.cuda.Event()
                     grad_ready.record(comm_stream)
                 else:
                     with timer("grad_handoff", comm_stream):
-                        ops.rows_grad_handoff(shs_grad, None, h_grad, ids, 0, None, bitmap, 0, accum=True)
+                        ops.rows_grad_handoff(shs_grad, None, h_grad, ids, 0, None, bitmap, bsz - 1 - k, 0, accum=2)
                 ops.set_signal(signal, k, 1)
             keep.append((shs, shs_grad, fw, v_render, src_map))
             if k < bsz - 1:
@@ -302,13 +309,18 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
             gaussians.optimizer.gpu_adam.step(grads, visibility=oc["visibility"] if args.sparse_adam else None,
                                               grad_scale=1.0 / bsz)
 
-    worker.join()
+    import time as _t
+    comm_stream.synchronize()
+    compute.synchronize()
+    t_join = _t.perf_counter()
+    worker.join()  # "trailing overhead": host Adam still running after the GPU finished (engine.py:888-917)
+    join_ms = (_t.perf_counter() - t_join) * 1e3
     if worker_err:
         raise worker_err[0]
     torch.cuda.synchronize()
     if timer.enabled:
         timer.collect()
-    gaussians.last_batch_stats = dict(n_visible=[f.shape[0] for f in filters],
+    gaussians.last_batch_stats = dict(cpu_adam_trailing_ms=join_ms, n_visible=[f.shape[0] for f in filters],
                                       n_isects=[kk[2]["n_isects"] for kk in keep[2:]])
     return losses, ordered_cams, sparsity
 

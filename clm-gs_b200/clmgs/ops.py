@@ -276,9 +276,9 @@ def rows_prefetch_next(d_next, h_rows, d_this, ids_this, ids_next, bitmap, bit_t
     return src_map
 
 
-def rows_grad_handoff(d_grad, d_next_grad, h_grad, ids_this, n_next, src_map, bitmap, bit_next, accum=True):
+def rows_grad_handoff(d_grad, d_next_grad, h_grad, ids_this, n_next, src_map, bitmap, bit_this, bit_next, accum=2):
     call("clmgs_rows_grad_handoff", d_grad, d_next_grad, h_grad, ids_this, ids_this.shape[0], int(n_next), src_map,
-         bitmap, bitmap.element_size(), int(bit_next), int(accum), _st())
+         bitmap, bitmap.element_size(), int(bit_this), int(bit_next), int(accum), _st())
 
 
 # --------------------------------------------------------------------------- A2 bitmaps

@@ -40,7 +40,8 @@ def make_gaussians(spec: SceneSpec, n=None, chunk=4_000_000, sh_out=None):
     """Returns dict of float32 arrays: xyz[N,3], log_scale[N,3], raw_quat[N,4],
     opacity_logit[N,1], sh[N,48].  ``sh_out`` may be a preallocated (pinned) [N,48]
     array that is filled in place (large scenes)."""
-    N = int(n if n is not None else spec.n_gaussians)
+    N = int(n if n is not None else spec.n_gaussians)   # how many to generate (a prefix of the scene)
+    NF = int(spec.n_gaussians)                          # the scene's size: fixes spacing / extent
     rng = np.random.default_rng(1234 + spec.index)
     xyz = np.empty((N, 3), np.float32)
     if spec.shape == "object":
@@ -53,17 +54,17 @@ def make_gaussians(spec: SceneSpec, n=None, chunk=4_000_000, sh_out=None):
             k = min(len(p), N - filled)
             xyz[filled:filled + k] = p[:k]
             filled += k
-        spacing = (4.0 / 3.0 * math.pi * 27.0 / N) ** (1.0 / 3.0)
+        spacing = (4.0 / 3.0 * math.pi * 27.0 / NF) ** (1.0 / 3.0)
         L = 3.0
     else:
-        L = 0.5 * math.sqrt(N / 1e4)
+        L = 0.5 * math.sqrt(NF / 1e4)
         for s in range(0, N, chunk):
             e = min(N, s + chunk)
             u = rng.random((e - s, 3), dtype=np.float32)
             xyz[s:e, 0] = (2 * u[:, 0] - 1) * L
             xyz[s:e, 1] = (2 * u[:, 1] - 1) * L
             xyz[s:e, 2] = u[:, 2] * 0.1 * L
-        spacing = (2 * L * 2 * L * 0.1 * L / N) ** (1.0 / 3.0)
+        spacing = (2 * L * 2 * L * 0.1 * L / NF) ** (1.0 / 3.0)
     log_scale = np.empty((N, 3), np.float32)
     raw_quat = np.empty((N, 4), np.float32)
     opacity = np.empty((N, 1), np.float32)

@@ -22,9 +22,13 @@ __device__ __forceinline__ float4 ld_stream(const float4 *p) {
     return v;
 }
 
+// Transfer kernels run on a side stream next to the render kernels and spend their time waiting on
+// PCIe: one 256-thread CTA per SM (12.5% of the thread slots) with 4 x 16 B in flight per thread is
+// ~2.4 MB outstanding -- far above the link's bandwidth-delay product -- and leaves the SMs to the
+// compute stream.  (Filling every slot starved the render kernels: measured 24 ms for a 0.4 ms Adam.)
 inline unsigned grid_for(int64_t n_rows) {
     int64_t work = ceil_div64(n_rows * kRowF4, (int64_t)kThreads * kUnroll);
-    int64_t cap = (int64_t)kNumSMs * 8;
+    int64_t cap = (int64_t)kNumSMs;
     return (unsigned)(work < 1 ? 1 : (work > cap ? cap : work));
 }
 
@@ -107,7 +111,8 @@ __device__ __forceinline__ int32_t rank_of(const int64_t *__restrict__ ids, int6
     return (int32_t)lo;
 }
 
-// One 16-lane group per destination row; lane 0 classifies and searches.
+// One 16-lane group handles 4 destination rows per iteration: lanes 0..3 classify one row each
+// (bitmap test + binary search), then lanes 0..11 move the four 192-B rows with 4 loads in flight.
 __global__ void __launch_bounds__(kThreads)
 prefetch_next_kernel(float4 *__restrict__ d_next, const float4 *__restrict__ h_rows,
                      const float4 *__restrict__ d_this, const int64_t *__restrict__ ids_this, int64_t n_this,
@@ -115,53 +120,93 @@ prefetch_next_kernel(float4 *__restrict__ d_next, const float4 *__restrict__ h_r
                      int bit_this, int32_t *__restrict__ src_map) {
     const int sub = threadIdx.x & 15;
     const int64_t groups = ((int64_t)gridDim.x * kThreads) >> 4;
-    for (int64_t r = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4; r < n_next; r += groups) {
-        int64_t id = 0;
-        int32_t src = -1;
-        if (sub == 0) {
-            id = ids_next[r];
-            if (n_this > 0 && test_bit_any(bitmap, wb, id, bit_this)) src = rank_of(ids_this, n_this, id);
-            src_map[r] = src;
+    const unsigned gmask = 0xffffu << (threadIdx.x & 16);
+    for (int64_t r0 = (((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4) * 4; r0 < n_next; r0 += groups * 4) {
+        int64_t my_id = 0;
+        int32_t my_src = -1;
+        if (sub < 4 && r0 + sub < n_next) {
+            my_id = ids_next[r0 + sub];
+            if (n_this > 0 && test_bit_any(bitmap, wb, my_id, bit_this)) my_src = rank_of(ids_this, n_this, my_id);
+            src_map[r0 + sub] = my_src;
         }
-        const unsigned gmask = 0xffffu << (threadIdx.x & 16);
-        id = __shfl_sync(gmask, id, 0, 16);
-        src = __shfl_sync(gmask, src, 0, 16);
-        if (sub < kRowF4) {
-            const float4 *s = src >= 0 ? d_this + (int64_t)src * kRowF4 + sub : h_rows + id * kRowF4 + sub;
-            d_next[r * kRowF4 + sub] = ld_stream(s);
+        float4 v[4];
+        bool live[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t id = __shfl_sync(gmask, my_id, u, 16);
+            const int32_t src = __shfl_sync(gmask, my_src, u, 16);
+            live[u] = sub < kRowF4 && r0 + u < n_next;
+            if (live[u]) v[u] = ld_stream(src >= 0 ? d_this + (int64_t)src * kRowF4 + sub : h_rows + id * kRowF4 + sub);
         }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (live[u]) d_next[(r0 + u) * kRowF4 + sub] = v[u];
     }
 }
 
 // Part A: next_grad rows (retained or zero).  Part B: flush rows camera k+1 does not see.
+// accum: 0 = store, 1 = read-modify-write over the link (the reference, CK/clm_kernels.cu:201),
+//        2 = RMW only for rows that were already flushed once in this batch.  A row was flushed
+//            before iff, among the cameras before the current run of consecutive visibility, some
+//            camera saw it: with hi = word >> (bit_this+1) that is (hi & (hi+1)) != 0.  Everything
+//            else is the first write to a zeroed row (cpu-adam leaves consumed rows zeroed) -> store.
+__device__ __forceinline__ uint64_t load_word(const void *bitmap, int wb, int64_t i) {
+    switch (wb) {
+        case 1: return ((const uint8_t *)bitmap)[i];
+        case 2: return ((const uint16_t *)bitmap)[i];
+        case 4: return ((const uint32_t *)bitmap)[i];
+        default: return ((const uint64_t *)bitmap)[i];
+    }
+}
+
 __global__ void __launch_bounds__(kThreads)
 grad_handoff_kernel(const float4 *__restrict__ d_grad, float4 *__restrict__ d_next_grad, float4 *__restrict__ h_grad,
                     const int64_t *__restrict__ ids_this, int64_t n_this, int64_t n_next,
-                    const int32_t *__restrict__ src_map, const void *__restrict__ bitmap, int wb, int bit_next,
-                    int accum) {
+                    const int32_t *__restrict__ src_map, const void *__restrict__ bitmap, int wb, int bit_this,
+                    int bit_next, int accum) {
     const int sub = threadIdx.x & 15;
     const int64_t groups = ((int64_t)gridDim.x * kThreads) >> 4;
     const int64_t g0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4;
     const unsigned gmask = 0xffffu << (threadIdx.x & 16);
-    for (int64_t r = g0; r < n_next; r += groups) {
-        int32_t src = sub == 0 ? src_map[r] : 0;
-        src = __shfl_sync(gmask, src, 0, 16);
-        if (sub < kRowF4)
-            d_next_grad[r * kRowF4 + sub] = src >= 0 ? d_grad[(int64_t)src * kRowF4 + sub] : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t r0 = g0 * 4; r0 < n_next; r0 += groups * 4) {
+        int32_t my_src = (sub < 4 && r0 + sub < n_next) ? src_map[r0 + sub] : -1;
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int32_t src = __shfl_sync(gmask, my_src, u, 16);
+            v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (sub < kRowF4 && src >= 0) v[u] = d_grad[(int64_t)src * kRowF4 + sub];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (sub < kRowF4 && r0 + u < n_next) d_next_grad[(r0 + u) * kRowF4 + sub] = v[u];
     }
-    for (int64_t r = g0; r < n_this; r += groups) {
-        int64_t id = -1;
-        if (sub == 0) {
-            id = ids_this[r];
-            if (n_next > 0 && test_bit_any(bitmap, wb, id, bit_next)) id = -1;  // retained on the GPU
+    for (int64_t r0 = g0 * 4; r0 < n_this; r0 += groups * 4) {
+        int64_t my_id = -1;
+        int my_rmw = 0;
+        if (sub < 4 && r0 + sub < n_this) {
+            my_id = ids_this[r0 + sub];
+            const uint64_t w = load_word(bitmap, wb, my_id);
+            if (n_next > 0 && ((w >> bit_next) & 1)) my_id = -1;  // retained on the GPU
+            else if (accum == 1) my_rmw = 1;
+            else if (accum == 2) { const uint64_t hi = w >> (bit_this + 1); my_rmw = (hi & (hi + 1)) != 0; }
         }
-        id = __shfl_sync(gmask, id, 0, 16);
-        if (id >= 0 && sub < kRowF4) {
-            float4 v = d_grad[r * kRowF4 + sub];
-            float4 *dst = h_grad + id * kRowF4 + sub;
-            if (accum) { float4 o = *dst; v = make_float4(o.x + v.x, o.y + v.y, o.z + v.z, o.w + v.w); }
-            *dst = v;
+        float4 v[4], o[4];
+        int64_t id[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            id[u] = __shfl_sync(gmask, my_id, u, 16);
+            const int rmw = __shfl_sync(gmask, my_rmw, u, 16);
+            o[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (sub < kRowF4 && id[u] >= 0) {
+                v[u] = d_grad[(r0 + u) * kRowF4 + sub];
+                if (rmw) o[u] = h_grad[id[u] * kRowF4 + sub];
+            }
         }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (sub < kRowF4 && id[u] >= 0)
+                h_grad[id[u] * kRowF4 + sub] = make_float4(o[u].x + v[u].x, o[u].y + v[u].y, o[u].z + v[u].z, o[u].w + v[u].w);
     }
 }
 
@@ -251,8 +296,8 @@ CLMGS_EXPORT int clmgs_rows_prefetch_next(float *d_next_rows, const float *h_row
                                           int32_t *src_map, void *stream) {
     if (n_next == 0) return CLMGS_OK;
     CLMGS_REQUIRE(word_bytes == 1 || word_bytes == 2 || word_bytes == 4 || word_bytes == 8, "bad word_bytes");
-    int64_t blocks = ceil_div64(n_next * 16, kThreads);
-    int64_t cap = (int64_t)kNumSMs * 8;
+    int64_t blocks = ceil_div64(n_next * 4, kThreads);
+    int64_t cap = (int64_t)kNumSMs;
     prefetch_next_kernel<<<(unsigned)(blocks > cap ? cap : blocks), kThreads, 0, as_stream(stream)>>>(
         F4(d_next_rows), CF4(h_rows), CF4(d_this_rows), ids_this, n_this, ids_next, n_next, bitmap, word_bytes,
         bit_this, src_map);
@@ -262,16 +307,17 @@ CLMGS_EXPORT int clmgs_rows_prefetch_next(float *d_next_rows, const float *h_row
 
 CLMGS_EXPORT int clmgs_rows_grad_handoff(const float *d_grad_this, float *d_next_grad, float *h_grad,
                                          const int64_t *ids_this, int64_t n_this, int64_t n_next,
-                                         const int32_t *src_map, const void *bitmap, int word_bytes, int bit_next,
-                                         int accum, void *stream) {
+                                         const int32_t *src_map, const void *bitmap, int word_bytes, int bit_this,
+                                         int bit_next, int accum, void *stream) {
     int64_t n = n_this > n_next ? n_this : n_next;
     if (n == 0) return CLMGS_OK;
     CLMGS_REQUIRE(word_bytes == 1 || word_bytes == 2 || word_bytes == 4 || word_bytes == 8, "bad word_bytes");
-    int64_t blocks = ceil_div64(n * 16, kThreads);
-    int64_t cap = (int64_t)kNumSMs * 8;
+    CLMGS_REQUIRE(accum >= 0 && accum <= 2, "grad_handoff: accum must be 0, 1 or 2");
+    int64_t blocks = ceil_div64(n * 4, kThreads);
+    int64_t cap = (int64_t)kNumSMs;
     grad_handoff_kernel<<<(unsigned)(blocks > cap ? cap : blocks), kThreads, 0, as_stream(stream)>>>(
         CF4(d_grad_this), F4(d_next_grad), F4(h_grad), ids_this, n_this, n_next, src_map, bitmap, word_bytes,
-        bit_next, accum);
+        bit_this, bit_next, accum);
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }

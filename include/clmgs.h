@@ -284,8 +284,11 @@ int clmgs_group_by_ffs(const uint8_t *ffs, int64_t N, int bsz, int32_t *out_ids,
  * clmgs_rows_grad_handoff: after the backward of camera k: next_grad[r'] =
  * grad_this[src_map[r']] (retained rows) or 0 (rows new to the GPU); rows of
  * camera k that camera k+1 does not see go to the pinned gradient table
- * (h_grad[id] += or =).  ids_next == NULL (n_next == 0) flushes every row
- * (last camera, engine.py:812-822). */
+ * (accum 0: store; 1: += over the link, the reference's read-modify-write;
+ * 2: += only for rows already flushed once in this batch -- known from the
+ * bitmap -- and a plain store otherwise, which requires the table rows to be
+ * zero at batch start, as cpu-adam leaves them).  n_next == 0 flushes every
+ * row (last camera, engine.py:812-822). */
 int clmgs_rows_prefetch_next(float *d_next_rows, const float *h_rows, const float *d_this_rows,
                              const int64_t *ids_this, int64_t n_this, const int64_t *ids_next,
                              int64_t n_next, const void *bitmap, int word_bytes, int bit_this,
@@ -293,7 +296,7 @@ int clmgs_rows_prefetch_next(float *d_next_rows, const float *h_rows, const floa
 int clmgs_rows_grad_handoff(const float *d_grad_this, float *d_next_grad, float *h_grad,
                             const int64_t *ids_this, int64_t n_this, int64_t n_next,
                             const int32_t *src_map, const void *bitmap, int word_bytes,
-                            int bit_next, int accum, void *stream);
+                            int bit_this, int bit_next, int accum, void *stream);
 
 /* ---------------------------------------------------------------------------
  * A16  GPU Adam.  selective_adam_update (CK/adam.cu:43-78; masked, no bias

@@ -197,9 +197,10 @@ def test_rows_gather_scatter_pinned_host():
     assert flags.tolist() == [0, 0, 1, 0]
 
 
-def test_rows_retention_list_api_and_fused():
+@pytest.mark.parametrize("accum,bsz", [(1, 4), (2, 4), (2, 8)])
+def test_rows_retention_list_api_and_fused(accum, bsz):
     rng = np.random.default_rng(1)
-    N, bsz = 40_000, 4
+    N = 40_000
     h = torch.from_numpy(rng.standard_normal((N, 48)).astype(np.float32)).pin_memory()
     hn = h.numpy()
     vis = rng.random((bsz, N)) < 0.4
@@ -228,7 +229,7 @@ def test_rows_retention_list_api_and_fused():
             src_map = ops.rows_prefetch_next(nxt, h, cur, ids_this, ids_next, bitmap, bsz - 1 - k)
             nxt_grad = torch.empty_like(nxt)
             ops.rows_grad_handoff(cur_grad, nxt_grad, hg, ids_this, len(filters[k + 1]), src_map, bitmap,
-                                  bsz - 1 - (k + 1), accum=True)
+                                  bsz - 1 - k, bsz - 1 - (k + 1), accum=accum)
             # reference bookkeeping
             both = vis[k] & vis[k + 1]
             pos_this = np.cumsum(vis[k]) - 1; pos_next = np.cumsum(vis[k + 1]) - 1
@@ -243,7 +244,7 @@ def test_rows_retention_list_api_and_fused():
             cur, cur_grad, ref_grad = nxt, nxt_grad, new_ref
             np.testing.assert_array_equal(cur_grad.cpu().numpy(), ref_grad)
         else:
-            ops.rows_grad_handoff(cur_grad, None, hg, ids_this, 0, None, bitmap, 0, accum=True)
+            ops.rows_grad_handoff(cur_grad, None, hg, ids_this, 0, None, bitmap, bsz - 1 - k, 0, accum=accum)
             ref_hg[filters[k]] += ref_grad
     torch.cuda.synchronize()
     np.testing.assert_allclose(hg.numpy(), ref_hg, rtol=0, atol=0)
