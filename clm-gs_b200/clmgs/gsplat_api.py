@@ -1,0 +1,168 @@
+"""gsplat-shaped operators over libclmgs.so -- same names, arguments and return tuples as
+``gsplat.cuda._wrapper`` (submodules/gsplat/gsplat/cuda/_wrapper.py) for the five ops CLM uses
+(engine.py:7-13) plus the ``rasterization()`` composite (gsplat/rendering.py:17-402).
+
+Differentiable through torch.autograd.Function exactly where the reference's are
+(_wrapper.py:691-927,1115-1145).  Restrictions, raised as errors (not silently ignored): 3 colour
+channels, tile_size 16, quats/scales (not precomputed covars), no sparse_grad, "classic"
+rasterize mode, render_mode "RGB".
+"""
+import math
+
+import torch
+
+from . import ops
+
+
+class _Projection(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane, radius_clip,
+                calc_compensations):
+        radii, means2d, depths, conics, comp = ops.projection_fwd(means, quats, scales, viewmats, Ks, width, height,
+                                                                  eps2d, near_plane, far_plane, radius_clip,
+                                                                  calc_compensations)
+        ctx.save_for_backward(means, quats, scales, viewmats, Ks, radii, conics)
+        ctx.dims = (width, height, eps2d)
+        ctx.mark_non_differentiable(radii)
+        return radii, means2d, depths, conics, comp
+
+    @staticmethod
+    def backward(ctx, v_radii, v_means2d, v_depths, v_conics, v_comp):
+        means, quats, scales, viewmats, Ks, radii, conics = ctx.saved_tensors
+        width, height, eps2d = ctx.dims
+        if v_comp is not None and v_comp.abs().sum() != 0:
+            raise NotImplementedError("gradient through compensations is not on the CLM path")
+        z = lambda t, ref: torch.zeros_like(ref) if t is None else t.contiguous()
+        v_means, v_quats, v_scales = ops.projection_bwd(means, quats, scales, viewmats, Ks, width, height, eps2d, radii,
+                                                        conics, z(v_means2d, conics[..., :2]), z(v_depths, conics[..., 0]),
+                                                        z(v_conics, conics))
+        return v_means, v_quats, v_scales, None, None, None, None, None, None, None, None, None
+
+
+def fully_fused_projection(means, covars, quats, scales, viewmats, Ks, width, height, eps2d=0.3, near_plane=0.01,
+                           far_plane=1e10, radius_clip=0.0, packed=False, sparse_grad=False,
+                           calc_compensations=False):
+    """_wrapper.py:141-219.  dense -> (radii [C,N] i32, means2d, depths, conics, compensations);
+    packed -> (camera_ids i64, gaussian_ids i64, radii, means2d, depths, conics, compensations), no grad."""
+    if covars is not None:
+        raise NotImplementedError("precomputed covars are not on the CLM path; pass quats and scales")
+    if sparse_grad:
+        raise NotImplementedError("sparse_grad is not on the CLM path")
+    if packed:
+        if means.requires_grad or quats.requires_grad or scales.requires_grad:
+            raise NotImplementedError("packed projection is forward-only here (CLM calls it under no_grad, base_engine.py:22)")
+        out = ops.cull(means, scales, quats, viewmats, Ks, width, height, True, eps2d, near_plane, far_plane,
+                       radius_clip, packed_outputs=True)
+        return (out["camera_ids"], out["gaussian_ids"], out["radii"], out["means2d"], out["depths"], out["conics"],
+                None)
+    return _Projection.apply(means.contiguous(), quats.contiguous(), scales.contiguous(), viewmats.contiguous(),
+                             Ks.contiguous(), int(width), int(height), eps2d, near_plane, far_plane, radius_clip,
+                             calc_compensations)
+
+
+class _SphericalHarmonics(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, degree, dirs, coeffs, masks):
+        colors = ops.sh_fwd(degree, dirs, coeffs, masks)
+        ctx.save_for_backward(dirs, coeffs, masks)
+        ctx.degree = degree
+        return colors
+
+    @staticmethod
+    def backward(ctx, v_colors):
+        dirs, coeffs, masks = ctx.saved_tensors
+        v_coeffs, v_dirs = ops.sh_bwd(ctx.degree, dirs, coeffs, v_colors.contiguous(), None, masks,
+                                      compute_v_dirs=ctx.needs_input_grad[1])
+        return None, v_dirs, v_coeffs, None
+
+
+def spherical_harmonics(degrees_to_use, dirs, coeffs, masks=None):
+    """_wrapper.py:17-47."""
+    assert (degrees_to_use + 1) ** 2 <= coeffs.shape[-2], coeffs.shape
+    assert dirs.shape[:-1] == coeffs.shape[:-2] and dirs.shape[-1] == 3 and coeffs.shape[-1] == 3
+    return _SphericalHarmonics.apply(int(degrees_to_use), dirs.contiguous(), coeffs.contiguous(), masks)
+
+
+@torch.no_grad()
+def isect_tiles(means2d, radii, depths, tile_size, tile_width, tile_height, sort=True, packed=False, n_cameras=None,
+                camera_ids=None, gaussian_ids=None):
+    """_wrapper.py:277-348."""
+    if packed:
+        return ops.isect_tiles(means2d, radii, depths, tile_size, tile_width, tile_height, sort, n_cameras, camera_ids)
+    return ops.isect_tiles(means2d, radii, depths, tile_size, tile_width, tile_height, sort)
+
+
+@torch.no_grad()
+def isect_offset_encode(isect_ids, n_cameras, tile_width, tile_height):
+    """_wrapper.py:351-368."""
+    return ops.isect_offset_encode(isect_ids, n_cameras, tile_width, tile_height)
+
+
+class _RasterizeToPixels(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means2d, conics, colors, opacities, backgrounds, width, height, tile_size, isect_offsets,
+                flatten_ids, absgrad):
+        rc, ra, last = ops.rasterize_fwd(means2d, conics, colors, opacities, width, height, tile_size, isect_offsets,
+                                         flatten_ids, backgrounds)
+        ctx.save_for_backward(means2d, conics, colors, opacities, backgrounds, isect_offsets, flatten_ids, ra, last)
+        ctx.cfg = (width, height, tile_size, absgrad)
+        return rc, ra
+
+    @staticmethod
+    def backward(ctx, v_rc, v_ra):
+        means2d, conics, colors, opacities, backgrounds, offsets, flat, ra, last = ctx.saved_tensors
+        width, height, tile_size, absgrad = ctx.cfg
+        v_means2d, v_conics, v_colors, v_opac, v_abs = ops.rasterize_bwd(
+            means2d, conics, colors, opacities, width, height, tile_size, offsets, flat, ra, last, v_rc.contiguous(),
+            None if v_ra is None else v_ra.contiguous(), backgrounds, absgrad)
+        if absgrad:
+            means2d.absgrad = v_abs
+        v_bg = None
+        if backgrounds is not None and ctx.needs_input_grad[4]:
+            v_bg = (v_rc * (1.0 - ra).float()).sum(dim=(1, 2))
+        return v_means2d, v_conics, v_colors, v_opac, v_bg, None, None, None, None, None, None
+
+
+def rasterize_to_pixels(means2d, conics, colors, opacities, image_width, image_height, tile_size, isect_offsets,
+                        flatten_ids, backgrounds=None, packed=False, absgrad=False):
+    """_wrapper.py:371-497 -> (render_colors [C,H,W,3], render_alphas [C,H,W,1])."""
+    if colors.shape[-1] != 3:
+        raise NotImplementedError("only 3 colour channels are on the CLM path (engine.py:106-117)")
+    if packed:
+        raise NotImplementedError("packed rasterisation inputs: pass dense [C,N,...] tensors")
+    return _RasterizeToPixels.apply(means2d.contiguous(), conics.contiguous(), colors.contiguous(),
+                                    opacities.contiguous(), backgrounds, int(image_width), int(image_height),
+                                    int(tile_size), isect_offsets, flatten_ids, absgrad)
+
+
+def rasterization(means, quats, scales, opacities, colors, viewmats, Ks, width, height, near_plane=0.01,
+                  far_plane=1e10, radius_clip=0.0, eps2d=0.3, sh_degree=None, packed=True, tile_size=16,
+                  backgrounds=None, render_mode="RGB", sparse_grad=False, absgrad=False, rasterize_mode="classic",
+                  channel_chunk=32):
+    """gsplat.rasterization() (gsplat/rendering.py:17-402) for the options CLM-style training uses.
+    `packed=True` is accepted and computed through the dense path (same results, different memory)."""
+    if render_mode != "RGB" or rasterize_mode != "classic" or sparse_grad:
+        raise NotImplementedError("render_mode=RGB, rasterize_mode=classic, sparse_grad=False only")
+    C, N = viewmats.shape[0], means.shape[0]
+    radii, means2d, depths, conics, _ = fully_fused_projection(means, None, quats, scales, viewmats, Ks, width, height,
+                                                               eps2d, near_plane, far_plane, radius_clip, False)
+    tile_width, tile_height = math.ceil(width / float(tile_size)), math.ceil(height / float(tile_size))
+    tiles_per_gauss, isect_ids, flatten_ids = isect_tiles(means2d, radii, depths, tile_size, tile_width, tile_height)
+    isect_offsets = isect_offset_encode(isect_ids, C, tile_width, tile_height)
+    if sh_degree is None:
+        cols = colors if colors.dim() == 3 else colors[None].expand(C, -1, -1)
+    else:
+        camtoworlds = torch.inverse(viewmats)
+        dirs = means[None, :, :] - camtoworlds[:, None, :3, 3]
+        shs = colors if colors.dim() == 4 else colors[None].expand(C, -1, -1, -1)
+        cols = spherical_harmonics(sh_degree, dirs.contiguous(), shs.contiguous(), masks=radii > 0)
+        cols = torch.clamp_min(cols + 0.5, 0.0)
+    opac = opacities[None].expand(C, -1).contiguous()
+    render_colors, render_alphas = rasterize_to_pixels(means2d, conics, cols.contiguous(), opac, width, height,
+                                                       tile_size, isect_offsets, flatten_ids, backgrounds,
+                                                       absgrad=absgrad)
+    meta = dict(camera_ids=None, gaussian_ids=None, radii=radii, means2d=means2d, depths=depths, conics=conics,
+                opacities=opac, tile_width=tile_width, tile_height=tile_height, tiles_per_gauss=tiles_per_gauss,
+                isect_ids=isect_ids, flatten_ids=flatten_ids, isect_offsets=isect_offsets, width=width, height=height,
+                tile_size=tile_size, n_cameras=C)
+    return render_colors, render_alphas, meta
