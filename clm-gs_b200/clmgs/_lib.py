@@ -20,6 +20,7 @@ LIB_PATH = os.path.join(_PKG, "libclmgs.so")
 
 _SCALARS = {"int": C.c_int, "int64_t": C.c_int64, "float": C.c_float, "size_t": C.c_size_t,
             "int32_t": C.c_int32}
+_NO_STATUS = ("clmgs_abi_version", "clmgs_isect_count_static_max")  # int-like returns that are values
 
 
 def parse_header(path=HEADER):
@@ -103,7 +104,7 @@ class _Lib:
             raise ClmgsError("%s expects %d arguments, got %d" % (name, len(spec), len(args)))
         cargs = [self._conv(v, t, p, name, an) for v, (t, an, p) in zip(args, spec)]
         rc = self._resolve(name)(*cargs)
-        if restype is C.c_int and name not in ("clmgs_abi_version",) and rc != 0:
+        if restype is C.c_int and name not in _NO_STATUS and rc != 0:
             raise ClmgsError("%s failed (%d): %s" % (name, rc, self.cdll.clmgs_last_error().decode()))
         return rc
 

@@ -546,3 +546,81 @@ CLMGS_EXPORT int clmgs_isect_offset_encode(int64_t n_isects, const int64_t *isec
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }
+
+// ---------------------------------------------------------------------------
+// Tile counting for callers that must not allocate.
+//
+// clmgs_isect_count needs a few KiB of temporary device memory (one int64 per
+// 1024 inputs) and asks the caller for it.  Some callers have no way to provide
+// that: a C or ctypes host that owns no device allocator, a trainer whose whole
+// HBM budget was carved up at start-up, or a latency-sensitive loop in which a
+// cudaMalloc / cudaFree (both may synchronise the device) is not acceptable.
+// For them this variant keeps the temporary in a fixed array that is part of
+// the loaded library image: nothing is allocated, here or in any routine this
+// function calls.
+//
+// Limits and rules
+//   * at most kStaticMaxTotal (16 Mi) inputs per call; larger calls are
+//     rejected with CLMGS_ERR_INVALID and a message, nothing is launched;
+//   * the array costs 128 KiB of device memory on every GPU that loads the
+//     library, until the process exits;
+//   * the first call on a device looks up the array's device address (once per
+//     device, with that device current).  Make that first call before starting
+//     any stream capture;
+//   * all calls on a device share the one array and it keeps whatever the last
+//     call left in it.  Nothing in it has to start at zero: each call writes
+//     the entries it is going to read before reading them.  Two calls that
+//     overlap on the GPU (different streams, no ordering between them) race on
+//     the array and produce garbage -- order them.
+// ---------------------------------------------------------------------------
+#include <mutex>
+
+constexpr int64_t kStaticMaxTotal = (int64_t)16 * 1024 * 1024;
+constexpr int64_t kStaticBlocks = kStaticMaxTotal / kScanThreads;  // 16384 block sums = 128 KiB
+static __device__ __align__(256) int64_t g_isect_static_block_sums[kStaticBlocks];
+
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mutex;
+static int64_t *g_static_dev_ptr[kStaticMaxDevices] = {nullptr};
+
+// The array's NAME is only a host-side handle: passing it to a kernel would hand the kernel a
+// host address.  The device address comes from cudaGetSymbolAddress, per device.
+static int static_block_sums(int64_t **out) {
+    int dev = -1;
+    CLMGS_CUDA(cudaGetDevice(&dev));
+    CLMGS_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "isect_count_static: device index %d not supported", dev);
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (g_static_dev_ptr[dev] == nullptr) {
+        void *p = nullptr;
+        CLMGS_CUDA(cudaGetSymbolAddress(&p, g_isect_static_block_sums));
+        CLMGS_REQUIRE(p != nullptr, "isect_count_static: no device address for the static scratch array");
+        g_static_dev_ptr[dev] = (int64_t *)p;
+    }
+    *out = g_static_dev_ptr[dev];
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int64_t clmgs_isect_count_static_max(void) { return kStaticMaxTotal; }
+
+CLMGS_EXPORT int clmgs_isect_count_static(int64_t total, const float *means2d, const int32_t *radii, int tile_size,
+                                          int tile_width, int tile_height, int32_t *tiles_per_gauss,
+                                          int64_t *cum_tiles, void *stream) {
+    CLMGS_REQUIRE(total >= 0 && tile_size > 0, "isect_count_static: bad sizes");
+    CLMGS_REQUIRE(total <= kStaticMaxTotal,
+                  "isect_count_static: %lld inputs exceed the built-in scratch (max %lld per call); "
+                  "split the call or use clmgs_isect_count with caller scratch",
+                  (long long)total, (long long)kStaticMaxTotal);
+    if (total == 0) return CLMGS_OK;
+    int64_t *bs = nullptr;
+    if (int rc = static_block_sums(&bs)) return rc;
+    cudaStream_t st = as_stream(stream);
+    const int64_t nblocks = ceil_div64(total, kScanThreads);
+    isect_count_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(total, means2d, radii, tile_size, tile_width,
+                                                                  tile_height, tiles_per_gauss, bs);
+    CLMGS_LAUNCH_OK();
+    scan_block_sums_kernel<<<1, kScanThreads, 0, st>>>(bs, nblocks);
+    CLMGS_LAUNCH_OK();
+    isect_cumsum_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(total, tiles_per_gauss, bs, cum_tiles);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}

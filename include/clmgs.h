@@ -158,6 +158,23 @@ size_t clmgs_isect_count_scratch_bytes(int64_t total);
 int clmgs_isect_count(int64_t total, const float *means2d, const int32_t *radii, int tile_size,
                       int tile_width, int tile_height, int32_t *tiles_per_gauss,
                       int64_t *cum_tiles, void *scratch, size_t scratch_bytes, void *stream);
+/* No counterpart in the reference (its torch extensions always allocate through
+ * torch).  Same result as clmgs_isect_count for hosts that cannot give it
+ * scratch memory: an embedding without a device allocator, a process whose HBM
+ * was fully handed out at start-up, or a loop where cudaMalloc/cudaFree (which
+ * may synchronise the device) is off limits.  The temporary lives in a 128 KiB
+ * array inside the library image (held on every GPU that loads the library
+ * until exit), so nothing is allocated by this call or by anything it calls.
+ * total must be <= clmgs_isect_count_static_max() (16 Mi inputs); more is
+ * rejected with an error and nothing is launched.  The first call on each
+ * device resolves the array's device address -- make it before any stream
+ * capture begins.  The array is shared by all calls on a device and keeps the
+ * last call's contents (each call overwrites what it reads, nothing needs
+ * clearing); calls that overlap on the GPU race on it and must be ordered. */
+int64_t clmgs_isect_count_static_max(void);
+int clmgs_isect_count_static(int64_t total, const float *means2d, const int32_t *radii,
+                             int tile_size, int tile_width, int tile_height,
+                             int32_t *tiles_per_gauss, int64_t *cum_tiles, void *stream);
 size_t clmgs_isect_sort_scratch_bytes(int64_t n_isects);
 int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_ids, const float *means2d,
                           const int32_t *radii, const float *depths, const int64_t *cum_tiles,
