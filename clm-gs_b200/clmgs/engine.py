@@ -39,6 +39,8 @@ class StageTimer:
         self.pairs = []
         self.totals = {}
         self.counts = {}
+        self.base = None
+        self.timeline = []   # (name, start_ms, end_ms) relative to the first recorded event of the batch
 
     class _Ctx:
         def __init__(self, owner, name, stream):
@@ -61,9 +63,12 @@ class StageTimer:
 
     def collect(self):
         """Call after a device synchronize."""
+        self.timeline = []
+        base = self.pairs[0][1] if self.pairs else None
         for name, s, e in self.pairs:
             self.totals[name] = self.totals.get(name, 0.0) + s.elapsed_time(e)
             self.counts[name] = self.counts.get(name, 0) + 1
+            self.timeline.append((name, base.elapsed_time(s), base.elapsed_time(e)))
         self.pairs = []
 
 
@@ -84,6 +89,20 @@ def calculate_filters(batched_cameras, gaussians, timer=_NULL_TIMER):
         "every camera must see at least one Gaussian (strategies/base_engine.py:65-67)"
     filters = list(torch.split(cull["gaussian_ids"], cull["counts"]))
     return filters, cull
+
+
+_PINNED_ROWS = {}
+
+
+def _pinned_rows_buffer(n):
+    """Pinned int32 [n] staging buffer for the host-Adam row lists, allocated once (cudaHostAlloc of
+    tens of MB costs milliseconds and was on the critical path of every batch)."""
+    buf = _PINNED_ROWS.get(n)
+    if buf is None:
+        _PINNED_ROWS.clear()
+        buf = torch.empty(n, dtype=torch.int32).pin_memory()
+        _PINNED_ROWS[n] = buf
+    return buf
 
 
 def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, timer=_NULL_TIMER):
@@ -111,7 +130,7 @@ def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, tim
         ordered_bitmap = ops.bitmap_permute(bitmap, bsz, ordered_cams)
         ffs = ops.extract_ffs(ordered_bitmap)
         rows_dev, counts = ops.group_by_ffs(ffs, bsz)
-        rows_host = torch.empty(n_gaussians, dtype=torch.int32).pin_memory()
+        rows_host = _pinned_rows_buffer(n_gaussians)
         rows_host.copy_(rows_dev, non_blocking=True)
         counts_h = counts.cpu().numpy()  # sync: also completes the rows copy above (same stream)
     offs = np.concatenate([[0], np.cumsum(counts_h)]).astype(np.int64)
@@ -123,9 +142,10 @@ def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, tim
                 visibility=ffs, rows_host=rows_host, row_begin=row_begin, row_end=row_end)
 
 
-def forward_one_camera(gaussians, camera, ids, shs, background, timer=_NULL_TIMER):
-    """pipeline_forward_one_step_shs_inplace (engine.py:30-127) without autograd.  Returns a dict
-    with everything the backward needs."""
+def geometry_one_camera(gaussians, camera, ids, timer=_NULL_TIMER):
+    """The part of the forward that does not touch the offloaded SH rows (engine.py:51-63,85-100):
+    gather + activations, projection, tile intersection + sort.  Runs while SH rows are still in
+    flight on the copy stream."""
     W, H = camera.image_width, camera.image_height
     tw, th = math.ceil(W / float(TILE_SIZE)), math.ceil(H / float(TILE_SIZE))
     with timer("gather_activate"):
@@ -134,18 +154,34 @@ def forward_one_camera(gaussians, camera, ids, shs, background, timer=_NULL_TIME
     with timer("projection_fwd"):
         radii, means2d, depths, conics, _ = ops.projection_fwd(means, quats, scales, camera.viewmat[None],
                                                                camera.K[None], W, H)
-    with timer("sh_fwd"):
-        colors = ops.sh_colors_fwd(gaussians.active_sh_degree, means, camera.campos, shs)
     with timer("isect_sort"):
         _, isect_ids, flatten_ids = ops.isect_tiles(means2d, radii, depths, TILE_SIZE, tw, th)
         offsets = ops.isect_offset_encode(isect_ids, 1, tw, th)
-    bg = None if background is None else background.reshape(1, 3)
-    with timer("raster_fwd"):
-        rc, ra, last = ops.rasterize_fwd(means2d, conics, colors[None], opac[None], W, H, TILE_SIZE, offsets,
-                                         flatten_ids, bg)
+    del isect_ids, depths
     return dict(means=means, scales=scales, quats=quats, opac=opac, radii=radii, means2d=means2d, conics=conics,
-                colors=colors, offsets=offsets, flatten_ids=flatten_ids, render=rc, alphas=ra, last=last, bg=bg,
-                n_isects=flatten_ids.shape[0])
+                offsets=offsets, flatten_ids=flatten_ids, n_isects=flatten_ids.shape[0])
+
+
+def shade_one_camera(gaussians, camera, fw, shs, background, timer=_NULL_TIMER, rows_ready=None):
+    """SH colour + rasterisation (engine.py:67-78,106-119); needs the SH rows."""
+    W, H = camera.image_width, camera.image_height
+    if rows_ready is not None:  # the SH rows arrive on the copy stream
+        torch.cuda.current_stream().wait_event(rows_ready)
+    with timer("sh_fwd"):
+        fw["colors"] = ops.sh_colors_fwd(gaussians.active_sh_degree, fw["means"], camera.campos, shs)
+    fw["bg"] = None if background is None else background.reshape(1, 3)
+    with timer("raster_fwd"):
+        fw["render"], fw["alphas"], fw["last"] = ops.rasterize_fwd(
+            fw["means2d"], fw["conics"], fw["colors"][None], fw["opac"][None], W, H, TILE_SIZE, fw["offsets"],
+            fw["flatten_ids"], fw["bg"])
+    return fw
+
+
+def forward_one_camera(gaussians, camera, ids, shs, background, timer=_NULL_TIMER, rows_ready=None):
+    """pipeline_forward_one_step_shs_inplace (engine.py:30-127) without autograd.  Returns a dict
+    with everything the backward needs."""
+    fw = geometry_one_camera(gaussians, camera, ids, timer)
+    return shade_one_camera(gaussians, camera, fw, shs, background, timer, rows_ready)
 
 
 def backward_one_camera(gaussians, camera, ids, shs, shs_grad, fw, v_render, grads, timer=_NULL_TIMER):
@@ -189,8 +225,12 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     bitmap = oc["ordered_bitmap"]
 
     # ---- stage 2: host Adam thread --------------------------------------------------------------
-    if not hasattr(gaussians, "signal_tensor_pinned") or gaussians.signal_tensor_pinned.shape[0] != bsz:
-        gaussians.signal_tensor_pinned = torch.zeros(bsz, dtype=torch.int32).pin_memory()
+    # flags 0..bsz-2: cameras 0..bsz-2 done; flags bsz-1..: pieces of the last camera's flush
+    n_last = filters[-1].shape[0]
+    J = max(1, min(int(getattr(args, "final_flush_chunks", 1)), max(1, n_last // 65536)))
+    n_flags = bsz - 1 + J
+    if not hasattr(gaussians, "signal_tensor_pinned") or gaussians.signal_tensor_pinned.shape[0] != n_flags:
+        gaussians.signal_tensor_pinned = torch.zeros(n_flags, dtype=torch.int32).pin_memory()
     else:
         gaussians.signal_tensor_pinned.zero_()
     signal = gaussians.signal_tensor_pinned
@@ -198,13 +238,26 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     worker_err = []
 
     worker_times = {}
+    # host-Adam segments (see clmgs.h): group 0 = untouched rows (skipped when sparse_adam), group m = rows
+    # last used by camera m-1; the last group is cut into J pieces that match the J pieces of the final flush
+    # (both lists are the last camera's ascending ids).
+    rb, re_ = oc["row_begin"], oc["row_end"]
+    assert int(re_[bsz] - rb[bsz]) == n_last, "last-use group of the final camera must equal its filter"
+    chunk_edges = [n_last * j // J for j in range(J + 1)]
+    seg_begin, seg_end, seg_signal = [], [], []
+    if not args.sparse_adam:
+        seg_begin.append(int(rb[0])); seg_end.append(int(re_[0])); seg_signal.append(-1)
+    for m in range(1, bsz):
+        seg_begin.append(int(rb[m])); seg_end.append(int(re_[m])); seg_signal.append(m - 1)
+    for j in range(J):
+        seg_begin.append(int(rb[bsz]) + chunk_edges[j]); seg_end.append(int(rb[bsz]) + chunk_edges[j + 1])
+        seg_signal.append(bsz - 1 + j)
 
     def cpuadam_thread():
         import time as _t
         t0 = _t.perf_counter()
         try:
-            cpu_adam.batched_sparse_step(h_grad, bsz, oc["rows_host"], oc["row_begin"], oc["row_end"], signal,
-                                         1.0 / bsz, args.sparse_adam)
+            cpu_adam.batched_sparse_step(h_grad, oc["rows_host"], seg_begin, seg_end, seg_signal, signal, 1.0 / bsz)
         except Exception as e:  # surfaced after join
             worker_err.append(e)
         worker_times["cpu_adam_thread_ms"] = (_t.perf_counter() - t0) * 1e3
@@ -213,19 +266,19 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     worker.start()
     try:
         out = _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_grad, background, comm_stream,
-                             signal, timer, worker, worker_err)
+                             signal, timer, worker, worker_err, chunk_edges)
         gaussians.last_batch_stats.update(worker_times)
         return out
     except BaseException:
         # never leave the host-Adam thread spinning on flags that will not come
         torch.cuda.synchronize()
-        signal.fill_(1)
+        gaussians.signal_tensor_pinned.fill_(1)
         worker.join()
         raise
 
 
 def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_grad, background, comm_stream, signal,
-                   timer, worker, worker_err):
+                   timer, worker, worker_err, chunk_edges):
     args = gaussians.args
     bsz = len(batched_cameras)
     N = gaussians.n_gaussians
@@ -242,46 +295,68 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
     start_evt.record(compute)
     comm_stream.wait_event(start_evt)  # filters / bitmap are ready for the copy stream
     losses, keep = [], [cull, oc]
-    shs = shs_grad = shs_next = shs_grad_next = src_map = None
-    rows_ready = grad_ready = None
+    lookahead = max(0, int(getattr(args, "geometry_lookahead", 3)))
+    geoms = [None] * bsz
 
     with torch.no_grad():
+        # SH-row pipeline on the copy stream: rows[j] = buffer of camera j, src_maps[j] = where each row of
+        # camera j+1 sits in rows[j] (-1: came from host).  Parameter rows never change inside a batch, so
+        # prefetches run `rows_lookahead` cameras ahead of the compute stream and never wait for it.
+        rows = [None] * bsz
+        rows_evt = [None] * bsz
+        src_maps = [None] * bsz
+        rows_lookahead = max(1, int(getattr(args, "rows_lookahead", 1)))
+        issued = 0  # prefetches issued so far: rows[0..issued] exist
+
+        def issue_rows(upto):
+            nonlocal issued
+            with torch.cuda.stream(comm_stream):
+                if rows_evt[0] is None:
+                    rows[0] = ops._empty((filters[0].shape[0], 48), torch.float32, dev)
+                    with timer("rows_load_first", comm_stream):
+                        ops.rows_gather(rows[0], h_params, filters[0])
+                    rows_evt[0] = torch.cuda.Event()
+                    rows_evt[0].record(comm_stream)
+                    rows[0].record_stream(compute)
+                while issued < min(upto, bsz - 1):
+                    j = issued
+                    rows[j + 1] = ops._empty((filters[j + 1].shape[0], 48), torch.float32, dev)
+                    with timer("rows_prefetch", comm_stream):
+                        src_maps[j] = ops.rows_prefetch_next(rows[j + 1], h_params, rows[j], filters[j],
+                                                             filters[j + 1], bitmap, bsz - 1 - j)
+                    rows_evt[j + 1] = torch.cuda.Event()
+                    rows_evt[j + 1].record(comm_stream)
+                    rows[j + 1].record_stream(compute)
+                    issued += 1
+
+        with torch.cuda.stream(comm_stream):
+            shs_grad = ops._zeros((filters[0].shape[0], 48), torch.float32, dev)
+            grad_ready = torch.cuda.Event()
+            grad_ready.record(comm_stream)
+            shs_grad.record_stream(compute)
+
         for k in range(bsz):
             ids = filters[k]
-            n_k = ids.shape[0]
-            # -- 4.1 / 4.2: SH rows of this camera, prefetch of the next (copy stream) -------------
-            with torch.cuda.stream(comm_stream):
-                if k == 0:
-                    shs = torch.empty(n_k, 48, device=dev)
-                    shs_grad = torch.zeros(n_k, 48, device=dev)
-                    with timer("rows_load_first", comm_stream):
-                        ops.rows_gather(shs, h_params, ids)
-                    rows_ready = torch.cuda.Event()
-                    rows_ready.record(comm_stream)
-                    grad_ready = rows_ready
-                cur_rows_ready, cur_grad_ready = rows_ready, grad_ready
-                if k < bsz - 1:
-                    ids_next = filters[k + 1]
-                    shs_next = torch.empty(ids_next.shape[0], 48, device=dev)
-                    with timer("rows_prefetch", comm_stream):
-                        src_map = ops.rows_prefetch_next(shs_next, h_params, shs, ids, ids_next, bitmap,
-                                                         bsz - 1 - k)
-                    rows_ready = torch.cuda.Event()
-                    rows_ready.record(comm_stream)
-            for t in (shs, shs_grad):
-                t.record_stream(compute)
+            # -- 4.1 / 4.2: SH rows of this camera and of the next ones (copy stream) -----------------
+            issue_rows(k + rows_lookahead)
+            shs = rows[k]
 
             # -- 4.3: forward ---------------------------------------------------------------------
-            compute.wait_event(cur_rows_ready)
             cam = cams[k]
-            fw = forward_one_camera(gaussians, cam, ids, shs, background, timer)
+            # geometry of this and the next few cameras does not need SH rows: issue it before waiting on the
+            # copy stream so that it hides the host-link latency of the first load / the prefetches
+            for kk in range(k, min(bsz, k + 1 + lookahead)):
+                if geoms[kk] is None:
+                    geoms[kk] = geometry_one_camera(gaussians, cams[kk], filters[kk], timer)
+            fw, geoms[k] = geoms[k], None
+            fw = shade_one_camera(gaussians, cam, fw, shs, background, timer, rows_ready=rows_evt[k])
             with timer("loss"):
                 loss_vec, v_render = ops.loss_fwd_bwd(fw["render"][0], cam.original_image, args.lambda_dssim,
                                                       hwc=True)
             losses.append(loss_vec[0])
 
             # -- 4.4 / 4.5: backward ----------------------------------------------------------------
-            compute.wait_event(cur_grad_ready)
+            compute.wait_event(grad_ready)
             backward_one_camera(gaussians, cam, ids, shs, shs_grad, fw, v_render[None], grads, timer)
             bwd_done = torch.cuda.Event()
             bwd_done.record(compute)
@@ -290,19 +365,29 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
             with torch.cuda.stream(comm_stream):
                 comm_stream.wait_event(bwd_done)
                 if k < bsz - 1:
-                    shs_grad_next = torch.empty_like(shs_next)
+                    n_next = filters[k + 1].shape[0]
+                    shs_grad_next = ops._empty((n_next, 48), torch.float32, dev)
+                    shs_grad_next.record_stream(compute)
                     with timer("grad_handoff", comm_stream):
-                        ops.rows_grad_handoff(shs_grad, shs_grad_next, h_grad, ids, shs_next.shape[0], src_map,
-                                              bitmap, bsz - 1 - k, bsz - 1 - (k + 1), accum=2)
+                        ops.rows_grad_handoff(shs_grad, shs_grad_next, h_grad, ids, n_next, src_maps[k], bitmap,
+                                              bsz - 1 - k, bsz - 1 - (k + 1), accum=2)
                     grad_ready = torch.cuda.Event()
                     grad_ready.record(comm_stream)
+                    ops.set_signal(signal, k, 1)
                 else:
+                    # last camera: everything goes to the host table, in pieces, each announced on its own
+                    # flag so the host Adam starts on piece j while piece j+1 is still crossing the link
                     with timer("grad_handoff", comm_stream):
-                        ops.rows_grad_handoff(shs_grad, None, h_grad, ids, 0, None, bitmap, bsz - 1 - k, 0, accum=2)
-                ops.set_signal(signal, k, 1)
-            keep.append((shs, shs_grad, fw, v_render, src_map))
+                        for j in range(len(chunk_edges) - 1):
+                            a, b = chunk_edges[j], chunk_edges[j + 1]
+                            ops.rows_grad_handoff(shs_grad[a:b], None, h_grad, ids[a:b], 0, None, bitmap, bsz - 1 - k, 0,
+                                                  accum=2)
+                            ops.set_signal(signal, bsz - 1 + j, 1)
+            keep.append((shs, shs_grad, fw, v_render, src_maps[k]))
             if k < bsz - 1:
-                shs, shs_grad = shs_next, shs_grad_next
+                shs_grad = shs_grad_next
+            if k >= 1:
+                rows[k - 1] = None  # rows[k-1] was last read by the prefetch k-1 -> k (kept alive in `keep` until the sync)
 
         # ---- stage 5: GPU Adam (grads / bsz fused as grad_scale) ------------------------------------
         with timer("gpu_adam"):

@@ -44,6 +44,9 @@ class TrainArgs:
     lambda_dssim: float = 0.2
     spatial_lr_scale: float = 1.0
     cpu_adam_threads: int = 0  # 0 = all hardware threads
+    final_flush_chunks: int = 8  # last camera: flush + host Adam pipelined in this many pieces
+    rows_lookahead: int = 1  # SH-row prefetches issued this many cameras ahead on the copy stream
+    geometry_lookahead: int = 3  # cameras whose projection/tile sort is issued ahead of their SH rows
 
 
 class _Group(dict):
@@ -92,13 +95,12 @@ class CpuAdam:
         self.step_count = 0
         self.n_threads = n_threads
 
-    def batched_sparse_step(self, grad, batch_size, rows, row_begin, row_end, signal_tensor_pinned, scale,
-                            sparse_adam):
+    def batched_sparse_step(self, grad, rows, seg_begin, seg_end, seg_signal, signal_tensor_pinned, scale):
         """engine.py:320-327.  Blocking; run it on a worker thread (ctypes drops the GIL)."""
         self.step_count += 1
         ops.cpu_adam_batched_sparse_step(self.param, grad, self.exp_avg, self.exp_avg_sq, self.columns_lr, rows,
-                                         row_begin, row_end, batch_size, signal_tensor_pinned, self.betas[0],
-                                         self.betas[1], self.eps, self.step_count, scale, sparse_adam, self.n_threads)
+                                         seg_begin, seg_end, seg_signal, signal_tensor_pinned, self.betas[0],
+                                         self.betas[1], self.eps, self.step_count, scale, self.n_threads)
 
 
 class UnifiedAdam:

@@ -16,8 +16,33 @@ def _st():
     return torch.cuda.current_stream().cuda_stream
 
 
+def _bucket(n):
+    """Round a row count up to 1/8-octave steps.  Per-camera sizes (visible Gaussians, tile
+    intersections) differ a little from camera to camera; asking torch's caching allocator for the
+    exact size makes it cudaMalloc fresh segments in steady state, and cudaMalloc waits for running
+    kernels (measured: a 3 ms sort stalled 20 ms behind the SH-row transfer).  Bucketed sizes hit the
+    cache."""
+    n = int(n)
+    if n <= 4096:
+        return max(n, 1)
+    step = 1 << (n.bit_length() - 4)
+    return (n + step - 1) // step * step
+
+
+def _empty(shape, dtype, device):
+    shape = (shape,) if isinstance(shape, int) else tuple(shape)
+    n = shape[0]
+    return torch.empty((_bucket(n),) + shape[1:], dtype=dtype, device=device)[:n]
+
+
+def _zeros(shape, dtype, device):
+    t = _empty(shape, dtype, device)
+    t.zero_()
+    return t
+
+
 def _scratch(nbytes, device):
-    return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=device)
+    return torch.empty(_bucket(max(int(nbytes), 16)), dtype=torch.uint8, device=device)
 
 
 _WORD_DTYPE = {1: torch.uint8, 2: torch.int16, 4: torch.int32, 8: torch.int64}
@@ -69,10 +94,11 @@ def cull(means, scales, quats, viewmats, Ks, width, height, activated=True, eps2
 # --------------------------------------------------------------------------- A4
 def gather_activate(xyz, log_scale, raw_quat, opacity_logit, ids):
     n, dev = ids.shape[0], xyz.device
-    means = torch.empty(n, 3, device=dev)
-    scales = torch.empty(n, 3, device=dev)
-    quats = torch.empty(n, 4, device=dev)
-    opac = torch.empty(n, device=dev)
+    f32 = torch.float32
+    means = _empty((n, 3), f32, dev)
+    scales = _empty((n, 3), f32, dev)
+    quats = _empty((n, 4), f32, dev)
+    opac = _empty((n,), f32, dev)
     call("clmgs_gather_activate", _f32c(xyz), _f32c(log_scale), _f32c(raw_quat), _f32c(opacity_logit),
          ids.contiguous(), n, means, scales, quats, opac, _st())
     return means, scales, quats, opac
@@ -92,11 +118,12 @@ def projection_fwd(means, quats, scales, viewmats, Ks, width, height, eps2d=0.3,
     viewmats, Ks = _f32c(viewmats), _f32c(Ks)
     dev = means.device
     N, C = means.shape[0], viewmats.shape[0]
-    radii = torch.empty(C, N, dtype=torch.int32, device=dev)
-    means2d = torch.empty(C, N, 2, device=dev)
-    depths = torch.empty(C, N, device=dev)
-    conics = torch.empty(C, N, 3, device=dev)
-    comp = torch.empty(C, N, device=dev) if calc_compensations else None
+    CN = C * N
+    radii = _empty((CN,), torch.int32, dev).view(C, N)
+    means2d = _empty((CN, 2), torch.float32, dev).view(C, N, 2)
+    depths = _empty((CN,), torch.float32, dev).view(C, N)
+    conics = _empty((CN, 3), torch.float32, dev).view(C, N, 3)
+    comp = _empty((CN,), torch.float32, dev).view(C, N) if calc_compensations else None
     call("clmgs_projection_fwd", C, N, means, quats, scales, viewmats, Ks, int(width), int(height),
          float(eps2d), float(near_plane), float(far_plane), float(radius_clip), radii, means2d, depths,
          conics, comp, _st())
@@ -107,9 +134,9 @@ def projection_bwd(means, quats, scales, viewmats, Ks, width, height, eps2d, rad
                    v_means2d, v_depths, v_conics):
     dev = means.device
     N, C = means.shape[0], viewmats.shape[0]
-    v_means = torch.zeros(N, 3, device=dev)
-    v_quats = torch.zeros(N, 4, device=dev)
-    v_scales = torch.zeros(N, 3, device=dev)
+    v_means = _zeros((N, 3), torch.float32, dev)
+    v_quats = _zeros((N, 4), torch.float32, dev)
+    v_scales = _zeros((N, 3), torch.float32, dev)
     call("clmgs_projection_bwd", C, N, _f32c(means), _f32c(quats), _f32c(scales), _f32c(viewmats),
          _f32c(Ks), int(width), int(height), float(eps2d), radii.contiguous(), _f32c(conics),
          _f32c(v_means2d), None if v_depths is None else _f32c(v_depths), _f32c(v_conics), v_means, v_quats,
@@ -158,14 +185,14 @@ def isect_tiles(means2d, radii, depths, tile_size, tile_width, tile_height, sort
     else:
         C, N = radii.shape
         total = C * N
-    tpg = torch.empty(radii.shape, dtype=torch.int32, device=dev)
-    cum = torch.empty(max(total, 1), dtype=torch.int64, device=dev)
+    tpg = _empty((max(total, 1),), torch.int32, dev)[:total].view(radii.shape)
+    cum = _empty((max(total, 1),), torch.int64, dev)
     sc = _scratch(call("clmgs_isect_count_scratch_bytes", total), dev)
     call("clmgs_isect_count", total, means2d, radii, int(tile_size), int(tile_width), int(tile_height),
          tpg, cum, sc, sc.numel(), _st())
     n_isects = int(cum[total - 1].item()) if total > 0 else 0
-    ids = torch.empty(n_isects, dtype=torch.int64, device=dev)
-    flat = torch.empty(n_isects, dtype=torch.int32, device=dev)
+    ids = _empty((n_isects,), torch.int64, dev)
+    flat = _empty((n_isects,), torch.int32, dev)
     sc2 = _scratch(call("clmgs_isect_sort_scratch_bytes", n_isects) if sort else 0, dev)
     call("clmgs_isect_emit_sort", C, N, camera_ids, means2d, radii, depths, cum, int(tile_size),
          int(tile_width), int(tile_height), n_isects, int(bool(sort)), ids, flat, sc2, sc2.numel(), _st())
@@ -203,11 +230,12 @@ def rasterize_bwd(means2d, conics, colors, opacities, width, height, tile_size, 
     dev = means2d.device
     C, th, tw = isect_offsets.shape
     N = opacities.shape[-1]
-    v_means2d = torch.zeros_like(means2d)
-    v_conics = torch.zeros_like(conics)
-    v_colors = torch.zeros_like(colors)
-    v_opac = torch.zeros_like(opacities)
-    v_abs = torch.zeros_like(means2d) if absgrad else None
+    CN = C * N
+    v_means2d = _zeros((CN, 2), torch.float32, dev).view(means2d.shape)
+    v_conics = _zeros((CN, 3), torch.float32, dev).view(conics.shape)
+    v_colors = _zeros((CN, 3), torch.float32, dev).view(colors.shape)
+    v_opac = _zeros((CN,), torch.float32, dev).view(opacities.shape)
+    v_abs = _zeros((CN, 2), torch.float32, dev).view(means2d.shape) if absgrad else None
     bg = None if backgrounds is None else _f32c(backgrounds)
     vra = None if v_render_alphas is None else _f32c(v_render_alphas)
     call("clmgs_rasterize_bwd", C, N, flatten_ids.shape[0], means2d, conics, colors, opacities, bg,
@@ -270,7 +298,7 @@ def set_signal(h_flags, index, value):
 
 def rows_prefetch_next(d_next, h_rows, d_this, ids_this, ids_next, bitmap, bit_this):
     n_next = ids_next.shape[0]
-    src_map = torch.empty(max(n_next, 1), dtype=torch.int32, device=d_next.device)
+    src_map = _empty((max(n_next, 1),), torch.int32, d_next.device)
     call("clmgs_rows_prefetch_next", d_next, h_rows, d_this, ids_this, 0 if ids_this is None else ids_this.shape[0],
          ids_next, n_next, bitmap, bitmap.element_size(), int(bit_this), src_map, _st())
     return src_map
@@ -337,20 +365,24 @@ def adam_dense(param, grad, exp_avg, exp_avg_sq, lr, b1, b2, eps, step, grad_sca
          float(grad_scale), int(step), param.numel(), _st())
 
 
-def cpu_adam_batched_sparse_step(param, grad, exp_avg, exp_avg_sq, col_lr, rows, row_begin, row_end, bsz, signal,
-                                 b1, b2, eps, step, scale, sparse_adam, n_threads=0):
+def cpu_adam_batched_sparse_step(param, grad, exp_avg, exp_avg_sq, col_lr, rows, seg_begin, seg_end, seg_signal,
+                                 signal, b1, b2, eps, step, scale, n_threads=0):
     """All arguments are HOST tensors/arrays (pinned where the GPU also touches them).  Blocking.
-    Group m (m = 0..bsz) = rows[row_begin[m]:row_end[m]]."""
+    Segment s = rows[seg_begin[s]:seg_end[s]], processed after signal[seg_signal[s]] != 0 (no wait if < 0)."""
+    import numpy as np
+    seg_begin = np.ascontiguousarray(seg_begin, np.int64)
+    seg_end = np.ascontiguousarray(seg_end, np.int64)
+    seg_signal = np.ascontiguousarray(seg_signal, np.int32)
     call("clmgs_cpu_adam_batched_sparse_step", param, grad, exp_avg, exp_avg_sq, int(param.shape[1]), col_lr, rows,
-         row_begin, row_end, int(bsz), signal, float(b1), float(b2), float(eps), int(step), float(scale),
-         int(sparse_adam), int(n_threads))
+         seg_begin, seg_end, seg_signal, len(seg_begin), signal, float(b1), float(b2), float(eps), int(step),
+         float(scale), int(n_threads))
 
 
 def sh_colors_fwd(degree, means, campos, coeffs):
     """Engine-fused: colours = clamp_min(SH(means - campos) + 0.5, 0).  coeffs [n,48] or [n,K,3]."""
     n = means.shape[0]
     K = coeffs.numel() // (3 * n) if n else 16
-    colors = torch.empty(n, 3, device=means.device)
+    colors = _empty((n, 3), torch.float32, means.device)
     call("clmgs_sh_colors_fwd", n, K, int(degree), means, campos, coeffs, colors, _st())
     return colors
 

@@ -65,11 +65,12 @@ inline void wait_flag(const volatile int32_t *flag) {
 
 CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, float *host_exp_avg,
                                                     float *host_exp_avg_sq, int cols, const float *col_lr,
-                                                    const int32_t *host_rows, const int64_t *row_begin, const int64_t *row_end, int bsz,
+                                                    const int32_t *host_rows, const int64_t *seg_begin,
+                                                    const int64_t *seg_end, const int32_t *seg_signal, int n_segments,
                                                     const volatile int32_t *h_signal, float b1, float b2, float eps,
-                                                    int64_t step, float scale, int sparse_adam, int n_threads) {
-    if (cols <= 0 || bsz < 0 || step < 1) {
-        clmgs_set_error("cpu_adam: bad arguments (cols=%d bsz=%d step=%lld)", cols, bsz, (long long)step);
+                                                    int64_t step, float scale, int n_threads) {
+    if (cols <= 0 || n_segments < 0 || step < 1) {
+        clmgs_set_error("cpu_adam: bad arguments (cols=%d n_segments=%d step=%lld)", cols, n_segments, (long long)step);
         return CLMGS_ERR_INVALID;
     }
     if (n_threads <= 0) n_threads = (int)std::max(1u, std::thread::hardware_concurrency());
@@ -79,10 +80,9 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
     c.inv_bc1 = (float)(1.0 / (1.0 - pow((double)b1, (double)step)));
     c.bc2_rsqrt = (float)(1.0 / sqrt(1.0 - pow((double)b2, (double)step)));
     auto worker = [&](int tid) {
-        for (int m = 0; m <= bsz; ++m) {
-            if (m == 0 && sparse_adam) continue;        // untouched rows: no update at all
-            if (m >= 1 && h_signal) wait_flag(h_signal + (m - 1));  // gradients of camera m-1 have landed
-            const int64_t lo = row_begin[m], hi = row_end[m], n = hi - lo;
+        for (int m = 0; m < n_segments; ++m) {
+            if (seg_signal[m] >= 0 && h_signal) wait_flag(h_signal + seg_signal[m]);  // these gradients have landed
+            const int64_t lo = seg_begin[m], hi = seg_end[m], n = hi - lo;
             const int64_t a = lo + n * tid / n_threads, b = lo + n * (tid + 1) / n_threads;
             for (int64_t r = a; r < b; ++r) {
                 const int64_t base = (int64_t)host_rows[r] * cols;

@@ -155,6 +155,12 @@ __device__ __forceinline__ float butterfly8(float v[8], int lane) {
     return v[0];
 }
 
+// bin_final is 0 both for "entry 0 was blended" and for "nothing blended"; either way entries
+// above it are dead, so the value itself is the bound (clamped below the range it means "none").
+__device__ __forceinline__ int inside_any(int warp_bin_final, int start) {
+    return warp_bin_final >= start ? warp_bin_final : start - 1;
+}
+
 template <bool HAS_BG, bool ABSGRAD>
 __global__ void __launch_bounds__(kBlock)
 raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float *__restrict__ conics,
@@ -199,8 +205,19 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
     int warp_bin_final = bin_final;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
+    // Entries behind the last one any pixel of this tile blended contribute nothing: with early
+    // termination that is most of a long tile list, so do not even stage those batches (the
+    // reference loads every batch).  tile_last = max over the CTA of bin_final.
+    __shared__ int s_tile_last;
+    if (tr == 0) s_tile_last = -1;
+    __syncthreads();
+    if (lane == 0) atomicMax(&s_tile_last, inside_any(warp_bin_final, start));
+    __syncthreads();
+    const int tile_last = s_tile_last;
+    if (tile_last < start) return;  // nothing was blended anywhere in this tile
+    const int first_batch = (end - 1 - tile_last) / kBlock;
 
-    for (int bt = 0; bt < num_batches; ++bt) {
+    for (int bt = first_batch; bt < num_batches; ++bt) {
         __syncthreads();
         const int batch_end = end - 1 - kBlock * bt;  // absolute index of the back-most entry of this batch
         const int batch_size = min(kBlock, batch_end + 1 - start);

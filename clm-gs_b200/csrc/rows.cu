@@ -84,6 +84,16 @@ accum_rows_kernel(float4 *__restrict__ dst, const float4 *__restrict__ src, int6
     }
 }
 
+// A transfer kernel sits on every SM for tens of milliseconds.  An SM cannot change its L1/shared
+// split while a CTA is resident, so if these kernels ran with the default (L1-heavy) split, any
+// render kernel that needs a large shared-memory carve-out -- the radix sort's onesweep passes --
+// could not be placed until the transfer finished (measured: a 3.5 ms sort took 22 ms).  They use no
+// L1 (streaming loads), so ask for the maximum shared carve-out and let everything co-reside.
+template <typename K>
+inline void prefer_shared(K kernel) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
+
 struct Identity { __device__ int64_t operator()(int64_t r) const { return r; } };
 struct Map64 { const int64_t *p; __device__ int64_t operator()(int64_t r) const { return p[r]; } };
 struct Map32 { const int32_t *p; __device__ int64_t operator()(int64_t r) const { return p[r]; } };
@@ -111,45 +121,13 @@ __device__ __forceinline__ int32_t rank_of(const int64_t *__restrict__ ids, int6
     return (int32_t)lo;
 }
 
-// One 16-lane group handles 4 destination rows per iteration: lanes 0..3 classify one row each
-// (bitmap test + binary search), then lanes 0..11 move the four 192-B rows with 4 loads in flight.
-__global__ void __launch_bounds__(kThreads)
-prefetch_next_kernel(float4 *__restrict__ d_next, const float4 *__restrict__ h_rows,
-                     const float4 *__restrict__ d_this, const int64_t *__restrict__ ids_this, int64_t n_this,
-                     const int64_t *__restrict__ ids_next, int64_t n_next, const void *__restrict__ bitmap, int wb,
-                     int bit_this, int32_t *__restrict__ src_map) {
-    const int sub = threadIdx.x & 15;
-    const int64_t groups = ((int64_t)gridDim.x * kThreads) >> 4;
-    const unsigned gmask = 0xffffu << (threadIdx.x & 16);
-    for (int64_t r0 = (((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4) * 4; r0 < n_next; r0 += groups * 4) {
-        int64_t my_id = 0;
-        int32_t my_src = -1;
-        if (sub < 4 && r0 + sub < n_next) {
-            my_id = ids_next[r0 + sub];
-            if (n_this > 0 && test_bit_any(bitmap, wb, my_id, bit_this)) my_src = rank_of(ids_this, n_this, my_id);
-            src_map[r0 + sub] = my_src;
-        }
-        float4 v[4];
-        bool live[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int64_t id = __shfl_sync(gmask, my_id, u, 16);
-            const int32_t src = __shfl_sync(gmask, my_src, u, 16);
-            live[u] = sub < kRowF4 && r0 + u < n_next;
-            if (live[u]) v[u] = ld_stream(src >= 0 ? d_this + (int64_t)src * kRowF4 + sub : h_rows + id * kRowF4 + sub);
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-            if (live[u]) d_next[(r0 + u) * kRowF4 + sub] = v[u];
-    }
-}
-
-// Part A: next_grad rows (retained or zero).  Part B: flush rows camera k+1 does not see.
-// accum: 0 = store, 1 = read-modify-write over the link (the reference, CK/clm_kernels.cu:201),
-//        2 = RMW only for rows that were already flushed once in this batch.  A row was flushed
-//            before iff, among the cameras before the current run of consecutive visibility, some
-//            camera saw it: with hi = word >> (bit_this+1) that is (hi & (hi+1)) != 0.  Everything
-//            else is the first write to a zeroed row (cpu-adam leaves consumed rows zeroed) -> store.
+// ---------------------------------------------------------------------------
+// Retention transfers, two launches each:
+//   *_dev_kernel  : rows that stay on the GPU (device -> device), full-occupancy grid, HBM-bound;
+//   *_host_kernel : rows that cross the host link, 1 CTA/SM (see grid_for), PCIe-latency-bound.
+// A 16-lane group handles 4 rows per iteration: lanes 0..3 classify one row each (bitmap test +
+// binary search), lanes 0..11 then move the four 192-B rows with 4 independent 16-B loads in flight.
+// ---------------------------------------------------------------------------
 __device__ __forceinline__ uint64_t load_word(const void *bitmap, int wb, int64_t i) {
     switch (wb) {
         case 1: return ((const uint8_t *)bitmap)[i];
@@ -159,16 +137,66 @@ __device__ __forceinline__ uint64_t load_word(const void *bitmap, int wb, int64_
     }
 }
 
+// next rows that the current camera also sees: copy from the current buffer; records src_map for all rows
 __global__ void __launch_bounds__(kThreads)
-grad_handoff_kernel(const float4 *__restrict__ d_grad, float4 *__restrict__ d_next_grad, float4 *__restrict__ h_grad,
-                    const int64_t *__restrict__ ids_this, int64_t n_this, int64_t n_next,
-                    const int32_t *__restrict__ src_map, const void *__restrict__ bitmap, int wb, int bit_this,
-                    int bit_next, int accum) {
+prefetch_dev_kernel(float4 *__restrict__ d_next, const float4 *__restrict__ d_this,
+                    const int64_t *__restrict__ ids_this, int64_t n_this, const int64_t *__restrict__ ids_next,
+                    int64_t n_next, const void *__restrict__ bitmap, int wb, int bit_this,
+                    int32_t *__restrict__ src_map) {
     const int sub = threadIdx.x & 15;
     const int64_t groups = ((int64_t)gridDim.x * kThreads) >> 4;
-    const int64_t g0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4;
     const unsigned gmask = 0xffffu << (threadIdx.x & 16);
-    for (int64_t r0 = g0 * 4; r0 < n_next; r0 += groups * 4) {
+    for (int64_t r0 = (((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4) * 4; r0 < n_next; r0 += groups * 4) {
+        int32_t my_src = -1;
+        if (sub < 4 && r0 + sub < n_next) {
+            const int64_t id = ids_next[r0 + sub];
+            if (n_this > 0 && ((load_word(bitmap, wb, id) >> bit_this) & 1)) my_src = rank_of(ids_this, n_this, id);
+            src_map[r0 + sub] = my_src;
+        }
+        float4 v[4];
+        int32_t src[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            src[u] = __shfl_sync(gmask, my_src, u, 16);
+            if (sub < kRowF4 && src[u] >= 0) v[u] = ld_stream(d_this + (int64_t)src[u] * kRowF4 + sub);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (sub < kRowF4 && src[u] >= 0) d_next[(r0 + u) * kRowF4 + sub] = v[u];
+    }
+}
+
+// next rows that are not on the GPU (src_map < 0): zero-copy loads from the pinned table
+__global__ void __launch_bounds__(kThreads)
+prefetch_host_kernel(float4 *__restrict__ d_next, const float4 *__restrict__ h_rows,
+                     const int64_t *__restrict__ ids_next, int64_t n_next, const int32_t *__restrict__ src_map) {
+    const int sub = threadIdx.x & 15;
+    const int64_t groups = ((int64_t)gridDim.x * kThreads) >> 4;
+    const unsigned gmask = 0xffffu << (threadIdx.x & 16);
+    for (int64_t r0 = (((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4) * 4; r0 < n_next; r0 += groups * 4) {
+        int64_t my_id = -1;
+        if (sub < 4 && r0 + sub < n_next && src_map[r0 + sub] < 0) my_id = ids_next[r0 + sub];
+        float4 v[4];
+        int64_t id[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            id[u] = __shfl_sync(gmask, my_id, u, 16);
+            if (sub < kRowF4 && id[u] >= 0) v[u] = ld_stream(h_rows + id[u] * kRowF4 + sub);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (sub < kRowF4 && id[u] >= 0) d_next[(r0 + u) * kRowF4 + sub] = v[u];
+    }
+}
+
+// next_grad[r'] = grad_this[src_map[r']] for retained rows, 0 for rows new to the GPU
+__global__ void __launch_bounds__(kThreads)
+handoff_dev_kernel(const float4 *__restrict__ d_grad, float4 *__restrict__ d_next_grad, int64_t n_next,
+                   const int32_t *__restrict__ src_map) {
+    const int sub = threadIdx.x & 15;
+    const int64_t groups = ((int64_t)gridDim.x * kThreads) >> 4;
+    const unsigned gmask = 0xffffu << (threadIdx.x & 16);
+    for (int64_t r0 = (((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4) * 4; r0 < n_next; r0 += groups * 4) {
         int32_t my_src = (sub < 4 && r0 + sub < n_next) ? src_map[r0 + sub] : -1;
         float4 v[4];
 #pragma unroll
@@ -181,13 +209,28 @@ grad_handoff_kernel(const float4 *__restrict__ d_grad, float4 *__restrict__ d_ne
         for (int u = 0; u < 4; ++u)
             if (sub < kRowF4 && r0 + u < n_next) d_next_grad[(r0 + u) * kRowF4 + sub] = v[u];
     }
-    for (int64_t r0 = g0 * 4; r0 < n_this; r0 += groups * 4) {
+}
+
+// Rows of this camera that the next one does not see go to the pinned gradient table.
+// accum: 0 = store, 1 = read-modify-write over the link (the reference, CK/clm_kernels.cu:201),
+//        2 = RMW only for rows that were already flushed once in this batch.  A row was flushed
+//            before iff, among the cameras before the current run of consecutive visibility, some
+//            camera saw it: with hi = word >> (bit_this+1) that is (hi & (hi+1)) != 0.  Everything
+//            else is the first write to a zeroed row (cpu-adam leaves consumed rows zeroed) -> store.
+__global__ void __launch_bounds__(kThreads)
+handoff_host_kernel(const float4 *__restrict__ d_grad, float4 *__restrict__ h_grad,
+                    const int64_t *__restrict__ ids_this, int64_t n_this, int has_next,
+                    const void *__restrict__ bitmap, int wb, int bit_this, int bit_next, int accum) {
+    const int sub = threadIdx.x & 15;
+    const int64_t groups = ((int64_t)gridDim.x * kThreads) >> 4;
+    const unsigned gmask = 0xffffu << (threadIdx.x & 16);
+    for (int64_t r0 = (((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 4) * 4; r0 < n_this; r0 += groups * 4) {
         int64_t my_id = -1;
         int my_rmw = 0;
         if (sub < 4 && r0 + sub < n_this) {
             my_id = ids_this[r0 + sub];
             const uint64_t w = load_word(bitmap, wb, my_id);
-            if (n_next > 0 && ((w >> bit_next) & 1)) my_id = -1;  // retained on the GPU
+            if (has_next && ((w >> bit_next) & 1)) my_id = -1;  // retained on the GPU
             else if (accum == 1) my_rmw = 1;
             else if (accum == 2) { const uint64_t hi = w >> (bit_this + 1); my_rmw = (hi & (hi + 1)) != 0; }
         }
@@ -216,6 +259,16 @@ __global__ void set_signal_kernel(volatile int32_t *flags, int index, int value)
     __threadfence_system();
 }
 
+void set_carveouts() {
+    prefer_shared(copy_rows_kernel<Map64, Identity>);
+    prefer_shared(copy_rows_kernel<Map32, Map32>);
+    prefer_shared(copy_rows_kernel<Identity, Map64>);
+    prefer_shared(accum_rows_kernel<Identity, Map64>);
+    prefer_shared(accum_rows_kernel<Map32, Map32>);
+    prefer_shared(prefetch_host_kernel);
+    prefer_shared(handoff_host_kernel);
+}
+
 int check_align(const void *p, const char *what) {
     CLMGS_REQUIRE((((uintptr_t)p) & 15) == 0, "%s must be 16-byte aligned", what);
     return CLMGS_OK;
@@ -228,6 +281,7 @@ int check_align(const void *p, const char *what) {
 
 CLMGS_EXPORT int clmgs_rows_gather_i64(float *d_rows, const float *h_rows, const int64_t *ids, int64_t n,
                                        void *stream) {
+    set_carveouts();
     if (n == 0) return CLMGS_OK;
     if (int rc = check_align(d_rows, "d_rows")) return rc;
     if (int rc = check_align(h_rows, "h_rows")) return rc;
@@ -240,6 +294,7 @@ CLMGS_EXPORT int clmgs_rows_gather_retention(float *d_rows, const float *h_rows,
                                              const int32_t *host_ids, const int32_t *prev_src_rows,
                                              const int32_t *dst_rows_from_host, const int32_t *dst_rows_from_prev,
                                              int64_t n_host, int64_t n_prev, void *stream) {
+    set_carveouts();
     if (int rc = check_align(d_rows, "d_rows")) return rc;
     cudaStream_t st = as_stream(stream);
     if (n_host > 0) {
@@ -257,6 +312,7 @@ CLMGS_EXPORT int clmgs_rows_gather_retention(float *d_rows, const float *h_rows,
 
 CLMGS_EXPORT int clmgs_rows_scatter_grad_i64(const float *d_grad, float *h_grad, const int64_t *ids, int64_t n,
                                              int accum, void *stream) {
+    set_carveouts();
     if (n == 0) return CLMGS_OK;
     if (int rc = check_align(h_grad, "h_grad")) return rc;
     cudaStream_t st = as_stream(stream);
@@ -270,6 +326,7 @@ CLMGS_EXPORT int clmgs_rows_scatter_grad_retention(const float *d_grad, float *h
                                                    const int32_t *host_ids, const int32_t *next_dst_rows,
                                                    const int32_t *src_rows_to_host, const int32_t *src_rows_to_next,
                                                    int64_t n_host, int64_t n_next, int accum, void *stream) {
+    set_carveouts();
     cudaStream_t st = as_stream(stream);
     if (n_host > 0) {
         if (accum) accum_rows_kernel<<<grid_for(n_host), kThreads, 0, st>>>(F4(h_grad), CF4(d_grad), n_host, Map32{src_rows_to_host}, Map32{host_ids});
@@ -294,13 +351,17 @@ CLMGS_EXPORT int clmgs_rows_prefetch_next(float *d_next_rows, const float *h_row
                                           const int64_t *ids_this, int64_t n_this, const int64_t *ids_next,
                                           int64_t n_next, const void *bitmap, int word_bytes, int bit_this,
                                           int32_t *src_map, void *stream) {
+    set_carveouts();
     if (n_next == 0) return CLMGS_OK;
     CLMGS_REQUIRE(word_bytes == 1 || word_bytes == 2 || word_bytes == 4 || word_bytes == 8, "bad word_bytes");
-    int64_t blocks = ceil_div64(n_next * 4, kThreads);
-    int64_t cap = (int64_t)kNumSMs;
-    prefetch_next_kernel<<<(unsigned)(blocks > cap ? cap : blocks), kThreads, 0, as_stream(stream)>>>(
-        F4(d_next_rows), CF4(h_rows), CF4(d_this_rows), ids_this, n_this, ids_next, n_next, bitmap, word_bytes,
-        bit_this, src_map);
+    cudaStream_t st = as_stream(stream);
+    const int64_t blocks = ceil_div64(n_next * 4, kThreads);
+    const int64_t cap_dev = (int64_t)kNumSMs * 8, cap_host = (int64_t)kNumSMs;
+    prefetch_dev_kernel<<<(unsigned)(blocks > cap_dev ? cap_dev : blocks), kThreads, 0, st>>>(
+        F4(d_next_rows), CF4(d_this_rows), ids_this, n_this, ids_next, n_next, bitmap, word_bytes, bit_this, src_map);
+    CLMGS_LAUNCH_OK();
+    prefetch_host_kernel<<<(unsigned)(blocks > cap_host ? cap_host : blocks), kThreads, 0, st>>>(
+        F4(d_next_rows), CF4(h_rows), ids_next, n_next, src_map);
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }
@@ -309,15 +370,25 @@ CLMGS_EXPORT int clmgs_rows_grad_handoff(const float *d_grad_this, float *d_next
                                          const int64_t *ids_this, int64_t n_this, int64_t n_next,
                                          const int32_t *src_map, const void *bitmap, int word_bytes, int bit_this,
                                          int bit_next, int accum, void *stream) {
+    set_carveouts();
     int64_t n = n_this > n_next ? n_this : n_next;
     if (n == 0) return CLMGS_OK;
     CLMGS_REQUIRE(word_bytes == 1 || word_bytes == 2 || word_bytes == 4 || word_bytes == 8, "bad word_bytes");
     CLMGS_REQUIRE(accum >= 0 && accum <= 2, "grad_handoff: accum must be 0, 1 or 2");
-    int64_t blocks = ceil_div64(n * 4, kThreads);
-    int64_t cap = (int64_t)kNumSMs;
-    grad_handoff_kernel<<<(unsigned)(blocks > cap ? cap : blocks), kThreads, 0, as_stream(stream)>>>(
-        CF4(d_grad_this), F4(d_next_grad), F4(h_grad), ids_this, n_this, n_next, src_map, bitmap, word_bytes,
-        bit_this, bit_next, accum);
+    cudaStream_t st = as_stream(stream);
+    const int64_t cap_dev = (int64_t)kNumSMs * 8, cap_host = (int64_t)kNumSMs;
+    if (n_next > 0) {
+        const int64_t blocks = ceil_div64(n_next * 4, kThreads);
+        handoff_dev_kernel<<<(unsigned)(blocks > cap_dev ? cap_dev : blocks), kThreads, 0, st>>>(
+            CF4(d_grad_this), F4(d_next_grad), n_next, src_map);
+        CLMGS_LAUNCH_OK();
+    }
+    if (n_this > 0) {
+        const int64_t blocks = ceil_div64(n_this * 4, kThreads);
+        handoff_host_kernel<<<(unsigned)(blocks > cap_host ? cap_host : blocks), kThreads, 0, st>>>(
+            CF4(d_grad_this), F4(h_grad), ids_this, n_this, n_next > 0 ? 1 : 0, bitmap, word_bytes, bit_this, bit_next,
+            accum);
+    }
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }

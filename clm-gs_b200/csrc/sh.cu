@@ -108,6 +108,64 @@ __device__ __forceinline__ void sh_basis_grad(int degree, float x, float y, floa
     dx[24] = 0.6258357354491763f * fC3_x; dy[24] = 0.6258357354491763f * fC3_y;
 }
 
+// Visitor form: f(k, b_k, db_k/dx, db_k/dy, db_k/dz) is called for k = 0 .. (degree+1)^2-1 as soon as the
+// value is known, so a consumer that uses each basis once keeps ~20 live registers instead of 4 x 25.
+template <typename F>
+__device__ __forceinline__ void sh_visit(int degree, float x, float y, float z, F &&f) {
+    f(0, 0.2820947917738781f, 0.f, 0.f, 0.f);
+    if (degree < 1) return;
+    f(1, -0.48860251190292f * y, 0.f, -0.48860251190292f, 0.f);
+    f(2, 0.48860251190292f * z, 0.f, 0.f, 0.48860251190292f);
+    f(3, -0.48860251190292f * x, -0.48860251190292f, 0.f, 0.f);
+    if (degree < 2) return;
+    const float z2 = z * z;
+    const float fTmp0B = -1.092548430592079f * z;
+    const float fC1 = x * x - y * y, fS1 = 2.f * x * y;
+    const float fC1_x = 2.f * x, fC1_y = -2.f * y, fS1_x = 2.f * y, fS1_y = 2.f * x;
+    const float b6 = 0.9461746957575601f * z2 - 0.3153915652525201f;
+    const float b6_z = 2.f * 0.9461746957575601f * z;
+    f(4, 0.5462742152960395f * fS1, 0.5462742152960395f * fS1_x, 0.5462742152960395f * fS1_y, 0.f);
+    f(5, fTmp0B * y, 0.f, fTmp0B, -1.092548430592079f * y);
+    f(6, b6, 0.f, 0.f, b6_z);
+    f(7, fTmp0B * x, fTmp0B, 0.f, -1.092548430592079f * x);
+    f(8, 0.5462742152960395f * fC1, 0.5462742152960395f * fC1_x, 0.5462742152960395f * fC1_y, 0.f);
+    if (degree < 3) return;
+    const float fTmp0C = -2.285228997322329f * z2 + 0.4570457994644658f;
+    const float fTmp1B = 1.445305721320277f * z;
+    const float fC2 = x * fC1 - y * fS1, fS2 = x * fS1 + y * fC1;
+    const float fC2_x = fC1 + x * fC1_x - y * fS1_x, fC2_y = x * fC1_y - fS1 - y * fS1_y;
+    const float fS2_x = fS1 + x * fS1_x + y * fC1_x, fS2_y = x * fS1_y + fC1 + y * fC1_y;
+    const float fTmp0C_z = -2.285228997322329f * 2.f * z;
+    const float b12 = z * (1.865881662950577f * z2 - 1.119528997770346f);
+    const float b12_z = 3.f * 1.865881662950577f * z2 - 1.119528997770346f;
+    f(9, -0.5900435899266435f * fS2, -0.5900435899266435f * fS2_x, -0.5900435899266435f * fS2_y, 0.f);
+    f(10, fTmp1B * fS1, fTmp1B * fS1_x, fTmp1B * fS1_y, 1.445305721320277f * fS1);
+    f(11, fTmp0C * y, 0.f, fTmp0C, fTmp0C_z * y);
+    f(12, b12, 0.f, 0.f, b12_z);
+    f(13, fTmp0C * x, fTmp0C, 0.f, fTmp0C_z * x);
+    f(14, fTmp1B * fC1, fTmp1B * fC1_x, fTmp1B * fC1_y, 1.445305721320277f * fC1);
+    f(15, -0.5900435899266435f * fC2, -0.5900435899266435f * fC2_x, -0.5900435899266435f * fC2_y, 0.f);
+    if (degree < 4) return;
+    const float fTmp0D = z * (-4.683325804901025f * z2 + 2.007139630671868f);
+    const float fTmp1C = 3.31161143515146f * z2 - 0.47308734787878f;
+    const float fTmp2B = -1.770130769779931f * z;
+    const float fC3 = x * fC2 - y * fS2, fS3 = x * fS2 + y * fC2;
+    const float fTmp0D_z = 3.f * -4.683325804901025f * z2 + 2.007139630671868f;
+    const float fTmp1C_z = 2.f * 3.31161143515146f * z;
+    const float fC3_x = fC2 + x * fC2_x - y * fS2_x, fC3_y = x * fC2_y - fS2 - y * fS2_y;
+    const float fS3_x = fS2 + y * fC2_x + x * fS2_x, fS3_y = x * fS2_y + fC2 + y * fC2_y;
+    f(16, 0.6258357354491763f * fS3, 0.6258357354491763f * fS3_x, 0.6258357354491763f * fS3_y, 0.f);
+    f(17, fTmp2B * fS2, fTmp2B * fS2_x, fTmp2B * fS2_y, -1.770130769779931f * fS2);
+    f(18, fTmp1C * fS1, fTmp1C * fS1_x, fTmp1C * fS1_y, fTmp1C_z * fS1);
+    f(19, fTmp0D * y, 0.f, fTmp0D, fTmp0D_z * y);
+    f(20, 1.984313483298443f * z * b12 - 1.006230589874905f * b6, 0.f, 0.f,
+      1.984313483298443f * (b12 + z * b12_z) - 1.006230589874905f * b6_z);
+    f(21, fTmp0D * x, fTmp0D, 0.f, fTmp0D_z * x);
+    f(22, fTmp1C * fC1, fTmp1C * fC1_x, fTmp1C * fC1_y, fTmp1C_z * fC1);
+    f(23, fTmp2B * fC2, fTmp2B * fC2_x, fTmp2B * fC2_y, -1.770130769779931f * fC2);
+    f(24, 0.6258357354491763f * fC3, 0.6258357354491763f * fC3_x, 0.6258357354491763f * fC3_y, 0.f);
+}
+
 // Stage `rows` consecutive rows of `row_len` floats into smem with padded stride.
 __device__ __forceinline__ void stage_rows(float *s, int stride, const float *g, int rows, int row_len) {
     int total = rows * row_len;
@@ -216,32 +274,24 @@ sh_bwd_kernel(int64_t N, int K, int degree, const float *__restrict__ dirs, cons
                 inorm = rsqrtf(dx * dx + dy * dy + dz * dz);
                 x = dx * inorm; y = dy * inorm; z = dz * inorm;
             }
-            float b[25], bx[25], by[25], bz[25];
-            sh_basis_grad(degree, x, y, z, b, bx, by, bz);
             float vr = v_colors[3 * i], vg = v_colors[3 * i + 1], vb = v_colors[3 * i + 2];
             if (ENGINE) {  // gradient of clamp_min(c + 0.5, 0): passes where c + 0.5 >= 0
                 float cr = 0.f, cg = 0.f, cb = 0.f;
-#pragma unroll
-                for (int k = 0; k < 25; ++k)
-                    if (k < nb) { cr += b[k] * row[3 * k]; cg += b[k] * row[3 * k + 1]; cb += b[k] * row[3 * k + 2]; }
+                sh_visit(degree, x, y, z, [&](int k, float b, float, float, float) {
+                    cr += b * row[3 * k]; cg += b * row[3 * k + 1]; cb += b * row[3 * k + 2];
+                });
                 if (cr + 0.5f < 0.f) vr = 0.f;
                 if (cg + 0.5f < 0.f) vg = 0.f;
                 if (cb + 0.5f < 0.f) vb = 0.f;
             }
             float vx = 0.f, vy = 0.f, vz = 0.f;
-#pragma unroll
-            for (int k = 0; k < 25; ++k) {
-                if (k < K) {
-                    if (k < nb) {
-                        float cv = row[3 * k] * vr + row[3 * k + 1] * vg + row[3 * k + 2] * vb;
-                        vx += bx[k] * cv; vy += by[k] * cv; vz += bz[k] * cv;
-                        // overwrite the staged coefficient with its gradient contribution
-                        row[3 * k] = b[k] * vr; row[3 * k + 1] = b[k] * vg; row[3 * k + 2] = b[k] * vb;
-                    } else {
-                        row[3 * k] = row[3 * k + 1] = row[3 * k + 2] = 0.f;
-                    }
-                }
-            }
+            sh_visit(degree, x, y, z, [&](int k, float b, float dx, float dy, float dz) {
+                const float cv = row[3 * k] * vr + row[3 * k + 1] * vg + row[3 * k + 2] * vb;
+                vx += dx * cv; vy += dy * cv; vz += dz * cv;
+                // overwrite the staged coefficient with its gradient contribution
+                row[3 * k] = b * vr; row[3 * k + 1] = b * vg; row[3 * k + 2] = b * vb;
+            });
+            for (int k = nb; k < K; ++k) row[3 * k] = row[3 * k + 1] = row[3 * k + 2] = 0.f;
             if (v_dirs) {
                 if (degree >= 1) {
                     float dot = vx * x + vy * y + vz * z;

@@ -333,21 +333,25 @@ int clmgs_adam_dense(float *param, const float *grad, float *exp_avg, float *exp
  * the reference's cpu-adam, submodule TarzanZhao/cpu-adam @ f169c36, source
  * not in the mount; call sites optimizer.py:130-142, engine.py:301-335).
  * Blocking; releases nothing itself -- call it from a thread that does not
- * hold the GIL (ctypes does that).  For m in 0..bsz: waits (spins with pause)
- * until h_signal[m-1] != 0 for m >= 1, then updates rows
- * host_rows[row_begin[m] .. row_end[m]) of the pinned [N,48] tensors (group m
- * = rows whose last user is camera m-1; group 0 = untouched rows).
- * Group 0 (rows untouched this batch) is skipped when sparse_adam != 0.
+ * hold the GIL (ctypes does that).  Work is given as n_segments segments
+ * processed in order: segment s = host_rows[seg_begin[s] .. seg_end[s]) of the
+ * pinned [N,cols] tensors; before touching it every worker waits (spin with
+ * pause) until h_signal[seg_signal[s]] != 0, or not at all if seg_signal[s] < 0.
+ * The reference's batched_sparse_step(batch_size, lists, signals) is the case
+ * "segment m = rows whose last user is camera m-1, waiting on flag m-1; segment
+ * 0 = untouched rows, no wait, omitted when sparse_adam"; a caller may split a
+ * segment further and signal the pieces separately (the engine does this for
+ * the last camera so that the update overlaps the final gradient flush).
  * Gradients are multiplied by `scale`, and zeroed in place afterwards
  * (the reference's version=3).  n_threads <= 0 picks hardware concurrency.
  * ------------------------------------------------------------------------- */
 int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, float *host_exp_avg,
                                        float *host_exp_avg_sq, int cols, const float *col_lr,
-                                       const int32_t *host_rows, const int64_t *row_begin,
-                                       const int64_t *row_end, int bsz,
-                                       const volatile int32_t *h_signal, float b1,
+                                       const int32_t *host_rows, const int64_t *seg_begin,
+                                       const int64_t *seg_end, const int32_t *seg_signal,
+                                       int n_segments, const volatile int32_t *h_signal, float b1,
                                        float b2, float eps, int64_t step, float scale,
-                                       int sparse_adam, int n_threads);
+                                       int n_threads);
 
 /* fast_tsp.find_tour(dist, 0.001) (engine.py:179; submodule TarzanZhao/fast-tsp
  * @ 069eb3d, source not in the mount): deterministic greedy + 2-opt/Or-opt

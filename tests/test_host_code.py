@@ -73,8 +73,11 @@ def test_cpu_adam_matches_oracle_and_waits_for_signals():
 
         th = threading.Thread(target=fire); th.start()
         t0 = time.time()
-        ops.cpu_adam_batched_sparse_step(pp, gg, mm, vv, col_lr, rows, offs[:-1].copy(), offs[1:].copy(), bsz, signal, 0.9 ** 4, 0.999 ** 4,
-                                         1e-15 / 2, 2, 0.25, sparse, n_threads=3)
+        first = 1 if sparse else 0   # sparse_adam: the untouched group is simply not passed
+        seg_b, seg_e = offs[first:-1], offs[first + 1:]
+        seg_sig = np.arange(first, bsz + 1) - 1   # group m waits on flag m-1; group 0 (-1) does not wait
+        ops.cpu_adam_batched_sparse_step(pp, gg, mm, vv, col_lr, rows, seg_b, seg_e, seg_sig, signal, 0.9 ** 4,
+                                         0.999 ** 4, 1e-15 / 2, 2, 0.25, n_threads=3)
         dt = time.time() - t0
         th.join()
         assert dt > 0.06, "did not wait for the per-camera signals"
