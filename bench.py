@@ -151,7 +151,7 @@ def run_ours(a):
     import torch
     import torch.distributed as dist
 
-    from clmgs import _lib, engine, model, scene as S
+    from clmgs import _lib, engine, engine_dist, model, scene as S
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -170,13 +170,27 @@ def run_ours(a):
     spec = S.SceneSpec(spec.name, N, spec.width, spec.height, bsz, spec.shape, spec.fovx_deg, spec.index)
     W, H = spec.width, spec.height
     t0 = time.time()
-    # weak scaling over cameras: every rank trains its own replica on its own camera batches
-    # (multi-GPU sharded state: see DESIGN.md "Multi-GPU"; round 1 = replicas, no data-path collective)
-    sh_host = torch.empty(N, 48, dtype=torch.float32).pin_memory()
-    g = S.make_gaussians(spec, sh_out=sh_host.numpy())
-    args = model.TrainArgs(bsz=bsz, sparse_adam=a.sparse_adam, cpu_adam_threads=a.cpu_threads)
+    # N > 1: one global batch of world x bsz cameras per step, cameras data-parallel, SH rows + host Adam
+    # state sharded by Gaussian id, NCCL all-to-all-v for rows/gradients and all-reduce for the replicated
+    # attributes (clmgs/engine_dist.py).  Weak scaling: `bsz` cameras per GPU per step.
+    g = S.make_gaussians(spec)
+    ctx = engine_dist.DistContext(N) if world > 1 else None
+    lo, hi = (ctx.lo, ctx.hi) if ctx else (0, N)
+    sh_host = torch.empty(hi - lo, 48, dtype=torch.float32).pin_memory()
+    sh_host.copy_(torch.from_numpy(g["sh"][lo:hi]))
+    g["sh"] = None
+    args = model.TrainArgs(bsz=bsz * world, sparse_adam=a.sparse_adam,
+                           cpu_adam_threads=a.cpu_threads or max(1, (os.cpu_count() or 1) // world))
     gm = model.GaussianModelCLMOffload(3, dev).create_from_arrays(g["xyz"], g["log_scale"], g["raw_quat"],
                                                                  g["opacity_logit"], sh_host).training_setup(args)
+
+    def train_step(cams, timer=None):
+        if ctx is None:
+            return engine.clm_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None, comm, gen,
+                                                      timer=timer)
+        return engine_dist.clm_offload_train_one_batch_dist(gm, None, cams, gm.parameters_grad_buffer, None, None,
+                                                            comm, gen, ctx, timer=timer)
+
     n_batches = a.warmup + a.steps
     spec_r = S.SceneSpec(spec.name, N, W, H, bsz, spec.shape, spec.fovx_deg, spec.index + 100 * rank)
     V, K, P, gts = make_host_batches(spec_r, g, n_batches, bsz)
@@ -198,8 +212,7 @@ def run_ours(a):
             j = b * bsz + i
             img = gts_pinned[j % len(gts)].to(dev, non_blocking=True)
             cams.append(model.Camera(V_p[j], K_p[j], img, dev, uid=j))
-        losses, order, sp = engine.clm_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None,
-                                                               comm, gen)
+        losses, order, sp = train_step(cams)
         return torch.stack(losses).cpu()
 
     def barrier():
@@ -230,8 +243,7 @@ def run_ours(a):
     timer = engine.StageTimer(False)
 
     def step_resident(b):
-        engine.clm_offload_train_one_batch(gm, None, resident[b], gm.parameters_grad_buffer, None, None, comm, gen,
-                                           timer=timer)
+        train_step(resident[b], timer=timer)
 
     for b in range(a.warmup):
         step_resident(b)
@@ -242,7 +254,8 @@ def run_ours(a):
     launches = counter["n"]
     clk = clocks.stop()
     ms_per_step = ms_total / a.steps
-    value = world * 1000.0 / ms_per_step  # whole-job iterations/s (weak scaling: one iteration per rank per step)
+    # whole-job throughput in iterations of `bsz` cameras: a global step over world x bsz cameras counts `world`
+    value = world * 1000.0 / ms_per_step
 
     # ---- per-stage device times (separate pass: event pairs around every stage) -----------------
     timer = engine.StageTimer(True)
@@ -283,7 +296,9 @@ def run_ours(a):
                    dtype="f32", data="synthetic",
                    config=dict(workload="%s: %d Gaussians, %dx%d, batch %d cameras/iteration, SH degree 3, "
                                "clm_offload (48-float SH rows + Adam state in pinned host memory)" % (spec.name, N, W, H, bsz),
-                               parallelism="replica per GPU (camera batches data-parallel, weak)" if world > 1 else "1 GPU",
+                               parallelism=("dp%d over cameras: global batch %d cameras/step (counted as %d iterations of %d), SH rows + "
+                                            "host Adam sharded by Gaussian id, NCCL all-to-all-v + all-reduce" % (world, bsz * world, world, bsz))
+                               if world > 1 else "1 GPU",
                                l2="inputs larger than L2 (Gaussian tables %.0f MB >> 126 MB); no explicit flush" % (N * 44 / 1e6),
                                sparse_adam=bool(a.sparse_adam), cpu_adam_threads=a.cpu_threads or os.cpu_count(),
                                visible_per_camera=stats["n_visible"], isects_per_camera=stats["n_isects"],

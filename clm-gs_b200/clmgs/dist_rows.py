@@ -1,0 +1,76 @@
+"""Gaussian-sharded SH rows across ranks (SURVEY.md 8e -- new design, the reference is single-GPU).
+
+Rank g owns the contiguous id range [bounds[g], bounds[g+1]) of the offloaded table: its pinned
+host rows, gradient table and host-Adam moments.  A rank that renders a camera needs rows owned by
+others; per batch it asks every owner once (ids), owners gather from their pinned shard and the rows
+travel over NCCL all-to-all-v (NVLink); gradients of touched rows go back the same way and are summed
+at the owner (several ranks may touch one row).
+
+Device-agnostic on purpose: the only collectives are torch.distributed.all_to_all_single, and row
+gather / accumulate are callbacks (CUDA kernels in the engine, plain indexing in the gloo CPU tests).
+"""
+from dataclasses import dataclass
+from typing import Callable, List
+
+import torch
+import torch.distributed as dist
+
+
+class ShardMap:
+    def __init__(self, n_total: int, world: int):
+        self.n_total, self.world = int(n_total), int(world)
+        self.bounds = [self.n_total * g // self.world for g in range(self.world + 1)]
+
+    def range_of(self, rank):
+        return self.bounds[rank], self.bounds[rank + 1]
+
+    def n_local(self, rank):
+        return self.bounds[rank + 1] - self.bounds[rank]
+
+
+@dataclass
+class Plan:
+    need_ids: torch.Tensor      # ascending global ids this rank needs (its cameras' union)
+    send_counts: List[int]      # how many of need_ids each owner holds (owner-major == ascending)
+    recv_counts: List[int]      # how many ids each rank asks me for
+    recv_local: torch.Tensor    # the requested rows as LOCAL row indices of my shard, requester-major
+
+
+class RowExchange:
+    def __init__(self, shard: ShardMap, rank: int, group=None):
+        self.shard, self.rank, self.group = shard, rank, group
+        self.world = shard.world
+
+    def plan(self, need_ids: torch.Tensor) -> Plan:
+        dev = need_ids.device
+        inner = torch.tensor(self.shard.bounds[1:-1], dtype=need_ids.dtype, device=dev)
+        cuts = torch.searchsorted(need_ids, inner).tolist() if self.world > 1 else []
+        edges = [0] + cuts + [need_ids.shape[0]]
+        send_counts = [edges[i + 1] - edges[i] for i in range(self.world)]
+        cnt_in = torch.tensor(send_counts, dtype=torch.int64, device=dev)
+        cnt_out = torch.empty(self.world, dtype=torch.int64, device=dev)
+        dist.all_to_all_single(cnt_out, cnt_in, group=self.group)
+        recv_counts = cnt_out.tolist()
+        recv_ids = torch.empty(sum(recv_counts), dtype=need_ids.dtype, device=dev)
+        dist.all_to_all_single(recv_ids, need_ids.contiguous(), output_split_sizes=recv_counts,
+                               input_split_sizes=send_counts, group=self.group)
+        lo, hi = self.shard.range_of(self.rank)
+        recv_local = recv_ids - lo
+        return Plan(need_ids, send_counts, recv_counts, recv_local)
+
+    def fetch(self, plan: Plan, gather_local: Callable[[torch.Tensor], torch.Tensor], cols=48) -> torch.Tensor:
+        """rows[i] = table row of need_ids[i].  gather_local(local_idx) -> [n, cols] from my shard."""
+        send_rows = gather_local(plan.recv_local)
+        rows = torch.empty(plan.need_ids.shape[0], cols, dtype=send_rows.dtype, device=send_rows.device)
+        dist.all_to_all_single(rows, send_rows.contiguous(), output_split_sizes=plan.send_counts,
+                               input_split_sizes=plan.recv_counts, group=self.group)
+        return rows
+
+    def return_grads(self, plan: Plan, grad_rows: torch.Tensor,
+                     accumulate_local: Callable[[torch.Tensor, torch.Tensor], None]):
+        """grad_rows aligned with need_ids; every owner gets accumulate_local(local_idx, rows) with the
+        contributions of all ranks (local_idx may repeat across requesters: the callback must sum)."""
+        recv = torch.empty(plan.recv_local.shape[0], grad_rows.shape[1], dtype=grad_rows.dtype, device=grad_rows.device)
+        dist.all_to_all_single(recv, grad_rows.contiguous(), output_split_sizes=plan.recv_counts,
+                               input_split_sizes=plan.send_counts, group=self.group)
+        accumulate_local(plan.recv_local, recv)

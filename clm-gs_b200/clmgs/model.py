@@ -151,12 +151,14 @@ class GaussianModelCLMOffload:
         self._opacity = torch.from_numpy(np.ascontiguousarray(opacity_logit).reshape(N, 1)).to(dev)
         self._scaling = torch.from_numpy(np.ascontiguousarray(log_scale)).to(dev)
         self._rotation = torch.from_numpy(np.ascontiguousarray(raw_quat)).to(dev)
+        # the SH table may be a shard of the N Gaussians (multi-GPU: this rank's contiguous id range)
+        n_rows = sh.shape[0]
         if isinstance(sh, torch.Tensor):
             self.parameters_buffer = sh
         else:
-            self.parameters_buffer = _pinned_empty((capacity or N, 48))
-            self.parameters_buffer[:N].copy_(torch.from_numpy(np.ascontiguousarray(sh)))
-        self._parameters = self.parameters_buffer[:N]
+            self.parameters_buffer = _pinned_empty((capacity or n_rows, 48))
+            self.parameters_buffer[:n_rows].copy_(torch.from_numpy(np.ascontiguousarray(sh)))
+        self._parameters = self.parameters_buffer[:n_rows]
         self.parameters_grad_buffer = _pinned_zeros(tuple(self.parameters_buffer.shape))
         return self
 

@@ -292,6 +292,10 @@ def rows_scatter_grad_retention(d_grad, h_grad, d_next_grad, host_ids, next_dst_
          src_to_next, host_ids.shape[0], next_dst_rows.shape[0], int(accum), _st())
 
 
+def rows_accumulate(d_dst_rows, d_src_rows, dst_index):
+    call("clmgs_rows_accumulate", d_dst_rows, d_src_rows, dst_index.contiguous(), dst_index.shape[0], _st())
+
+
 def set_signal(h_flags, index, value):
     call("clmgs_set_signal", h_flags, int(index), int(value), _st())
 

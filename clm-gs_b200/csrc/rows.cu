@@ -253,6 +253,19 @@ handoff_host_kernel(const float4 *__restrict__ d_grad, float4 *__restrict__ h_gr
     }
 }
 
+// dst[idx[r]] += src[r], device memory, indices may repeat (several ranks touching one row): 16-byte
+// vector atomics (red.global.add.v4.f32, sm_90+).
+__global__ void __launch_bounds__(kThreads)
+accumulate_rows_kernel(float4 *__restrict__ dst, const float4 *__restrict__ src, const int64_t *__restrict__ idx,
+                       int64_t n) {
+    const int64_t total = n * kRowF4;
+    for (int64_t e = (int64_t)blockIdx.x * kThreads + threadIdx.x; e < total; e += (int64_t)gridDim.x * kThreads) {
+        const int64_t r = e / kRowF4;
+        const int c = (int)(e - r * kRowF4);
+        atomicAdd(dst + idx[r] * kRowF4 + c, src[e]);
+    }
+}
+
 __global__ void set_signal_kernel(volatile int32_t *flags, int index, int value) {
     __threadfence_system();  // everything this stream wrote to host memory is visible first
     flags[index] = value;
@@ -389,6 +402,17 @@ CLMGS_EXPORT int clmgs_rows_grad_handoff(const float *d_grad_this, float *d_next
             CF4(d_grad_this), F4(h_grad), ids_this, n_this, n_next > 0 ? 1 : 0, bitmap, word_bytes, bit_this, bit_next,
             accum);
     }
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_rows_accumulate(float *d_dst_rows, const float *d_src_rows, const int64_t *dst_index,
+                                       int64_t n, void *stream) {
+    if (n == 0) return CLMGS_OK;
+    int64_t blocks = ceil_div64(n * kRowF4, kThreads);
+    int64_t cap = (int64_t)kNumSMs * 8;
+    accumulate_rows_kernel<<<(unsigned)(blocks > cap ? cap : blocks), kThreads, 0, as_stream(stream)>>>(
+        F4(d_dst_rows), CF4(d_src_rows), dst_index, n);
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }

@@ -254,6 +254,11 @@ int clmgs_rows_scatter_grad_retention(const float *d_grad, float *h_grad, float 
                                       const int32_t *src_rows_to_next, int64_t n_host,
                                       int64_t n_next, int accum, void *stream);
 int clmgs_set_signal(int32_t *h_flags, int index, int value, void *stream);
+/* Multi-GPU owner-side sum (new design; the reference is single-GPU):
+ * d_dst_rows[dst_index[r]] += d_src_rows[r] for 48-float rows in device memory;
+ * indices may repeat (several ranks touched the same row). */
+int clmgs_rows_accumulate(float *d_dst_rows, const float *d_src_rows, const int64_t *dst_index,
+                          int64_t n, void *stream);
 
 /* ---------------------------------------------------------------------------
  * A2  Camera ordering / retention bookkeeping bitmaps.
