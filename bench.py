@@ -92,7 +92,7 @@ class ClockSampler:
 # kernels launched per C-ABI call (static table; the radix sort is CUB: 1 histogram + 1 scan-free
 # onesweep pass per 8 key bits for 46-bit keys -> 7 launches, + 2 copy-back memcpys not counted)
 LAUNCHES = dict(clmgs_cull_count=2, clmgs_cull_emit=1, clmgs_gather_activate=1, clmgs_projection_fwd=1,
-                clmgs_sh_colors_fwd=1, clmgs_isect_count=3, clmgs_isect_emit_sort=8, clmgs_isect_offset_encode=1,
+                clmgs_sh_colors_fwd=1, clmgs_isect_count=3, clmgs_isect_emit_sort=15, clmgs_isect_offset_encode=1,
                 clmgs_rasterize_fwd=1, clmgs_loss_fwd_bwd=3, clmgs_rasterize_bwd=1, clmgs_projection_bwd=1,
                 clmgs_sh_colors_bwd=1, clmgs_activate_bwd_scatter=1, clmgs_rows_gather_i64=1,
                 clmgs_rows_prefetch_next=2, clmgs_rows_grad_handoff=2, clmgs_set_signal=1,

@@ -193,7 +193,7 @@ def isect_tiles(means2d, radii, depths, tile_size, tile_width, tile_height, sort
     n_isects = int(cum[total - 1].item()) if total > 0 else 0
     ids = _empty((n_isects,), torch.int64, dev)
     flat = _empty((n_isects,), torch.int32, dev)
-    sc2 = _scratch(call("clmgs_isect_sort_scratch_bytes", n_isects) if sort else 0, dev)
+    sc2 = _scratch(call("clmgs_isect_sort_scratch_bytes", total, n_isects) if sort else 0, dev)
     call("clmgs_isect_emit_sort", C, N, camera_ids, means2d, radii, depths, cum, int(tile_size),
          int(tile_width), int(tile_height), n_isects, int(bool(sort)), ids, flat, sc2, sc2.numel(), _st())
     return tpg, ids, flat

@@ -482,6 +482,9 @@ isect_emit_kernel(int64_t total, int64_t N, const int64_t *__restrict__ camera_i
 int clmgs_radix_sort_pairs(int64_t n, int64_t *keys, int32_t *vals, int end_bit, void *scratch,
                            size_t scratch_bytes, cudaStream_t st);  // sort.cu
 size_t clmgs_radix_sort_scratch(int64_t n);
+size_t clmgs_sort_u32_temp_bytes(int64_t n);
+int clmgs_sort_pairs_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t *vals, int32_t *vals_alt, int end_bit,
+                         void *tmp, size_t tmp_bytes, cudaStream_t st, uint32_t **keys_out, int32_t **vals_out);
 
 static int n_bits_of(int64_t v) {  // floor(log2(v)) + 1, CSRC/isect_tiles.cu:143-144
     int b = 0;
@@ -489,7 +492,97 @@ static int n_bits_of(int64_t v) {  // floor(log2(v)) + 1, CSRC/isect_tiles.cu:14
     return b;
 }
 
-CLMGS_EXPORT size_t clmgs_isect_sort_scratch_bytes(int64_t n_isects) { return clmgs_radix_sort_scratch(n_isects); }
+// ---------------------------------------------------------------------------
+// Two-level tile sort.  The reference sorts I = n_isects pairs on a 64-bit key (cam | tile | depth)
+// with a stable LSD radix sort: ceil((32 + tile + cam bits)/8) = 6 passes over 12-byte pairs.  The
+// same permutation comes from (1) sorting the n Gaussians by depth bits (n << I, 32-bit keys), (2)
+// emitting intersections in that order and (3) one STABLE sort on the (cam | tile) bits alone
+// (13-14 bits = 2 passes over 8-byte pairs): within a tile the entries keep the order of step (1),
+// i.e. ascending depth with ties in ascending flatten index -- exactly what the 64-bit stable sort
+// leaves.  Traffic per intersection drops from ~6 x 24 B to ~2 x 16 B + 20 B.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+depth_keys_kernel(int64_t total, const int32_t *__restrict__ radii, const float *__restrict__ depths,
+                  uint32_t *__restrict__ keys, int32_t *__restrict__ perm) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    keys[i] = radii[i] > 0 ? (uint32_t)__float_as_int(depths[i]) : 0xffffffffu;  // culled entries last (emit nothing)
+    perm[i] = (int32_t)i;
+}
+
+__global__ void __launch_bounds__(kScanThreads)
+perm_count_kernel(int64_t total, const int32_t *__restrict__ perm, const float *__restrict__ means2d,
+                  const int32_t *__restrict__ radii, int tile_size, int tw, int th, int64_t *__restrict__ block_sums) {
+    __shared__ int64_t s_warp[33];
+    int64_t j = (int64_t)blockIdx.x * kScanThreads + threadIdx.x;
+    int64_t v = j < total ? tiles_of(means2d, radii, perm[j], tile_size, tw, th) : 0, tot;
+    block_excl_scan_1024<int64_t>(v, s_warp, &tot);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
+}
+
+// emits the (cam|tile) key and the flatten index of every intersection, Gaussians in depth order
+__global__ void __launch_bounds__(kScanThreads)
+perm_emit_kernel(int64_t total, int64_t N, const int64_t *__restrict__ camera_ids, const int32_t *__restrict__ perm,
+                 const float *__restrict__ means2d, const int32_t *__restrict__ radii,
+                 const int64_t *__restrict__ block_sums, int tile_size, int tw, int th, int tile_n_bits,
+                 uint32_t *__restrict__ tkeys, int32_t *__restrict__ vals) {
+    __shared__ int64_t s_warp[33];
+    int64_t j = (int64_t)blockIdx.x * kScanThreads + threadIdx.x;
+    int idx = j < total ? perm[j] : 0;
+    int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    int64_t v = 0, tot;
+    if (j < total && radii[idx] > 0) {
+        tile_rect(means2d[2 * (int64_t)idx], means2d[2 * (int64_t)idx + 1], radii[idx], tile_size, tw, th, x0, y0, x1, y1);
+        v = (int64_t)(y1 - y0) * (x1 - x0);
+    }
+    int64_t cur = block_sums[blockIdx.x] + block_excl_scan_1024<int64_t>(v, s_warp, &tot);
+    if (v == 0) return;
+    const uint32_t cid = (uint32_t)(camera_ids ? camera_ids[idx] : idx / N);
+    const uint32_t cid_enc = cid << tile_n_bits;
+    for (int i = y0; i < y1; ++i)
+        for (int jj = x0; jj < x1; ++jj) {
+            tkeys[cur] = cid_enc | (uint32_t)(i * tw + jj);
+            vals[cur] = idx;
+            ++cur;
+        }
+}
+
+__global__ void __launch_bounds__(256)
+isect_finalize_kernel(int64_t n_isects, const uint32_t *__restrict__ tkeys, const int32_t *__restrict__ vals,
+                      const float *__restrict__ depths, int64_t *__restrict__ isect_ids,
+                      int32_t *__restrict__ flatten_ids) {
+    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_isects) return;
+    const int32_t g = vals[p];
+    isect_ids[p] = ((int64_t)tkeys[p] << 32) | (int64_t)(uint32_t)__float_as_int(depths[g]);
+    if (flatten_ids != vals) flatten_ids[p] = g;
+}
+
+static inline size_t a256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct TwoLevelLayout {
+    size_t dkeys, dkeys_alt, perm, perm_alt, block_sums, tkeys, tkeys_alt, vals_alt, tmp, total_bytes, tmp_bytes;
+};
+static TwoLevelLayout two_level_layout(int64_t total, int64_t n_isects) {
+    TwoLevelLayout L;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o += a256(bytes); return r; };
+    L.dkeys = take(4 * (size_t)total); L.dkeys_alt = take(4 * (size_t)total);
+    L.perm = take(4 * (size_t)total); L.perm_alt = take(4 * (size_t)total);
+    L.block_sums = take(8 * (size_t)ceil_div64(total > 0 ? total : 1, kScanThreads));
+    L.tkeys = take(4 * (size_t)n_isects); L.tkeys_alt = take(4 * (size_t)n_isects);
+    L.vals_alt = take(4 * (size_t)n_isects);
+    size_t t1 = clmgs_sort_u32_temp_bytes(total), t2 = clmgs_sort_u32_temp_bytes(n_isects);
+    L.tmp_bytes = t1 > t2 ? t1 : t2;
+    L.tmp = take(L.tmp_bytes);
+    L.total_bytes = o;
+    return L;
+}
+
+CLMGS_EXPORT size_t clmgs_isect_sort_scratch_bytes(int64_t total, int64_t n_isects) {
+    if (total <= 0 || n_isects <= 0) return 0;
+    return two_level_layout(total, n_isects).total_bytes;
+}
 
 CLMGS_EXPORT int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_ids, const float *means2d,
                                        const int32_t *radii, const float *depths, const int64_t *cum_tiles,
@@ -498,19 +591,55 @@ CLMGS_EXPORT int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_i
                                        size_t scratch_bytes, void *stream) {
     int64_t total = camera_ids ? N : (int64_t)C * N;
     if (total == 0 || n_isects == 0) return CLMGS_OK;
-    CLMGS_REQUIRE(n_isects < ((int64_t)1 << 31), "isect: n_isects=%lld does not fit int32 offsets", (long long)n_isects);
+    CLMGS_REQUIRE(n_isects < ((int64_t)1 << 31) && total < ((int64_t)1 << 31),
+                  "isect: n_isects=%lld / total=%lld do not fit int32 indices", (long long)n_isects, (long long)total);
     int tile_n_bits = n_bits_of((int64_t)tile_width * tile_height);
     int cam_n_bits = n_bits_of(C);
     CLMGS_REQUIRE(tile_n_bits + cam_n_bits <= 32, "isect: too many tiles/cameras for a 64-bit key");
     cudaStream_t st = as_stream(stream);
-    isect_emit_kernel<<<(unsigned)ceil_div64(total, 256), 256, 0, st>>>(total, N, camera_ids, means2d, radii, depths,
-                                                                       cum_tiles, tile_size, tile_width,
-                                                                       tile_height, tile_n_bits, isect_ids,
-                                                                       flatten_ids);
+    if (!sort) {  // unsorted emission in flatten-index order (gsplat's sort=False)
+        isect_emit_kernel<<<(unsigned)ceil_div64(total, 256), 256, 0, st>>>(total, N, camera_ids, means2d, radii, depths,
+                                                                           cum_tiles, tile_size, tile_width,
+                                                                           tile_height, tile_n_bits, isect_ids,
+                                                                           flatten_ids);
+        CLMGS_LAUNCH_OK();
+        return CLMGS_OK;
+    }
+    TwoLevelLayout L = two_level_layout(total, n_isects);
+    if (scratch == nullptr || scratch_bytes < L.total_bytes) {
+        clmgs_set_error("isect_emit_sort: scratch too small (%zu < %zu)", scratch_bytes, L.total_bytes);
+        return CLMGS_ERR_SCRATCH;
+    }
+    char *base = (char *)scratch;
+    uint32_t *dkeys = (uint32_t *)(base + L.dkeys), *dkeys_alt = (uint32_t *)(base + L.dkeys_alt);
+    int32_t *perm = (int32_t *)(base + L.perm), *perm_alt = (int32_t *)(base + L.perm_alt);
+    int64_t *bs = (int64_t *)(base + L.block_sums);
+    uint32_t *tkeys = (uint32_t *)(base + L.tkeys), *tkeys_alt = (uint32_t *)(base + L.tkeys_alt);
+    int32_t *vals_alt = (int32_t *)(base + L.vals_alt);
+    void *tmp = base + L.tmp;
+    // (1) Gaussians by depth
+    depth_keys_kernel<<<(unsigned)ceil_div64(total, 256), 256, 0, st>>>(total, radii, depths, dkeys, perm);
     CLMGS_LAUNCH_OK();
-    if (sort)
-        return clmgs_radix_sort_pairs(n_isects, isect_ids, flatten_ids, 32 + tile_n_bits + cam_n_bits, scratch,
-                                      scratch_bytes, st);
+    uint32_t *dk_sorted; int32_t *perm_sorted;
+    if (int rc = clmgs_sort_pairs_u32(total, dkeys, dkeys_alt, perm, perm_alt, 32, tmp, L.tmp_bytes, st, &dk_sorted, &perm_sorted)) return rc;
+    // (2) offsets in depth order, emission
+    const int64_t nblocks = ceil_div64(total, kScanThreads);
+    perm_count_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(total, perm_sorted, means2d, radii, tile_size, tile_width,
+                                                                 tile_height, bs);
+    CLMGS_LAUNCH_OK();
+    scan_block_sums_kernel<<<1, kScanThreads, 0, st>>>(bs, nblocks);
+    CLMGS_LAUNCH_OK();
+    perm_emit_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(total, N, camera_ids, perm_sorted, means2d, radii, bs,
+                                                                tile_size, tile_width, tile_height, tile_n_bits, tkeys,
+                                                                flatten_ids);
+    CLMGS_LAUNCH_OK();
+    // (3) stable partition by (cam | tile)
+    uint32_t *tk_sorted; int32_t *val_sorted;
+    if (int rc = clmgs_sort_pairs_u32(n_isects, tkeys, tkeys_alt, flatten_ids, vals_alt, tile_n_bits + cam_n_bits, tmp,
+                                      L.tmp_bytes, st, &tk_sorted, &val_sorted)) return rc;
+    isect_finalize_kernel<<<(unsigned)ceil_div64(n_isects, 256), 256, 0, st>>>(n_isects, tk_sorted, val_sorted, depths,
+                                                                              isect_ids, flatten_ids);
+    CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }
 

@@ -249,7 +249,7 @@ CLMGS_EXPORT int clmgs_sh_colors_fwd(int64_t N, int K, int degree, const float *
 // Backward: rows of coeffs AND of v_coeffs go through shared memory so that
 // both the read and the read-modify-write of the 192-B rows are coalesced.
 template <bool ENGINE>
-__global__ void __launch_bounds__(kShRows)
+__global__ void __launch_bounds__(kShRows, 8)  // <= 64 registers: 8 CTAs/SM (8 x 24.5 KB smem) keeps enough rows in flight
 sh_bwd_kernel(int64_t N, int K, int degree, const float *__restrict__ dirs, const float *__restrict__ campos,
               const float *__restrict__ coeffs, const uint8_t *__restrict__ masks,
               const float *__restrict__ v_colors, float *__restrict__ v_coeffs, int accumulate,

@@ -46,3 +46,28 @@ int clmgs_radix_sort_pairs(int64_t n, int64_t *keys, int32_t *vals, int end_bit,
         CLMGS_CUDA(cudaMemcpyAsync(vals, dv.Current(), sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
     return CLMGS_OK;
 }
+
+// ---- 32-bit key variant used by the two-level tile sort (proj.cu) -----------------------------
+size_t clmgs_sort_u32_temp_bytes(int64_t n) {
+    if (n <= 0) return 0;
+    size_t tmp = 0;
+    cub::DoubleBuffer<uint32_t> k(nullptr, nullptr);
+    cub::DoubleBuffer<int32_t> v(nullptr, nullptr);
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp, k, v, n, 0, 32, (cudaStream_t)0);
+    return align256(tmp);
+}
+
+// Sorts (keys, vals) over key bits [0, end_bit); *keys_out / *vals_out tell which of the two
+// buffers holds the result (no copy back).
+int clmgs_sort_pairs_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t *vals, int32_t *vals_alt, int end_bit,
+                         void *tmp, size_t tmp_bytes, cudaStream_t st, uint32_t **keys_out, int32_t **vals_out) {
+    *keys_out = keys;
+    *vals_out = vals;
+    if (n <= 1 || end_bit <= 0) return CLMGS_OK;
+    cub::DoubleBuffer<uint32_t> dk(keys, keys_alt);
+    cub::DoubleBuffer<int32_t> dv(vals, vals_alt);
+    CLMGS_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, dk, dv, (int)n, 0, end_bit, st));
+    *keys_out = dk.Current();
+    *vals_out = dv.Current();
+    return CLMGS_OK;
+}

@@ -150,9 +150,12 @@ int clmgs_sh_colors_bwd(int64_t N, int K, int degree, const float *means, const 
  * prefix sum, == torch.cumsum in the reference), n_isects = cum_tiles[last]
  * (device scalar, also returned in *d_n_isects if non-NULL).
  * clmgs_isect_emit_sort: writes isect_ids [n_isects] i64 and flatten_ids
- * [n_isects] i32; if `sort`, they are sorted by the low
- * 32+tile_n_bits+cam_n_bits key bits with a stable LSD radix sort
- * (cub::DeviceRadixSort semantics, CSRC/isect_tiles.cu:196-203).
+ * [n_isects] i32; if `sort`, they come out in the order a stable LSD radix
+ * sort on the low 32+tile_n_bits+cam_n_bits key bits gives
+ * (cub::DeviceRadixSort semantics, CSRC/isect_tiles.cu:196-203), computed as
+ * depth sort of the Gaussians + stable (cam|tile) partition of the
+ * intersections (same permutation, a quarter of the traffic).  scratch:
+ * clmgs_isect_sort_scratch_bytes(total = C*N or nnz, n_isects).
  * ------------------------------------------------------------------------- */
 size_t clmgs_isect_count_scratch_bytes(int64_t total);
 int clmgs_isect_count(int64_t total, const float *means2d, const int32_t *radii, int tile_size,
@@ -175,7 +178,7 @@ int64_t clmgs_isect_count_static_max(void);
 int clmgs_isect_count_static(int64_t total, const float *means2d, const int32_t *radii,
                              int tile_size, int tile_width, int tile_height,
                              int32_t *tiles_per_gauss, int64_t *cum_tiles, void *stream);
-size_t clmgs_isect_sort_scratch_bytes(int64_t n_isects);
+size_t clmgs_isect_sort_scratch_bytes(int64_t total, int64_t n_isects);
 int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_ids, const float *means2d,
                           const int32_t *radii, const float *depths, const int64_t *cum_tiles,
                           int tile_size, int tile_width, int tile_height, int64_t n_isects,
