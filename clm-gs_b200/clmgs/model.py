@@ -45,7 +45,7 @@ class TrainArgs:
     spatial_lr_scale: float = 1.0
     cpu_adam_threads: int = 0  # 0 = all hardware threads
     final_flush_chunks: int = 8  # last camera: flush + host Adam pipelined in this many pieces
-    rows_lookahead: int = 1  # SH-row prefetches issued this many cameras ahead on the copy stream
+    rows_lookahead: int = 2  # SH-row prefetches issued this many cameras ahead on the copy stream
     geometry_lookahead: int = 3  # cameras whose projection/tile sort is issued ahead of their SH rows
 
 

@@ -36,48 +36,62 @@ CONFIGS = {
 }
 
 
-def make_gaussians(spec: SceneSpec, n=None, chunk=4_000_000, sh_out=None):
+def make_gaussians(spec: SceneSpec, n=None, chunk=1_000_000, sh_out=None, sh_rows=None, want_sh=True):
     """Returns dict of float32 arrays: xyz[N,3], log_scale[N,3], raw_quat[N,4],
-    opacity_logit[N,1], sh[N,48].  ``sh_out`` may be a preallocated (pinned) [N,48]
-    array that is filled in place (large scenes)."""
+    opacity_logit[N,1], sh[rows,48].
+
+    Generation is chunked with one RNG per (scene seed, chunk index), so any row range can be
+    produced independently: ``sh_rows=(lo, hi)`` makes only that shard of the SH table (multi-GPU
+    ranks), ``n`` makes only the first n Gaussians (a uniform subsample -- ids are i.i.d.), and
+    ``sh_out`` may be a preallocated (pinned) array that is filled in place."""
     N = int(n if n is not None else spec.n_gaussians)   # how many to generate (a prefix of the scene)
     NF = int(spec.n_gaussians)                          # the scene's size: fixes spacing / extent
-    rng = np.random.default_rng(1234 + spec.index)
-    xyz = np.empty((N, 3), np.float32)
+    seed = 1234 + spec.index
     if spec.shape == "object":
-        # N(0, I) truncated to |x| < 3 (rejection, chunked)
-        filled = 0
-        while filled < N:
-            m = min(chunk, int((N - filled) * 1.05) + 16)
-            p = rng.standard_normal((m, 3), dtype=np.float32)
-            p = p[(p * p).sum(1) < 9.0]
-            k = min(len(p), N - filled)
-            xyz[filled:filled + k] = p[:k]
-            filled += k
         spacing = (4.0 / 3.0 * math.pi * 27.0 / NF) ** (1.0 / 3.0)
         L = 3.0
     else:
         L = 0.5 * math.sqrt(NF / 1e4)
-        for s in range(0, N, chunk):
-            e = min(N, s + chunk)
-            u = rng.random((e - s, 3), dtype=np.float32)
-            xyz[s:e, 0] = (2 * u[:, 0] - 1) * L
-            xyz[s:e, 1] = (2 * u[:, 1] - 1) * L
-            xyz[s:e, 2] = u[:, 2] * 0.1 * L
         spacing = (2 * L * 2 * L * 0.1 * L / NF) ** (1.0 / 3.0)
+    mu = math.log(0.5 * spacing)
+    xyz = np.empty((N, 3), np.float32)
     log_scale = np.empty((N, 3), np.float32)
     raw_quat = np.empty((N, 4), np.float32)
     opacity = np.empty((N, 1), np.float32)
-    sh = sh_out if sh_out is not None else np.empty((N, 48), np.float32)
-    mu = math.log(0.5 * spacing)
-    for s in range(0, N, chunk):
-        e = min(N, s + chunk)
-        log_scale[s:e] = mu + 0.4 * rng.standard_normal((e - s, 3), dtype=np.float32)
-        q = rng.standard_normal((e - s, 4), dtype=np.float32)
-        raw_quat[s:e] = q / np.linalg.norm(q, axis=1, keepdims=True)
-        opacity[s:e] = 1.5 * rng.standard_normal((e - s, 1), dtype=np.float32)
-        sh[s:e, :3] = 0.5 * rng.standard_normal((e - s, 3), dtype=np.float32)
-        sh[s:e, 3:] = 0.1 * rng.standard_normal((e - s, 45), dtype=np.float32)
+    lo, hi = (0, N) if sh_rows is None else (int(sh_rows[0]), int(sh_rows[1]))
+    sh = None
+    if want_sh:
+        sh = sh_out if sh_out is not None else np.empty((hi - lo, 48), np.float32)
+        assert sh.shape[0] == hi - lo
+    for ci, s0 in enumerate(range(0, N, chunk)):
+        e0 = min(N, s0 + chunk)
+        m = e0 - s0
+        # one stream per attribute, so that a shorter chunk (n < chunk) is a prefix of the full one
+        rng = np.random.default_rng([seed, ci, 0])
+        r_s, r_q, r_o = (np.random.default_rng([seed, ci, k]) for k in (1, 2, 3))
+        if spec.shape == "object":
+            # N(0, I) truncated to |x| < 3: draw extra and keep the first m accepted
+            p = rng.standard_normal((int(m * 1.05) + 64, 3), dtype=np.float32)
+            p = p[(p * p).sum(1) < 9.0]
+            while len(p) < m:
+                q = rng.standard_normal((m, 3), dtype=np.float32)
+                p = np.concatenate([p, q[(q * q).sum(1) < 9.0]])
+            xyz[s0:e0] = p[:m]
+        else:
+            u = rng.random((m, 3), dtype=np.float32)
+            xyz[s0:e0, 0] = (2 * u[:, 0] - 1) * L
+            xyz[s0:e0, 1] = (2 * u[:, 1] - 1) * L
+            xyz[s0:e0, 2] = u[:, 2] * 0.1 * L
+        log_scale[s0:e0] = mu + 0.4 * r_s.standard_normal((m, 3), dtype=np.float32)
+        q = r_q.standard_normal((m, 4), dtype=np.float32)
+        raw_quat[s0:e0] = q / np.linalg.norm(q, axis=1, keepdims=True)
+        opacity[s0:e0] = 1.5 * r_o.standard_normal((m, 1), dtype=np.float32)
+        a_, b_ = max(s0, lo), min(e0, hi)
+        if want_sh and a_ < b_:
+            dc = 0.5 * np.random.default_rng([seed, ci, 7]).standard_normal((m, 3), dtype=np.float32)
+            rest = 0.1 * np.random.default_rng([seed, ci, 8]).standard_normal((m, 45), dtype=np.float32)
+            sh[a_ - lo:b_ - lo, :3] = dc[a_ - s0:b_ - s0]
+            sh[a_ - lo:b_ - lo, 3:] = rest[a_ - s0:b_ - s0]
     return dict(xyz=xyz, log_scale=log_scale, raw_quat=raw_quat, opacity_logit=opacity, sh=sh,
                 extent=L, spacing=spacing)
 

@@ -7,6 +7,8 @@
 // float4 is always legal), the grid is sized to keep all 148 SMs issuing, and
 // each thread keeps UNROLL independent loads in flight -- what a PCIe-latency
 // bound transfer needs.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -23,12 +25,22 @@ __device__ __forceinline__ float4 ld_stream(const float4 *p) {
 }
 
 // Transfer kernels run on a side stream next to the render kernels and spend their time waiting on
-// PCIe: one 256-thread CTA per SM (12.5% of the thread slots) with 4 x 16 B in flight per thread is
-// ~2.4 MB outstanding -- far above the link's bandwidth-delay product -- and leaves the SMs to the
-// compute stream.  (Filling every slot starved the render kernels: measured 24 ms for a 0.4 ms Adam.)
-inline unsigned grid_for(int64_t n_rows) {
+// PCIe.  Every zero-copy load holds an L1 miss slot of its SM for ~2 us, so a host-bound CTA slows
+// whatever else runs on that SM (measured at C4: every render kernel 2-3x slower with one transfer
+// CTA on each of the 148 SMs; with all thread slots filled a 0.4 ms Adam took 24 ms).  The link needs
+// only bandwidth x latency = ~50 GB/s x 2 us = 100 KB in flight: 32 CTAs x 256 threads x 4 x 16 B
+// = 512 KB covers it while touching a fifth of the SMs (the reference also uses 32 CTAs, but with
+// 4-byte accesses).
+inline int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+// tunables (read once): CTAs of kernels that LOAD from host / STORE to host
+inline int host_load_ctas() { static int v = env_int("CLMGS_HOST_LOAD_CTAS", 48); return v; }
+inline int host_store_ctas() { static int v = env_int("CLMGS_HOST_STORE_CTAS", 64); return v; }
+inline unsigned grid_for(int64_t n_rows, bool store = false) {
     int64_t work = ceil_div64(n_rows * kRowF4, (int64_t)kThreads * kUnroll);
-    int64_t cap = (int64_t)kNumSMs;
+    int64_t cap = store ? host_store_ctas() : host_load_ctas();
     return (unsigned)(work < 1 ? 1 : (work > cap ? cap : work));
 }
 
@@ -329,8 +341,8 @@ CLMGS_EXPORT int clmgs_rows_scatter_grad_i64(const float *d_grad, float *h_grad,
     if (n == 0) return CLMGS_OK;
     if (int rc = check_align(h_grad, "h_grad")) return rc;
     cudaStream_t st = as_stream(stream);
-    if (accum) accum_rows_kernel<<<grid_for(n), kThreads, 0, st>>>(F4(h_grad), CF4(d_grad), n, Identity{}, Map64{ids});
-    else copy_rows_kernel<<<grid_for(n), kThreads, 0, st>>>(F4(h_grad), CF4(d_grad), n, Identity{}, Map64{ids});
+    if (accum) accum_rows_kernel<<<grid_for(n, true), kThreads, 0, st>>>(F4(h_grad), CF4(d_grad), n, Identity{}, Map64{ids});
+    else copy_rows_kernel<<<grid_for(n, true), kThreads, 0, st>>>(F4(h_grad), CF4(d_grad), n, Identity{}, Map64{ids});
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }
@@ -369,7 +381,7 @@ CLMGS_EXPORT int clmgs_rows_prefetch_next(float *d_next_rows, const float *h_row
     CLMGS_REQUIRE(word_bytes == 1 || word_bytes == 2 || word_bytes == 4 || word_bytes == 8, "bad word_bytes");
     cudaStream_t st = as_stream(stream);
     const int64_t blocks = ceil_div64(n_next * 4, kThreads);
-    const int64_t cap_dev = (int64_t)kNumSMs * 8, cap_host = (int64_t)kNumSMs;
+    const int64_t cap_dev = (int64_t)kNumSMs * 4, cap_host = host_load_ctas();
     prefetch_dev_kernel<<<(unsigned)(blocks > cap_dev ? cap_dev : blocks), kThreads, 0, st>>>(
         F4(d_next_rows), CF4(d_this_rows), ids_this, n_this, ids_next, n_next, bitmap, word_bytes, bit_this, src_map);
     CLMGS_LAUNCH_OK();
@@ -389,7 +401,7 @@ CLMGS_EXPORT int clmgs_rows_grad_handoff(const float *d_grad_this, float *d_next
     CLMGS_REQUIRE(word_bytes == 1 || word_bytes == 2 || word_bytes == 4 || word_bytes == 8, "bad word_bytes");
     CLMGS_REQUIRE(accum >= 0 && accum <= 2, "grad_handoff: accum must be 0, 1 or 2");
     cudaStream_t st = as_stream(stream);
-    const int64_t cap_dev = (int64_t)kNumSMs * 8, cap_host = (int64_t)kNumSMs;
+    const int64_t cap_dev = (int64_t)kNumSMs * 4, cap_host = host_store_ctas();
     if (n_next > 0) {
         const int64_t blocks = ceil_div64(n_next * 4, kThreads);
         handoff_dev_kernel<<<(unsigned)(blocks > cap_dev ? cap_dev : blocks), kThreads, 0, st>>>(

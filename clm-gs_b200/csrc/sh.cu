@@ -339,12 +339,92 @@ CLMGS_EXPORT int clmgs_sh_bwd(int64_t N, int K, int degree, const float *dirs, c
     return CLMGS_OK;
 }
 
+// Engine backward for K = 16 (degree <= 3): four lanes per Gaussian, lane j owns bases 4j..4j+3 = 12
+// consecutive floats = three float4 of the 192-B row.  No shared memory, no block barriers: the row of
+// coefficients is read and the row of gradients read-modified-written with 16-byte accesses that are
+// contiguous across the warp (8 Gaussians = 1536 B), the colour (for the clamp mask) and the direction
+// gradient are 4-lane shuffle reductions.  Each lane evaluates the whole basis but keeps only its four.
+__global__ void __launch_bounds__(256)
+sh_colors_bwd_lanes_kernel(int64_t N, int degree, const float *__restrict__ means, const float *__restrict__ campos,
+                           const float4 *__restrict__ coeffs, const float *__restrict__ v_colors,
+                           float4 *__restrict__ v_coeffs, float *__restrict__ v_means) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t g = tid >> 2;
+    const int j = (int)(tid & 3);
+    if (g >= N) return;  // N*4 threads: a whole 4-lane group leaves together
+    const unsigned gmask = 0xfu << ((threadIdx.x & 31) & ~3);
+    float x = 0.f, y = 0.f, z = 0.f, inorm = 0.f;
+    if (degree >= 1) {
+        float dx = __ldg(means + 3 * g) - campos[0], dy = __ldg(means + 3 * g + 1) - campos[1],
+              dz = __ldg(means + 3 * g + 2) - campos[2];
+        inorm = rsqrtf(dx * dx + dy * dy + dz * dz);
+        x = dx * inorm; y = dy * inorm; z = dz * inorm;
+    }
+    float mb[4] = {0.f, 0.f, 0.f, 0.f}, mx[4] = {0.f, 0.f, 0.f, 0.f}, my[4] = {0.f, 0.f, 0.f, 0.f},
+          mz[4] = {0.f, 0.f, 0.f, 0.f};
+    sh_visit(degree, x, y, z, [&](int k, float b, float bx, float by, float bz) {
+        if ((k >> 2) == j) { mb[k & 3] = b; mx[k & 3] = bx; my[k & 3] = by; mz[k & 3] = bz; }
+    });
+    const float4 *crow = coeffs + g * 12 + j * 3;
+    float cf[12];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        const float4 v = __ldg(crow + q);
+        cf[4 * q] = v.x; cf[4 * q + 1] = v.y; cf[4 * q + 2] = v.z; cf[4 * q + 3] = v.w;
+    }
+    // colour -> clamp mask (gradient of clamp_min(c + 0.5, 0) passes where c + 0.5 >= 0)
+    float cr = 0.f, cg = 0.f, cb = 0.f;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { cr += mb[t] * cf[3 * t]; cg += mb[t] * cf[3 * t + 1]; cb += mb[t] * cf[3 * t + 2]; }
+#pragma unroll
+    for (int o = 1; o < 4; o <<= 1) {
+        cr += __shfl_xor_sync(gmask, cr, o); cg += __shfl_xor_sync(gmask, cg, o); cb += __shfl_xor_sync(gmask, cb, o);
+    }
+    float vr = __ldg(v_colors + 3 * g), vg = __ldg(v_colors + 3 * g + 1), vb = __ldg(v_colors + 3 * g + 2);
+    if (cr + 0.5f < 0.f) vr = 0.f;
+    if (cg + 0.5f < 0.f) vg = 0.f;
+    if (cb + 0.5f < 0.f) vb = 0.f;
+    float vx = 0.f, vy = 0.f, vz = 0.f, gf[12];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const float cv = cf[3 * t] * vr + cf[3 * t + 1] * vg + cf[3 * t + 2] * vb;
+        vx += mx[t] * cv; vy += my[t] * cv; vz += mz[t] * cv;
+        gf[3 * t] = mb[t] * vr; gf[3 * t + 1] = mb[t] * vg; gf[3 * t + 2] = mb[t] * vb;
+    }
+    float4 *grow = v_coeffs + g * 12 + j * 3;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        float4 o = grow[q];
+        o.x += gf[4 * q]; o.y += gf[4 * q + 1]; o.z += gf[4 * q + 2]; o.w += gf[4 * q + 3];
+        grow[q] = o;
+    }
+    if (degree >= 1) {
+#pragma unroll
+        for (int o = 1; o < 4; o <<= 1) {
+            vx += __shfl_xor_sync(gmask, vx, o); vy += __shfl_xor_sync(gmask, vy, o); vz += __shfl_xor_sync(gmask, vz, o);
+        }
+        if (j == 0) {
+            const float dot = vx * x + vy * y + vz * z;
+            v_means[3 * g] += (vx - dot * x) * inorm;
+            v_means[3 * g + 1] += (vy - dot * y) * inorm;
+            v_means[3 * g + 2] += (vz - dot * z) * inorm;
+        }
+    }
+}
+
 CLMGS_EXPORT int clmgs_sh_colors_bwd(int64_t N, int K, int degree, const float *means, const float *campos,
                                      const float *coeffs, const float *v_colors, float *v_coeffs, float *v_means,
                                      void *stream) {
     CLMGS_REQUIRE(degree >= 0 && degree <= 4, "sh_colors_bwd: degree %d not in [0,4]", degree);
     CLMGS_REQUIRE(K >= (degree + 1) * (degree + 1) && K <= 25, "sh_colors_bwd: K=%d too small for degree %d (or > 25)", K, degree);
     if (N == 0) return CLMGS_OK;
+    if (K == 16 && degree <= 3 && ((((uintptr_t)coeffs) | ((uintptr_t)v_coeffs)) & 15) == 0) {
+        sh_colors_bwd_lanes_kernel<<<(unsigned)ceil_div64(N * 4, 256), 256, 0, as_stream(stream)>>>(
+            N, degree, means, campos, reinterpret_cast<const float4 *>(coeffs), v_colors,
+            reinterpret_cast<float4 *>(v_coeffs), v_means);
+        CLMGS_LAUNCH_OK();
+        return CLMGS_OK;
+    }
     size_t smem = (size_t)kShRows * ((K * 3) | 1) * sizeof(float);
     sh_bwd_kernel<true><<<(unsigned)ceil_div64(N, kShRows), kShRows, smem, as_stream(stream)>>>(
         N, K, degree, means, campos, coeffs, nullptr, v_colors, v_coeffs, 1, v_means);

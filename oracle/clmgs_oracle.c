@@ -277,10 +277,11 @@ ORC_API void orc_projection_bwd(int C, int64_t N, const float *means, const floa
                                 const float *conics, const float *v_means2d,
                                 const float *v_depths, const float *v_conics, float *v_means,
                                 float *v_quats, float *v_scales) {
-    for (int64_t idx = 0; idx < (int64_t)C * N; ++idx) {
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < N; ++i)
+    for (int c = 0; c < C; ++c) {
+        int64_t idx = (int64_t)c * N + i;
         if (radii[idx] <= 0) continue;
-        int c = (int)(idx / N);
-        int64_t i = idx % N;
         const float *vm = viewmats + 16 * c, *K = Ks + 9 * c;
         const float *mean = means + 3 * i, *quat = quats + 4 * i, *scale = scales + 3 * i;
         float R[3][3], t[3];
@@ -697,6 +698,8 @@ ORC_API void orc_rasterize_bwd(int C, int64_t N, int64_t n_isects, const float *
                                float *v_opacities) {
     int64_t CN = (int64_t)C * N;
     double *acc = (double *)calloc((size_t)CN * 11, sizeof(double));
+#define ACC(p, v) do { _Pragma("omp atomic") (p) += (v); } while (0)
+#pragma omp parallel for schedule(dynamic, 64)
     for (int64_t pix = 0; pix < (int64_t)C * H * W; ++pix) {
         int cam = (int)(pix / ((int64_t)H * W));
         int64_t p = pix % ((int64_t)H * W);
@@ -728,7 +731,7 @@ ORC_API void orc_rasterize_bwd(int C, int64_t N, int64_t n_isects, const float *
             double *a = acc + (int64_t)g * 11;
             float v_alpha = 0.f;
             for (int k = 0; k < 3; ++k) {
-                a[5 + k] += (double)(fac * vrc[k]);
+                ACC(a[5 + k], (double)(fac * vrc[k]));
                 v_alpha += (colors[3 * g + k] * T - buffer[k] * ra) * vrc[k];
             }
             v_alpha += T_final * ra * vra;
@@ -739,13 +742,13 @@ ORC_API void orc_rasterize_bwd(int C, int64_t N, int64_t n_isects, const float *
             }
             if (opac * vis <= 0.999f) {
                 float v_sigma = -opac * vis * v_alpha;
-                a[2] += (double)(0.5f * v_sigma * dx * dx);
-                a[3] += (double)(v_sigma * dx * dy);
-                a[4] += (double)(0.5f * v_sigma * dy * dy);
+                ACC(a[2], (double)(0.5f * v_sigma * dx * dx));
+                ACC(a[3], (double)(v_sigma * dx * dy));
+                ACC(a[4], (double)(0.5f * v_sigma * dy * dy));
                 float gx = v_sigma * (ca * dx + cb * dy), gy = v_sigma * (cb * dx + cc * dy);
-                a[0] += (double)gx; a[1] += (double)gy;
-                a[9] += (double)fabsf(gx); a[10] += (double)fabsf(gy);
-                a[8] += (double)(vis * v_alpha);
+                ACC(a[0], (double)gx); ACC(a[1], (double)gy);
+                ACC(a[9], (double)fabsf(gx)); ACC(a[10], (double)fabsf(gy));
+                ACC(a[8], (double)(vis * v_alpha));
             }
             for (int k = 0; k < 3; ++k) buffer[k] += colors[3 * g + k] * fac;
         }

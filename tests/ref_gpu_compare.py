@@ -176,10 +176,12 @@ def main():
     mp, gr = ref_loss()
     lv, vg = ops.loss_fwd_bwd(o_rc[0], gt_u8, 0.2, hwc=True)
     ref_total = 0.8 * (img - gt).abs().mean() + 0.2 * (1 - mp.mean())
-    ref_grad = 0.8 * torch.sign(img - gt) / img.numel() - 0.2 * gr[0]
-    out["loss"] = dict(abs_loss_diff=float((ref_total - lv[0]).abs()), rel_grad=rel(vg.permute(2, 0, 1), ref_grad),
+    s_our, g_our = ops.fused_ssim_fwd_bwd(img[None].contiguous(), gt[None].contiguous())
+    out["loss"] = dict(abs_loss_diff=float((ref_total - lv[0]).abs()), abs_ssim_diff=float((mp.mean() - s_our).abs()),
+                       rel_ssim_grad=rel(g_our, gr),
                        ref_ms=timeit(lambda: ref_loss()), ours_ms=timeit(lambda: ops.loss_fwd_bwd(o_rc[0], gt_u8, 0.2, hwc=True)),
-                       note="ref time = fusedssim + fusedssim_backward only (its L1 is a separate torch.compile kernel)")
+                       note="ref time = fusedssim + fusedssim_backward only (its L1 is a separate torch.compile kernel); "
+                            "ours = SSIM + L1 forward and backward")
 
     # ---- SH row gather from pinned host: reference 4-byte kernel (grid 32) vs ours ------------------------------------------------
     h = torch.from_numpy(g["sh"]).pin_memory()

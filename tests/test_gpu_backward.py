@@ -323,3 +323,31 @@ def test_gpu_adam_kernels():
         tp, tm, tv = _t(p), _t(m), _t(v)
         ops.adam_dense(tp, _t(g), tm, tv, 1e-2, 0.9, 0.999, 1e-15, 3, grad_scale=0.25)
         np.testing.assert_allclose(tp.cpu().numpy(), pr, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("deg", [0, 1, 2, 3])
+def test_engine_fused_sh_colors_fwd_bwd(deg):
+    """clmgs_sh_colors_fwd/_bwd (dirs = means - campos, clamp_min(c + 0.5, 0), += into retained grads,
+    v_means += v_dirs) vs the oracle composed the way engine.py:67-78,709-716 composes it."""
+    rng = np.random.default_rng(10 + deg)
+    n = 50_003
+    means = rng.standard_normal((n, 3)).astype(np.float32) * 2
+    campos = np.array([0.3, -4.0, 0.5], np.float32)
+    coeffs = (rng.standard_normal((n, 16, 3)) * 0.4).astype(np.float32)
+    v_colors = rng.standard_normal((n, 3)).astype(np.float32)
+    base_g = rng.standard_normal((n, 48)).astype(np.float32)
+    base_m = rng.standard_normal((n, 3)).astype(np.float32)
+    dirs = means - campos[None]
+    raw = oracle.sh_fwd(deg, dirs, coeffs)
+    col_ref = np.maximum(raw + np.float32(0.5), 0)
+    col = ops.sh_colors_fwd(deg, _t(means), _t(campos), _t(coeffs.reshape(n, 48))).cpu().numpy()
+    np.testing.assert_allclose(col, col_ref, rtol=1e-5, atol=1e-5)
+    # keep away from the clamp edge, where a 1-ulp colour difference legitimately flips the mask
+    safe = (np.abs(raw + 0.5) > 1e-4).all(1)
+    vmask = v_colors * (raw + np.float32(0.5) >= 0)
+    g_ref = base_g.reshape(n, 16, 3).copy()
+    vd_ref = oracle.sh_bwd_inplace(deg, dirs, coeffs, g_ref, vmask)
+    g, vm = _t(base_g), _t(base_m)
+    ops.sh_colors_bwd(deg, _t(means), _t(campos), _t(coeffs.reshape(n, 48)), _t(v_colors), g, vm)
+    np.testing.assert_allclose(g.cpu().numpy()[safe], g_ref.reshape(n, 48)[safe], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(vm.cpu().numpy()[safe], (base_m + vd_ref)[safe], rtol=1e-3, atol=1e-4)

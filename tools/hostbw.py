@@ -1,6 +1,6 @@
 """Debug helper: host DRAM bandwidth on the GPU box (STREAM-like, torch CPU threads) and host Adam alone."""
 import os, sys, time
-ROOT = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "clm-gs_b200")]
 import numpy as np, torch
 from clmgs import ops

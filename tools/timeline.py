@@ -1,6 +1,6 @@
 """Debug helper: print the device timeline of one C2 training iteration (not part of the product)."""
 import os, sys, time
-ROOT = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "clm-gs_b200")]
 import numpy as np, torch
 from clmgs import engine, model, scene as S
