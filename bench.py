@@ -398,7 +398,7 @@ def main():
     ap.add_argument("--cpu-threads", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
-    ap.add_argument("--cpu-sample-gaussians", type=int, default=100_000)
+    ap.add_argument("--cpu-sample-gaussians", type=int, default=1_000_000)
     a = ap.parse_args()
     a.warmup = max(a.warmup, 0)
     out = run_reference(a) if a.impl == "reference" else run_ours(a)
