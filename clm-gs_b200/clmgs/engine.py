@@ -365,7 +365,11 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
 
             # -- 4.4 / 4.5: backward ----------------------------------------------------------------
             compute.wait_event(grad_ready)
-            backward_one_camera(gaussians, cam, ids, shs, shs_grad, fw, v_render[None], grads, timer)
+            v_means2d = backward_one_camera(gaussians, cam, ids, shs, shs_grad, fw, v_render[None], grads, timer)
+            if args.densification_stats:  # engine.py:833-844
+                with timer("densification_stats"):
+                    ops.densification_stats(ids, v_means2d[0], fw["radii"][0], cam.image_width, cam.image_height,
+                                            gaussians.max_radii2D, gaussians.xyz_gradient_accum, gaussians.denom)
             bwd_done = torch.cuda.Event()
             bwd_done.record(compute)
 

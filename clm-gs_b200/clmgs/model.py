@@ -43,6 +43,7 @@ class TrainArgs:
     rotation_lr: float = 0.001
     lambda_dssim: float = 0.2
     spatial_lr_scale: float = 1.0
+    densification_stats: bool = False  # accumulate max_radii2D / xyz_gradient_accum / denom per camera (A17)
     cpu_adam_threads: int = 0  # 0 = all hardware threads
     final_flush_chunks: int = 8  # last camera: flush + host Adam pipelined in this many pieces
     rows_lookahead: int = 2  # SH-row prefetches issued this many cameras ahead on the copy stream
@@ -172,6 +173,10 @@ class GaussianModelCLMOffload:
     # -- optimiser (GM:122-234) --------------------------------------------------------
     def training_setup(self, args: TrainArgs):
         self.args = args
+        # densification statistics (GM:122-127, base_gaussian_model max_radii2D)
+        self.max_radii2D = torch.zeros(self.n_gaussians, device=self.device)
+        self.xyz_gradient_accum = torch.zeros(self.n_gaussians, 1, device=self.device)
+        self.denom = torch.zeros(self.n_gaussians, 1, device=self.device)
         bsz = args.bsz
         groups = [
             _Group(name="xyz", params=[self._xyz], lr=args.position_lr_init * args.spatial_lr_scale),

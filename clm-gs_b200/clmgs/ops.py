@@ -111,6 +111,11 @@ def activate_bwd_scatter(log_scale, raw_quat, opacity_logit, ids, v_means, v_sca
          g_raw_quat, g_opacity_logit, _st())
 
 
+def densification_stats(ids, v_means2d, radii, width, height, max_radii2d, xyz_gradient_accum, denom):
+    call("clmgs_densification_stats", ids, ids.shape[0], _f32c(v_means2d), radii.contiguous(), int(width), int(height),
+         max_radii2d, xyz_gradient_accum, denom, _st())
+
+
 # --------------------------------------------------------------------------- S3
 def projection_fwd(means, quats, scales, viewmats, Ks, width, height, eps2d=0.3, near_plane=0.01,
                    far_plane=1e10, radius_clip=0.0, calc_compensations=False):

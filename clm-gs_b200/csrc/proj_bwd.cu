@@ -213,7 +213,32 @@ activate_bwd_scatter_kernel(const float *__restrict__ log_scale, const float *__
     g_o[g] += v_opac[r] * o * (1.0f - o);
 }
 
+// A17 densification statistics (densification.py:59-102 -> gaussian_model.py:833-851): one thread per
+// visible Gaussian; ids are unique within a camera, so plain read-modify-write.
+__global__ void __launch_bounds__(256)
+densification_stats_kernel(const int64_t *__restrict__ ids, int64_t n, const float *__restrict__ v_means2d,
+                           const int32_t *__restrict__ radii, float half_w, float half_h,
+                           float *__restrict__ max_radii2d, float *__restrict__ grad_accum, float *__restrict__ denom) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n) return;
+    const int64_t g = ids[r];
+    max_radii2d[g] = fmaxf(max_radii2d[g], (float)radii[r]);
+    const float gx = v_means2d[2 * r] * half_w, gy = v_means2d[2 * r + 1] * half_h;
+    grad_accum[g] += sqrtf(gx * gx + gy * gy);
+    denom[g] += 1.0f;
+}
+
 }  // namespace
+
+CLMGS_EXPORT int clmgs_densification_stats(const int64_t *ids, int64_t n, const float *v_means2d,
+                                           const int32_t *radii, int width, int height, float *max_radii2d,
+                                           float *xyz_gradient_accum, float *denom, void *stream) {
+    if (n == 0) return CLMGS_OK;
+    densification_stats_kernel<<<(unsigned)ceil_div64(n, 256), 256, 0, as_stream(stream)>>>(
+        ids, n, v_means2d, radii, 0.5f * (float)width, 0.5f * (float)height, max_radii2d, xyz_gradient_accum, denom);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
 
 CLMGS_EXPORT int clmgs_projection_bwd(int C, int64_t N, const float *means, const float *quats,
                                       const float *scales, const float *viewmats, const float *Ks, int width,

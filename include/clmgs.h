@@ -94,6 +94,16 @@ int clmgs_activate_bwd_scatter(const float *log_scale, const float *raw_quat,
                                const float *v_opacities, float *g_xyz, float *g_log_scale,
                                float *g_raw_quat, float *g_opacity_logit, void *stream);
 
+/* A17  Densification statistics of one camera ("next" row of SURVEY.md 8f;
+ * update_densification_stats_offload_accum_grads, densification.py:59-102 ->
+ * gsplat_add_densification_stats_exact_filter, strategies/clm_offload/gaussian_model.py:833-851):
+ * max_radii2D[id] = max(., radii), xyz_gradient_accum[id] += |v_means2d * (W/2, H/2)|, denom[id] += 1
+ * for every filtered Gaussian (ids unique). v_means2d [n,2], radii [n] i32; the three [N] float
+ * tables are updated in place. */
+int clmgs_densification_stats(const int64_t *ids, int64_t n, const float *v_means2d,
+                              const int32_t *radii, int width, int height, float *max_radii2d,
+                              float *xyz_gradient_accum, float *denom, void *stream);
+
 /* ---------------------------------------------------------------------------
  * S3  Dense projection.  fully_fused_projection_fwd_tensor / _bwd_tensor
  * (CSRC/fully_fused_projection_fwd.cu:132-181, CSRC/fully_fused_projection_bwd.cu:188-283).

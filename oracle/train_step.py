@@ -95,8 +95,15 @@ def train_one_batch(st, viewmats, Ks, camposs, gts_u8, W, H, args, ordered_cams,
         img_chw = np.ascontiguousarray(fw["rc"][0].transpose(2, 0, 1))
         loss, v_chw, _, _ = O.loss_fwd_bwd(img_chw, gts_u8[c], args.lambda_dssim)
         losses.append(loss)
-        backward_camera(st, ids, fw, viewmats[c], Ks[c], W, H, args.sh_degree,
-                        np.ascontiguousarray(v_chw.transpose(1, 2, 0)), grads, sh_grad)
+        vm2 = backward_camera(st, ids, fw, viewmats[c], Ks[c], W, H, args.sh_degree,
+                              np.ascontiguousarray(v_chw.transpose(1, 2, 0)), grads, sh_grad)
+        if getattr(args, "densification_stats", False):  # gaussian_model.py:833-851
+            for key in ("max_radii2D", "xyz_gradient_accum", "denom"):
+                st.setdefault(key, np.zeros(N, np.float32))
+            st["max_radii2D"][ids] = np.maximum(st["max_radii2D"][ids], fw["radii"][0].astype(np.float32))
+            gg = vm2[0] * np.array([W * 0.5, H * 0.5], np.float32)
+            st["xyz_gradient_accum"][ids] += np.sqrt((gg * gg).sum(1))
+            st["denom"][ids] += 1
         stats.append(dict(n_visible=len(ids), n_isects=fw["n_isects"], examined=fw["examined"]))
     touched = mask[list(ordered_cams)].any(0)
     # GPU-resident attributes (engine.py:870-882)

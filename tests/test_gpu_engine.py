@@ -17,7 +17,7 @@ def _setup(n, W, H, bsz, sparse, shape="object"):
     g = S.make_gaussians(spec)
     V, K, P = S.make_cameras(spec, bsz, g["extent"])
     gts = S.make_gt_images(spec, bsz)
-    args = model.TrainArgs(bsz=bsz, sparse_adam=sparse, cpu_adam_threads=4)
+    args = model.TrainArgs(bsz=bsz, sparse_adam=sparse, cpu_adam_threads=4, densification_stats=True)
     gm = model.GaussianModelCLMOffload(3, DEV).create_from_arrays(g["xyz"], g["log_scale"], g["raw_quat"],
                                                                  g["opacity_logit"], g["sh"])
     gm.training_setup(args)
@@ -51,6 +51,10 @@ def test_train_one_batch_matches_oracle(bsz, sparse, shape):
         np.testing.assert_allclose(sparsity, [len(f) / 20_000 for f in ref_filters])
         got_losses = [float(l) for l in losses]
         np.testing.assert_allclose(got_losses, ref_losses, rtol=2e-5, atol=2e-6)
+        # densification statistics (A17): exact counters, gradient norms at 1e-3
+        np.testing.assert_array_equal(gm.denom.cpu().numpy()[:, 0], st["denom"])
+        np.testing.assert_array_equal(gm.max_radii2D.cpu().numpy(), st["max_radii2D"])
+        _close(gm.xyz_gradient_accum.cpu().numpy()[:, 0], st["xyz_gradient_accum"], 1e-3, (it, "xyz_gradient_accum"))
         # the host gradient table must be left zeroed (cpu-adam "version 3", engine.py:316)
         assert not gm.parameters_grad_buffer.numpy().any()
         # Gradients: Adam's first moment is linear in the accumulated gradient -> north_star's
