@@ -97,7 +97,9 @@ LAUNCHES = dict(clmgs_cull_count=2, clmgs_cull_emit=1, clmgs_gather_activate=1, 
                 clmgs_sh_colors_bwd=1, clmgs_activate_bwd_scatter=1, clmgs_rows_gather_i64=1,
                 clmgs_rows_prefetch_next=2, clmgs_rows_grad_handoff=2, clmgs_set_signal=1,
                 clmgs_bitmap_distance=2, clmgs_bitmap_permute=1, clmgs_extract_ffs=1, clmgs_group_by_ffs=3,
-                clmgs_selective_adam=1, clmgs_adam_dense=1)
+                clmgs_selective_adam=1, clmgs_adam_dense=1, clmgs_extract_first_use=1, clmgs_slot_map=1,
+                clmgs_rows_gather_i32=1, clmgs_rows_flush_slots=1, clmgs_sh_colors_fwd_slots=1,
+                clmgs_sh_colors_bwd_slots=1, clmgs_densification_stats=1, clmgs_rows_accumulate=1)
 
 
 def count_launches(lib):
@@ -300,6 +302,7 @@ def run_ours(a):
                                l2="inputs larger than L2 (Gaussian tables %.0f MB >> 126 MB); no explicit flush" % (N * 44 / 1e6),
                                sparse_adam=bool(a.sparse_adam), cpu_adam_threads=a.cpu_threads or os.cpu_count(),
                                visible_per_camera=stats["n_visible"], isects_per_camera=stats["n_isects"],
+                               touched_rows_per_step=stats.get("n_union", stats.get("n_need")),
                                setup_s=round(setup_s, 1)),
                    e2e=dict(value=round(world * 1000.0 / ms_e2e, 4), unit=UNIT, h2d_bytes_per_step=h2d,
                             d2h_bytes_per_step=d2h, ms_per_step=round(ms_e2e, 3)),

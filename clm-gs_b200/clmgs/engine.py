@@ -11,7 +11,8 @@ table left zeroed).  What changed underneath:
                                                        cameras, bitmap + ballot compaction
   bsz scatter_to_bit + randperm + (B,B,n) XOR tensor   bitmap comes from the cull; sampled distance kernel
   torch.sort(N bytes) + unique_consecutive + split      counting sort by last-use key (group_by_ffs)
-  ~8 torch ops + 2 nonzero_static per camera            clmgs_rows_prefetch_next / _grad_handoff (no lists)
+  ~8 torch ops + 2 nonzero_static per camera,           batch-resident SH rows: one device row ("slot") per touched
+  retained rows re-packed for every camera              Gaussian, loaded at first use, flushed after last use
   4 gathers + 3 activations + autograd                  clmgs_gather_activate / clmgs_activate_bwd_scatter
   autograd graph per camera                             explicit forward + backward kernel calls
   fused_ssim + torch.compile'd L1                       clmgs_loss_fwd_bwd (writes v_render_colors directly)
@@ -132,14 +133,25 @@ def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, tim
         rows_dev, counts = ops.group_by_ffs(ffs, bsz)
         rows_host = _pinned_rows_buffer(n_gaussians)
         rows_host.copy_(rows_dev, non_blocking=True)
+        # batch-resident rows: Gaussians grouped by the first camera that needs them; a Gaussian's slot in the
+        # device row table is its position in that grouping (so each first-use group is a contiguous slot range)
+        first = ops.extract_first_use(ordered_bitmap, bsz)
+        first_rows_dev, first_counts = ops.group_by_ffs(first, bsz)
         counts_h = counts.cpu().numpy()  # sync: also completes the rows copy above (same stream)
+        first_counts_h = first_counts.cpu().numpy()
+        n_untouched = int(first_counts_h[0])
+        union_ids = first_rows_dev[n_untouched:]
+        slot_of = torch.empty(n_gaussians, dtype=torch.int32, device=dev)
+        ops.slot_map(union_ids, slot_of)
     offs = np.concatenate([[0], np.cumsum(counts_h)]).astype(np.int64)
     # group m of the host Adam = rows whose last user is camera m-1 <-> ffs key bsz+1-m (engine.py:213)
     keys = [0] + [bsz + 1 - m for m in range(1, bsz + 1)]
     row_begin = np.ascontiguousarray(offs[keys], dtype=np.int64)
     row_end = np.ascontiguousarray(offs[[k + 1 for k in keys]], dtype=np.int64)
+    first_edges = np.concatenate([[0], np.cumsum(first_counts_h[1:])]).astype(np.int64)  # slots of first-use group k
     return dict(ordered_cams=ordered_cams, filters=filters, sparsity=sparsity, ordered_bitmap=ordered_bitmap,
-                visibility=ffs, rows_host=rows_host, row_begin=row_begin, row_end=row_end)
+                visibility=ffs, rows_host=rows_host, rows_dev=rows_dev, row_begin=row_begin, row_end=row_end,
+                union_ids=union_ids, slot_of=slot_of, first_edges=first_edges)
 
 
 def geometry_one_camera(gaussians, camera, ids, timer=_NULL_TIMER):
@@ -162,13 +174,19 @@ def geometry_one_camera(gaussians, camera, ids, timer=_NULL_TIMER):
                 offsets=offsets, flatten_ids=flatten_ids, n_isects=flatten_ids.shape[0])
 
 
-def shade_one_camera(gaussians, camera, fw, shs, background, timer=_NULL_TIMER, rows_ready=None):
-    """SH colour + rasterisation (engine.py:67-78,106-119); needs the SH rows."""
+def shade_one_camera(gaussians, camera, fw, shs, background, timer=_NULL_TIMER, rows_ready=None, ids=None,
+                     slot_of=None):
+    """SH colour + rasterisation (engine.py:67-78,106-119); needs the SH rows.  With `slot_of`, `shs` is
+    the batch-resident row table and row g is slot_of[ids[g]]."""
     W, H = camera.image_width, camera.image_height
     if rows_ready is not None:  # the SH rows arrive on the copy stream
         torch.cuda.current_stream().wait_event(rows_ready)
     with timer("sh_fwd"):
-        fw["colors"] = ops.sh_colors_fwd(gaussians.active_sh_degree, fw["means"], camera.campos, shs)
+        if slot_of is not None:
+            fw["colors"] = ops.sh_colors_fwd_slots(gaussians.active_sh_degree, fw["means"], camera.campos, shs, ids,
+                                                   slot_of)
+        else:
+            fw["colors"] = ops.sh_colors_fwd(gaussians.active_sh_degree, fw["means"], camera.campos, shs)
     fw["bg"] = None if background is None else background.reshape(1, 3)
     with timer("raster_fwd"):
         fw["render"], fw["alphas"], fw["last"] = ops.rasterize_fwd(
@@ -184,7 +202,7 @@ def forward_one_camera(gaussians, camera, ids, shs, background, timer=_NULL_TIME
     return shade_one_camera(gaussians, camera, fw, shs, background, timer, rows_ready)
 
 
-def backward_one_camera(gaussians, camera, ids, shs, shs_grad, fw, v_render, grads, timer=_NULL_TIMER):
+def backward_one_camera(gaussians, camera, ids, shs, shs_grad, fw, v_render, grads, timer=_NULL_TIMER, slot_of=None):
     """loss.backward() + spherical_harmonics_bwd_inplace + scatter_add_ (engine.py:703-742)."""
     W, H = camera.image_width, camera.image_height
     with timer("raster_bwd"):
@@ -196,7 +214,12 @@ def backward_one_camera(gaussians, camera, ids, shs, shs_grad, fw, v_render, gra
                                                         camera.K[None], W, H, 0.3, fw["radii"], fw["conics"],
                                                         v_means2d, None, v_conics)
     with timer("sh_bwd"):
-        ops.sh_colors_bwd(gaussians.active_sh_degree, fw["means"], camera.campos, shs, v_colors[0], shs_grad, v_means)
+        if slot_of is not None:
+            ops.sh_colors_bwd_slots(gaussians.active_sh_degree, fw["means"], camera.campos, shs, v_colors[0], shs_grad,
+                                    ids, slot_of, v_means)
+        else:
+            ops.sh_colors_bwd(gaussians.active_sh_degree, fw["means"], camera.campos, shs, v_colors[0], shs_grad,
+                              v_means)
     with timer("activate_bwd_scatter"):
         ops.activate_bwd_scatter(gaussians._scaling, gaussians._rotation, gaussians._opacity, ids, v_means, v_scales,
                                  v_quats, v_opac[0], grads["xyz"], grads["scaling"], grads["rotation"],
@@ -306,66 +329,44 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
     geoms = [None] * bsz
 
     with torch.no_grad():
-        # SH-row pipeline on the copy stream: rows[j] = buffer of camera j, src_maps[j] = where each row of
-        # camera j+1 sits in rows[j] (-1: came from host).  Parameter rows never change inside a batch, so
-        # prefetches run `rows_lookahead` cameras ahead of the compute stream and never wait for it.
-        rows = [None] * bsz
-        rows_evt = [None] * bsz
-        src_maps = [None] * bsz
-        rows_lookahead = max(1, int(getattr(args, "rows_lookahead", 2)))
-        issued = 0  # prefetches issued so far: rows[0..issued] exist
-
-        def issue_rows(upto):
-            nonlocal issued
-            with torch.cuda.stream(comm_stream):
-                if rows_evt[0] is None:
-                    rows[0] = ops._empty((filters[0].shape[0], 48), torch.float32, dev)
-                    with timer("rows_load_first", comm_stream):
-                        ops.rows_gather(rows[0], h_params, filters[0])
-                    rows_evt[0] = torch.cuda.Event()
-                    rows_evt[0].record(comm_stream)
-                    rows[0].record_stream(compute)
-                while issued < min(upto, bsz - 1):
-                    j = issued
-                    rows[j + 1] = ops._empty((filters[j + 1].shape[0], 48), torch.float32, dev)
-                    with timer("rows_prefetch", comm_stream):
-                        src_maps[j] = ops.rows_prefetch_next(rows[j + 1], h_params, rows[j], filters[j],
-                                                             filters[j + 1], bitmap, bsz - 1 - j)
-                    rows_evt[j + 1] = torch.cuda.Event()
-                    rows_evt[j + 1].record(comm_stream)
-                    rows[j + 1].record_stream(compute)
-                    src_maps[j].record_stream(flush_stream)
-                    issued += 1
-
-        with torch.cuda.stream(flush_stream):
-            shs_grad = ops._zeros((filters[0].shape[0], 48), torch.float32, dev)
-            grad_ready = torch.cuda.Event()
-            grad_ready.record(flush_stream)
-            shs_grad.record_stream(compute)
+        # Batch-resident SH rows: one device row per touched Gaussian for the whole batch (slot_of).  The copy
+        # stream loads first-use group k (rows first needed by camera k) into its contiguous slot range, in order
+        # and ahead of the compute stream; the flush stream stores last-use group k to the pinned gradient table
+        # once camera k's backward is done.  Every row crosses PCIe once each way; no re-packing between cameras.
+        slot_of, union_ids, fe = oc["slot_of"], oc["union_ids"], oc["first_edges"]
+        n_union = int(fe[-1])
+        with torch.cuda.stream(comm_stream):
+            d_rows = ops._empty((n_union, 48), torch.float32, dev)
+            d_rows.record_stream(compute)
+            rows_evt = []
+            for k in range(bsz):
+                a0, a1 = int(fe[k]), int(fe[k + 1])
+                with timer("rows_load_first" if k == 0 else "rows_prefetch", comm_stream):
+                    ops.rows_gather_i32(d_rows[a0:a1], h_params, union_ids[a0:a1])
+                e = torch.cuda.Event()
+                e.record(comm_stream)
+                rows_evt.append(e)
+        d_grad = ops._zeros((n_union, 48), torch.float32, dev)   # compute stream; the flush stream waits on bwd events
+        d_grad.record_stream(flush_stream)
+        last_rows, rb, re_ = oc["rows_dev"], oc["row_begin"], oc["row_end"]
 
         for k in range(bsz):
             ids = filters[k]
-            # -- 4.1 / 4.2: SH rows of this camera and of the next ones (copy stream) -----------------
-            issue_rows(k + rows_lookahead)
-            shs = rows[k]
-
-            # -- 4.3: forward ---------------------------------------------------------------------
             cam = cams[k]
             # geometry of this and the next few cameras does not need SH rows: issue it before waiting on the
-            # copy stream so that it hides the host-link latency of the first load / the prefetches
+            # copy stream so that it hides the host-link latency of the first load
             for kk in range(k, min(bsz, k + 1 + lookahead)):
                 if geoms[kk] is None:
                     geoms[kk] = geometry_one_camera(gaussians, cams[kk], filters[kk], timer)
             fw, geoms[k] = geoms[k], None
-            fw = shade_one_camera(gaussians, cam, fw, shs, background, timer, rows_ready=rows_evt[k])
+            fw = shade_one_camera(gaussians, cam, fw, d_rows, background, timer, rows_ready=rows_evt[k], ids=ids,
+                                  slot_of=slot_of)
             with timer("loss"):
                 loss_vec, v_render = ops.loss_fwd_bwd(fw["render"][0], cam.original_image, args.lambda_dssim,
                                                       hwc=True)
             losses.append(loss_vec[0])
-
-            # -- 4.4 / 4.5: backward ----------------------------------------------------------------
-            compute.wait_event(grad_ready)
-            v_means2d = backward_one_camera(gaussians, cam, ids, shs, shs_grad, fw, v_render[None], grads, timer)
+            v_means2d = backward_one_camera(gaussians, cam, ids, d_rows, d_grad, fw, v_render[None], grads, timer,
+                                            slot_of=slot_of)
             if args.densification_stats:  # engine.py:833-844
                 with timer("densification_stats"):
                     ops.densification_stats(ids, v_means2d[0], fw["radii"][0], cam.image_width, cam.image_height,
@@ -373,40 +374,24 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
             bwd_done = torch.cuda.Event()
             bwd_done.record(compute)
 
-            # -- 4.6: gradient hand-off + signal (flush stream) ----------------------------------------
+            # gradients of the rows whose last user is this camera -> pinned table, then the flag (flush stream)
+            m = k + 1
+            g0, g1 = int(rb[m]), int(re_[m])
             with torch.cuda.stream(flush_stream):
                 flush_stream.wait_event(bwd_done)
-                if k < bsz - 1:
-                    flush_stream.wait_event(rows_evt[k + 1])  # src_maps[k] comes from the prefetch k -> k+1
-                    n_next = filters[k + 1].shape[0]
-                    shs_grad_next = ops._empty((n_next, 48), torch.float32, dev)
-                    shs_grad_next.record_stream(compute)
-                    with timer("grad_handoff", flush_stream):
-                        ops.rows_grad_handoff(shs_grad, shs_grad_next, h_grad, ids, n_next, src_maps[k], bitmap,
-                                              bsz - 1 - k, bsz - 1 - (k + 1), accum=2)
-                    grad_ready = torch.cuda.Event()
-                    grad_ready.record(flush_stream)
-                    ops.set_signal(signal, k, 1)
-                else:
-                    # last camera: everything goes to the host table, in pieces, each announced on its own
-                    # flag so the host Adam starts on piece j while piece j+1 is still crossing the link
-                    with timer("grad_handoff", flush_stream):
+                with timer("grad_handoff", flush_stream):
+                    if k < bsz - 1:
+                        ops.rows_flush_slots(d_grad, slot_of, last_rows[g0:g1], h_grad)
+                        ops.set_signal(signal, k, 1)
+                    else:
+                        # last camera: in pieces, each announced on its own flag, so the host Adam starts on piece j
+                        # while piece j+1 is still crossing the link
                         for j in range(len(chunk_edges) - 1):
-                            a, b = chunk_edges[j], chunk_edges[j + 1]
-                            ops.rows_grad_handoff(shs_grad[a:b], None, h_grad, ids[a:b], 0, None, bitmap, bsz - 1 - k, 0,
-                                                  accum=2)
+                            c0, c1 = g0 + chunk_edges[j], g0 + chunk_edges[j + 1]
+                            ops.rows_flush_slots(d_grad, slot_of, last_rows[c0:c1], h_grad)
                             ops.set_signal(signal, bsz - 1 + j, 1)
             n_isects_log.append(fw["n_isects"])
-            # release this camera's buffers: every tensor that crosses streams carries record_stream marks, so the
-            # caching allocator recycles them only after the other stream's work is done (C4: 64 cameras x ~1.5 GB)
-            shs_grad.record_stream(flush_stream)
-            shs.record_stream(comm_stream)
             del fw, v_render, loss_vec
-            src_maps[k] = None
-            if k < bsz - 1:
-                shs_grad = shs_grad_next
-            if k >= 1:
-                rows[k - 1] = None  # last read by the prefetch k-1 -> k
 
         # ---- stage 5: GPU Adam (grads / bsz fused as grad_scale) ------------------------------------
         with timer("gpu_adam"):
@@ -425,7 +410,8 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
     torch.cuda.synchronize()
     if timer.enabled:
         timer.collect()
-    gaussians.last_batch_stats = dict(cpu_adam_trailing_ms=join_ms, n_visible=[f.shape[0] for f in filters],
+    gaussians.last_batch_stats = dict(cpu_adam_trailing_ms=join_ms, n_union=n_union,
+                                      n_visible=[f.shape[0] for f in filters],
                                       n_isects=n_isects_log)
     return losses, ordered_cams, sparsity
 

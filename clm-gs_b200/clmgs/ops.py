@@ -409,3 +409,34 @@ def tsp_tour(dist):
     tour = np.empty(n, np.int32)
     call("clmgs_tsp_tour", d, n, tour)
     return tour.tolist()
+
+
+# --------------------------------------------------------------------------- batch-resident rows (slots)
+def extract_first_use(bitmap, bsz):
+    out = torch.empty(bitmap.shape[0], dtype=torch.uint8, device=bitmap.device)
+    call("clmgs_extract_first_use", bitmap, bitmap.element_size(), int(bsz), out, bitmap.shape[0], _st())
+    return out
+
+
+def slot_map(ids32, slot_of):
+    call("clmgs_slot_map", ids32, ids32.shape[0], slot_of, _st())
+
+
+def rows_gather_i32(d_rows, h_rows, ids32):
+    call("clmgs_rows_gather_i32", d_rows, h_rows, ids32, ids32.shape[0], _st())
+
+
+def rows_flush_slots(d_grad_rows, slot_of, ids32, h_grad):
+    call("clmgs_rows_flush_slots", d_grad_rows, slot_of, ids32, ids32.shape[0], h_grad, _st())
+
+
+def sh_colors_fwd_slots(degree, means, campos, d_rows, ids, slot_of):
+    n = means.shape[0]
+    colors = _empty((n, 3), torch.float32, means.device)
+    call("clmgs_sh_colors_fwd_slots", n, int(degree), means, campos, d_rows, ids, slot_of, colors, _st())
+    return colors
+
+
+def sh_colors_bwd_slots(degree, means, campos, d_rows, v_colors, d_grad_rows, ids, slot_of, v_means):
+    call("clmgs_sh_colors_bwd_slots", means.shape[0], int(degree), means, campos, d_rows, _f32c(v_colors), d_grad_rows,
+         ids, slot_of, v_means, _st())

@@ -25,6 +25,16 @@ __global__ void extract_ffs_kernel(const W *__restrict__ bitmap, uint8_t *__rest
         out[i] = (uint8_t)__ffsll((long long)(uint64_t)bitmap[i]);
 }
 
+// first-use key of the ordered bitmap: 0 = untouched, f+1 = first seen by the camera at position f
+// (position k <-> bit bsz-1-k, so the first camera is the highest set bit)
+template <typename W>
+__global__ void first_use_kernel(const W *__restrict__ bitmap, int bsz, uint8_t *__restrict__ out, int64_t N) {
+    for (int64_t i = (int64_t)blockIdx.x * kT + threadIdx.x; i < N; i += (int64_t)gridDim.x * kT) {
+        const uint64_t w = (uint64_t)bitmap[i];
+        out[i] = w ? (uint8_t)(bsz - (64 - __clzll((long long)w)) + 1) : (uint8_t)0;
+    }
+}
+
 // cnt_d[k] = #{i : camera k and camera k+1 both see i}; ordered convention:
 // camera k <-> bit bsz-1-k.  Warp ballots, then one smem atomic per warp.
 template <typename W>
@@ -189,6 +199,15 @@ CLMGS_EXPORT int clmgs_scatter_to_bit(void *bitmap, int word_bytes, const int64_
 CLMGS_EXPORT int clmgs_extract_ffs(const void *bitmap, int word_bytes, uint8_t *out, int64_t N, void *stream) {
     if (N == 0) return CLMGS_OK;
     DISPATCH_W(word_bytes, (extract_ffs_kernel<W><<<grid_n(N), kT, 0, as_stream(stream)>>>((const W *)bitmap, out, N)));
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_extract_first_use(const void *bitmap, int word_bytes, int bsz, uint8_t *out, int64_t N,
+                                         void *stream) {
+    CLMGS_REQUIRE(bsz >= 1 && bsz <= 8 * word_bytes && bsz <= 64, "extract_first_use: bad bsz %d", bsz);
+    if (N == 0) return CLMGS_OK;
+    DISPATCH_W(word_bytes, (first_use_kernel<W><<<grid_n(N), kT, 0, as_stream(stream)>>>((const W *)bitmap, bsz, out, N)));
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }

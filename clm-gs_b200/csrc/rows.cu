@@ -106,6 +106,11 @@ inline void prefer_shared(K kernel) {
     cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
 }
 
+struct Map32Via {  // row = table[ids[r]] (slot lookup)
+    const int32_t *ids; const int32_t *table;
+    __device__ int64_t operator()(int64_t r) const { return table[ids[r]]; }
+};
+
 struct Identity { __device__ int64_t operator()(int64_t r) const { return r; } };
 struct Map64 { const int64_t *p; __device__ int64_t operator()(int64_t r) const { return p[r]; } };
 struct Map32 { const int32_t *p; __device__ int64_t operator()(int64_t r) const { return p[r]; } };
@@ -290,6 +295,8 @@ void set_carveouts() {
     prefer_shared(copy_rows_kernel<Identity, Map64>);
     prefer_shared(accum_rows_kernel<Identity, Map64>);
     prefer_shared(accum_rows_kernel<Map32, Map32>);
+    prefer_shared(copy_rows_kernel<Map32, Identity>);
+    prefer_shared(copy_rows_kernel<Map32Via, Map32>);
     prefer_shared(prefetch_host_kernel);
     prefer_shared(handoff_host_kernel);
 }
@@ -425,6 +432,48 @@ CLMGS_EXPORT int clmgs_rows_accumulate(float *d_dst_rows, const float *d_src_row
     int64_t cap = (int64_t)kNumSMs * 8;
     accumulate_rows_kernel<<<(unsigned)(blocks > cap ? cap : blocks), kThreads, 0, as_stream(stream)>>>(
         F4(d_dst_rows), CF4(d_src_rows), dst_index, n);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Batch-resident rows ("slots"): every Gaussian the batch touches owns one row of a device table for
+// the whole batch, so a row crosses the host link exactly once each way per batch and nothing is
+// copied between cameras (the reference re-packs the retained rows for every camera,
+// CK/clm_kernels.cu:71-126,206-268).
+// ---------------------------------------------------------------------------
+__global__ void slot_map_kernel(const int32_t *__restrict__ ids, int64_t n, int32_t *__restrict__ slot_of) {
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x)
+        slot_of[ids[p]] = (int32_t)p;
+}
+
+CLMGS_EXPORT int clmgs_slot_map(const int32_t *ids, int64_t n, int32_t *slot_of, void *stream) {
+    if (n == 0) return CLMGS_OK;
+    int64_t blocks = ceil_div64(n, 256);
+    int64_t cap = (int64_t)kNumSMs * 16;
+    slot_map_kernel<<<(unsigned)(blocks > cap ? cap : blocks), 256, 0, as_stream(stream)>>>(ids, n, slot_of);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_rows_gather_i32(float *d_rows, const float *h_rows, const int32_t *ids, int64_t n,
+                                       void *stream) {
+    set_carveouts();
+    if (n == 0) return CLMGS_OK;
+    if (int rc = check_align(d_rows, "d_rows")) return rc;
+    if (int rc = check_align(h_rows, "h_rows")) return rc;
+    copy_rows_kernel<<<grid_for(n), kThreads, 0, as_stream(stream)>>>(F4(d_rows), CF4(h_rows), n, Map32{ids}, Identity{});
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_rows_flush_slots(const float *d_grad_rows, const int32_t *slot_of, const int32_t *ids,
+                                        int64_t n, float *h_grad, void *stream) {
+    set_carveouts();
+    if (n == 0) return CLMGS_OK;
+    if (int rc = check_align(h_grad, "h_grad")) return rc;
+    copy_rows_kernel<<<grid_for(n, true), kThreads, 0, as_stream(stream)>>>(F4(h_grad), CF4(d_grad_rows), n,
+                                                                           Map32Via{ids, slot_of}, Map32{ids});
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }

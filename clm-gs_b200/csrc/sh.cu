@@ -347,7 +347,8 @@ CLMGS_EXPORT int clmgs_sh_bwd(int64_t N, int K, int degree, const float *dirs, c
 __global__ void __launch_bounds__(256)
 sh_colors_bwd_lanes_kernel(int64_t N, int degree, const float *__restrict__ means, const float *__restrict__ campos,
                            const float4 *__restrict__ coeffs, const float *__restrict__ v_colors,
-                           float4 *__restrict__ v_coeffs, float *__restrict__ v_means) {
+                           float4 *__restrict__ v_coeffs, float *__restrict__ v_means,
+                           const int64_t *__restrict__ ids, const int32_t *__restrict__ slot_of) {
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t g = tid >> 2;
     const int j = (int)(tid & 3);
@@ -365,7 +366,8 @@ sh_colors_bwd_lanes_kernel(int64_t N, int degree, const float *__restrict__ mean
     sh_visit(degree, x, y, z, [&](int k, float b, float bx, float by, float bz) {
         if ((k >> 2) == j) { mb[k & 3] = b; mx[k & 3] = bx; my[k & 3] = by; mz[k & 3] = bz; }
     });
-    const float4 *crow = coeffs + g * 12 + j * 3;
+    const int64_t row = slot_of ? (int64_t)slot_of[ids[g]] : g;  // batch-resident table: row = slot of the Gaussian
+    const float4 *crow = coeffs + row * 12 + j * 3;
     float cf[12];
 #pragma unroll
     for (int q = 0; q < 3; ++q) {
@@ -391,7 +393,7 @@ sh_colors_bwd_lanes_kernel(int64_t N, int degree, const float *__restrict__ mean
         vx += mx[t] * cv; vy += my[t] * cv; vz += mz[t] * cv;
         gf[3 * t] = mb[t] * vr; gf[3 * t + 1] = mb[t] * vg; gf[3 * t + 2] = mb[t] * vb;
     }
-    float4 *grow = v_coeffs + g * 12 + j * 3;
+    float4 *grow = v_coeffs + row * 12 + j * 3;
 #pragma unroll
     for (int q = 0; q < 3; ++q) {
         float4 o = grow[q];
@@ -421,13 +423,78 @@ CLMGS_EXPORT int clmgs_sh_colors_bwd(int64_t N, int K, int degree, const float *
     if (K == 16 && degree <= 3 && ((((uintptr_t)coeffs) | ((uintptr_t)v_coeffs)) & 15) == 0) {
         sh_colors_bwd_lanes_kernel<<<(unsigned)ceil_div64(N * 4, 256), 256, 0, as_stream(stream)>>>(
             N, degree, means, campos, reinterpret_cast<const float4 *>(coeffs), v_colors,
-            reinterpret_cast<float4 *>(v_coeffs), v_means);
+            reinterpret_cast<float4 *>(v_coeffs), v_means, nullptr, nullptr);
         CLMGS_LAUNCH_OK();
         return CLMGS_OK;
     }
     size_t smem = (size_t)kShRows * ((K * 3) | 1) * sizeof(float);
     sh_bwd_kernel<true><<<(unsigned)ceil_div64(N, kShRows), kShRows, smem, as_stream(stream)>>>(
         N, K, degree, means, campos, coeffs, nullptr, v_colors, v_coeffs, 1, v_means);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+// Forward in the same 4-lanes-per-Gaussian form (no shared memory), rows addressed through the
+// batch's slot table.
+__global__ void __launch_bounds__(256)
+sh_colors_fwd_lanes_kernel(int64_t N, int degree, const float *__restrict__ means, const float *__restrict__ campos,
+                           const float4 *__restrict__ coeffs, const int64_t *__restrict__ ids,
+                           const int32_t *__restrict__ slot_of, float *__restrict__ colors) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t g = tid >> 2;
+    const int j = (int)(tid & 3);
+    if (g >= N) return;
+    const unsigned gmask = 0xfu << ((threadIdx.x & 31) & ~3);
+    float x = 0.f, y = 0.f, z = 0.f;
+    if (degree >= 1) {
+        float dx = __ldg(means + 3 * g) - campos[0], dy = __ldg(means + 3 * g + 1) - campos[1],
+              dz = __ldg(means + 3 * g + 2) - campos[2];
+        const float inorm = rsqrtf(dx * dx + dy * dy + dz * dz);
+        x = dx * inorm; y = dy * inorm; z = dz * inorm;
+    }
+    float mb[4] = {0.f, 0.f, 0.f, 0.f};
+    sh_visit(degree, x, y, z, [&](int k, float b, float, float, float) {
+        if ((k >> 2) == j) mb[k & 3] = b;
+    });
+    const int64_t row = slot_of ? (int64_t)slot_of[ids[g]] : g;
+    const float4 *crow = coeffs + row * 12 + j * 3;
+    float cf[12];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        const float4 v = __ldg(crow + q);
+        cf[4 * q] = v.x; cf[4 * q + 1] = v.y; cf[4 * q + 2] = v.z; cf[4 * q + 3] = v.w;
+    }
+    float cr = 0.f, cg = 0.f, cb = 0.f;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { cr += mb[t] * cf[3 * t]; cg += mb[t] * cf[3 * t + 1]; cb += mb[t] * cf[3 * t + 2]; }
+#pragma unroll
+    for (int o = 1; o < 4; o <<= 1) {
+        cr += __shfl_xor_sync(gmask, cr, o); cg += __shfl_xor_sync(gmask, cg, o); cb += __shfl_xor_sync(gmask, cb, o);
+    }
+    if (j < 3) colors[3 * g + j] = fmaxf((j == 0 ? cr : (j == 1 ? cg : cb)) + 0.5f, 0.f);
+}
+
+CLMGS_EXPORT int clmgs_sh_colors_fwd_slots(int64_t N, int degree, const float *means, const float *campos,
+                                           const float *d_rows, const int64_t *ids, const int32_t *slot_of,
+                                           float *colors, void *stream) {
+    CLMGS_REQUIRE(degree >= 0 && degree <= 3, "sh_colors_fwd_slots: degree %d not in [0,3] (K = 16 rows)", degree);
+    CLMGS_REQUIRE((((uintptr_t)d_rows) & 15) == 0, "sh_colors_fwd_slots: rows must be 16-byte aligned");
+    if (N == 0) return CLMGS_OK;
+    sh_colors_fwd_lanes_kernel<<<(unsigned)ceil_div64(N * 4, 256), 256, 0, as_stream(stream)>>>(
+        N, degree, means, campos, reinterpret_cast<const float4 *>(d_rows), ids, slot_of, colors);
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_sh_colors_bwd_slots(int64_t N, int degree, const float *means, const float *campos,
+                                           const float *d_rows, const float *v_colors, float *d_grad_rows,
+                                           const int64_t *ids, const int32_t *slot_of, float *v_means, void *stream) {
+    CLMGS_REQUIRE(degree >= 0 && degree <= 3, "sh_colors_bwd_slots: degree %d not in [0,3] (K = 16 rows)", degree);
+    CLMGS_REQUIRE(((((uintptr_t)d_rows) | ((uintptr_t)d_grad_rows)) & 15) == 0, "sh_colors_bwd_slots: rows must be 16-byte aligned");
+    if (N == 0) return CLMGS_OK;
+    sh_colors_bwd_lanes_kernel<<<(unsigned)ceil_div64(N * 4, 256), 256, 0, as_stream(stream)>>>(
+        N, degree, means, campos, reinterpret_cast<const float4 *>(d_rows), v_colors,
+        reinterpret_cast<float4 *>(d_grad_rows), v_means, ids, slot_of);
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }

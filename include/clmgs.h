@@ -267,6 +267,32 @@ int clmgs_rows_scatter_grad_retention(const float *d_grad, float *h_grad, float 
                                       const int32_t *src_rows_to_next, int64_t n_host,
                                       int64_t n_next, int accum, void *stream);
 int clmgs_set_signal(int32_t *h_flags, int index, int value, void *stream);
+/* Batch-resident SH rows ("slots"; new design replacing the per-camera re-packing of retained rows,
+ * CK/clm_kernels.cu:71-126,206-268 + engine.py:519-641,767-803).  Every Gaussian the batch touches
+ * owns one row of a device table for the whole batch: rows are loaded when their first camera comes
+ * up and flushed after their last, so each row crosses the host link once each way per batch, with
+ * plain stores (no read-modify-write over PCIe) and no device-to-device copies between cameras.
+ *   clmgs_extract_first_use : key 0 = untouched, f+1 = first seen by the camera at position f of the
+ *                             ORDERED bitmap (counterpart of clmgs_extract_ffs, which gives the last use)
+ *   clmgs_slot_map          : slot_of[ids[p]] = p for the touched Gaussians grouped by first use
+ *   clmgs_rows_gather_i32   : clmgs_rows_gather_i64 with int32 ids (a first-use group -> its contiguous slots)
+ *   clmgs_rows_flush_slots  : h_grad[ids[r]] = d_grad_rows[slot_of[ids[r]]] (a last-use group, stored once)
+ *   clmgs_sh_colors_*_slots : the engine-fused SH colour stage reading / accumulating rows through
+ *                             slot_of[ids[g]] (K = 16, degree <= 3). */
+int clmgs_extract_first_use(const void *bitmap, int word_bytes, int bsz, uint8_t *out, int64_t N,
+                            void *stream);
+int clmgs_slot_map(const int32_t *ids, int64_t n, int32_t *slot_of, void *stream);
+int clmgs_rows_gather_i32(float *d_rows, const float *h_rows, const int32_t *ids, int64_t n,
+                          void *stream);
+int clmgs_rows_flush_slots(const float *d_grad_rows, const int32_t *slot_of, const int32_t *ids,
+                           int64_t n, float *h_grad, void *stream);
+int clmgs_sh_colors_fwd_slots(int64_t N, int degree, const float *means, const float *campos,
+                              const float *d_rows, const int64_t *ids, const int32_t *slot_of,
+                              float *colors, void *stream);
+int clmgs_sh_colors_bwd_slots(int64_t N, int degree, const float *means, const float *campos,
+                              const float *d_rows, const float *v_colors, float *d_grad_rows,
+                              const int64_t *ids, const int32_t *slot_of, float *v_means,
+                              void *stream);
 /* Multi-GPU owner-side sum (new design; the reference is single-GPU):
  * d_dst_rows[dst_index[r]] += d_src_rows[r] for 48-float rows in device memory;
  * indices may repeat (several ranks touched the same row). */
