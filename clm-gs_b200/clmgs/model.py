@@ -94,7 +94,9 @@ class CpuAdam:
         self.exp_avg = _pinned_zeros(param.shape)
         self.exp_avg_sq = _pinned_zeros(param.shape)
         self.step_count = 0
-        self.n_threads = n_threads
+        # default: all cores but one (the thread that launches kernels must not be time-sliced against
+        # 16 spinning workers)
+        self.n_threads = n_threads if n_threads > 0 else max(1, (os.cpu_count() or 2) - 1)
 
     def batched_sparse_step(self, grad, rows, seg_begin, seg_end, seg_signal, signal_tensor_pinned, scale):
         """engine.py:320-327.  Blocking; run it on a worker thread (ctypes drops the GIL)."""
