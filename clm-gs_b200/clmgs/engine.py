@@ -95,18 +95,33 @@ def calculate_filters(batched_cameras, gaussians, timer=_NULL_TIMER):
 _PINNED_ROWS = {}
 
 
-def _pinned_rows_buffer(n):
+def _pinned_rows_buffer(n, parity=0):
     """Pinned int32 [n] staging buffer for the host-Adam row lists, allocated once (cudaHostAlloc of
-    tens of MB costs milliseconds and was on the critical path of every batch)."""
-    buf = _PINNED_ROWS.get(n)
+    tens of MB costs milliseconds and was on the critical path of every batch).  Two of them, used
+    alternately: with pipeline_host_adam the previous batch's host Adam may still be reading its list."""
+    key = (n, parity)
+    buf = _PINNED_ROWS.get(key)
     if buf is None:
-        _PINNED_ROWS.clear()
+        for k in [k for k in _PINNED_ROWS if k[0] != n]:
+            del _PINNED_ROWS[k]
         buf = torch.empty(n, dtype=torch.int32).pin_memory()
-        _PINNED_ROWS[n] = buf
+        _PINNED_ROWS[key] = buf
     return buf
 
 
-def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, timer=_NULL_TIMER):
+def wait_host_adam(gaussians):
+    """Join a host Adam left running by a pipeline_host_adam call (no-op otherwise).  Call it before
+    reading the SH table or the host optimiser state."""
+    pend = getattr(gaussians, "_pending_adam", None)
+    if pend is not None:
+        pend["worker"].join()
+        gaussians._pending_adam = None
+        torch.cuda.synchronize()
+        if pend["err"]:
+            raise pend["err"][0]
+
+
+def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, timer=_NULL_TIMER, parity=0):
     """engine.py:135-298: camera order (TSP over sampled visibility distance), ordered bitmap,
     per-Gaussian last-use groups for the host Adam."""
     bitmap = cull["bitmap"]
@@ -131,7 +146,7 @@ def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, tim
         ordered_bitmap = ops.bitmap_permute(bitmap, bsz, ordered_cams)
         ffs = ops.extract_ffs(ordered_bitmap)
         rows_dev, counts = ops.group_by_ffs(ffs, bsz)
-        rows_host = _pinned_rows_buffer(n_gaussians)
+        rows_host = _pinned_rows_buffer(n_gaussians, parity)
         rows_host.copy_(rows_dev, non_blocking=True)
         # batch-resident rows: Gaussians grouped by the first camera that needs them; a Gaussian's slot in the
         # device row table is its position in that grouping (so each first-use group is a contiguous slot range)
@@ -239,10 +254,17 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     h_params = gaussians._parameters
     h_grad = parameters_grad_buffer[:N]
 
+    pipe = bool(getattr(args, "pipeline_host_adam", False))
+    prev = getattr(gaussians, "_pending_adam", None)
+    if prev is not None and not pipe:
+        wait_host_adam(gaussians)
+        prev = None
+    parity = gaussians._batch_parity = 1 - getattr(gaussians, "_batch_parity", 0)
+
     # ---- stage 1: visibility + order ------------------------------------------------------------
     with torch.no_grad():
         filters, cull = calculate_filters(batched_cameras, gaussians, timer)
-        oc = order_calculation(filters, cull, N, bsz, perm_generator, args, timer)
+        oc = order_calculation(filters, cull, N, bsz, perm_generator, args, timer, parity)
     ordered_cams, filters, sparsity = oc["ordered_cams"], oc["filters"], oc["sparsity"]
     cams = [batched_cameras[i] for i in ordered_cams]
     bitmap = oc["ordered_bitmap"]
@@ -252,11 +274,14 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     n_last = filters[-1].shape[0]
     J = max(1, min(int(getattr(args, "final_flush_chunks", 1)), max(1, n_last // 65536)))
     n_flags = bsz - 1 + J
-    if not hasattr(gaussians, "signal_tensor_pinned") or gaussians.signal_tensor_pinned.shape[0] != n_flags:
-        gaussians.signal_tensor_pinned = torch.zeros(n_flags, dtype=torch.int32).pin_memory()
+    ring = getattr(gaussians, "_signal_ring", None)
+    if ring is None:
+        ring = gaussians._signal_ring = [None, None]
+    if ring[parity] is None or ring[parity].shape[0] != n_flags:
+        ring[parity] = torch.zeros(n_flags, dtype=torch.int32).pin_memory()
     else:
-        gaussians.signal_tensor_pinned.zero_()
-    signal = gaussians.signal_tensor_pinned
+        ring[parity].zero_()  # its last user (two batches ago) has joined: the previous worker joined it
+    signal = gaussians.signal_tensor_pinned = ring[parity]
     cpu_adam = gaussians.optimizer.cpu_adam
     worker_err = []
 
@@ -276,11 +301,17 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
         seg_begin.append(int(rb[bsz]) + chunk_edges[j]); seg_end.append(int(rb[bsz]) + chunk_edges[j + 1])
         seg_signal.append(bsz - 1 + j)
 
+    progress = np.zeros(1, np.int64)
+    prev_worker = prev["worker"] if prev is not None else None
+
     def cpuadam_thread():
         import time as _t
+        if prev_worker is not None:
+            prev_worker.join()  # one host Adam at a time, in batch order
         t0 = _t.perf_counter()
         try:
-            cpu_adam.batched_sparse_step(h_grad, oc["rows_host"], seg_begin, seg_end, seg_signal, signal, 1.0 / bsz)
+            cpu_adam.batched_sparse_step(h_grad, oc["rows_host"], seg_begin, seg_end, seg_signal, signal, 1.0 / bsz,
+                                         progress)
         except Exception as e:  # surfaced after join
             worker_err.append(e)
         worker_times["cpu_adam_thread_ms"] = (_t.perf_counter() - t0) * 1e3
@@ -289,8 +320,15 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     worker.start()
     try:
         out = _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_grad, background, comm_stream,
-                             signal, timer, worker, worker_err, chunk_edges)
-        gaussians.last_batch_stats.update(worker_times)
+                             signal, timer, worker, worker_err, chunk_edges, prev, pipe)
+        if pipe:
+            # ids at the ends of the final-flush pieces: the next call loads rows up to hi[c] once piece c is updated
+            rows_host, g0 = oc["rows_host"], int(rb[bsz])
+            hi = [int(rows_host[g0 + chunk_edges[j + 1] - 1]) for j in range(J)]
+            gaussians._pending_adam = dict(worker=worker, progress=progress, chunk_hi=hi, n_seg=len(seg_begin), err=worker_err,
+                                           keep=[cull, oc, out])
+        else:
+            gaussians.last_batch_stats.update(worker_times)
         return out
     except BaseException:
         # never leave the host-Adam thread spinning on flags that will not come
@@ -300,8 +338,16 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
         raise
 
 
+def _wait_progress(pend, need):
+    """Spin (politely) until the previous batch's host Adam has finished `need` segments."""
+    import time as _t
+    prog, w = pend["progress"], pend["worker"]
+    while prog[0] < need and w.is_alive():
+        _t.sleep(5e-5)
+
+
 def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_grad, background, comm_stream, signal,
-                   timer, worker, worker_err, chunk_edges):
+                   timer, worker, worker_err, chunk_edges, prev=None, pipe=False):
     args = gaussians.args
     bsz = len(batched_cameras)
     N = gaussians.n_gaussians
@@ -338,17 +384,36 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
         with torch.cuda.stream(comm_stream):
             d_rows = ops._empty((n_union, 48), torch.float32, dev)
             d_rows.record_stream(compute)
+            union_ids.record_stream(comm_stream)
             rows_evt = []
             for k in range(bsz):
                 a0, a1 = int(fe[k]), int(fe[k + 1])
-                with timer("rows_load_first" if k == 0 else "rows_prefetch", comm_stream):
-                    ops.rows_gather_i32(d_rows[a0:a1], h_params, union_ids[a0:a1])
+                if k == 0 and prev is not None:
+                    # pipelined: the previous batch's host Adam is still updating rows.  It finishes its last group
+                    # in pieces of ascending ids; load our first group in matching id ranges, each as soon as the
+                    # piece covering it is done (everything before the last group is done by then as well).
+                    hi = torch.tensor(prev["chunk_hi"], dtype=union_ids.dtype, device=dev)
+                    cuts = torch.searchsorted(union_ids[a0:a1].contiguous(), hi, right=True).tolist()
+                    edges = [0] + cuts[:-1] + [a1 - a0]
+                    base = prev["n_seg"] - len(cuts)
+                    with timer("rows_load_first", comm_stream):
+                        for c in range(len(cuts)):
+                            _wait_progress(prev, prev["n_seg"] if c == len(cuts) - 1 else base + c + 1)
+                            if edges[c + 1] > edges[c]:
+                                ops.rows_gather_i32(d_rows[a0 + edges[c]:a0 + edges[c + 1]], h_params,
+                                                    union_ids[a0 + edges[c]:a0 + edges[c + 1]])
+                    prev["keep"] = None  # the previous batch is completely done: release its buffers
+                else:
+                    with timer("rows_load_first" if k == 0 else "rows_prefetch", comm_stream):
+                        ops.rows_gather_i32(d_rows[a0:a1], h_params, union_ids[a0:a1])
                 e = torch.cuda.Event()
                 e.record(comm_stream)
                 rows_evt.append(e)
         d_grad = ops._zeros((n_union, 48), torch.float32, dev)   # compute stream; the flush stream waits on bwd events
         d_grad.record_stream(flush_stream)
         last_rows, rb, re_ = oc["rows_dev"], oc["row_begin"], oc["row_end"]
+        last_rows.record_stream(flush_stream)
+        slot_of.record_stream(flush_stream)
 
         for k in range(bsz):
             ids = filters[k]
@@ -398,6 +463,12 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
             gaussians.optimizer.gpu_adam.step(grads, visibility=oc["visibility"] if args.sparse_adam else None,
                                               grad_scale=1.0 / bsz)
 
+    if pipe:
+        # return with the host Adam (and the tail of the GPU work) still running; the next call or
+        # wait_host_adam() picks it up.  Everything that crosses streams carries record_stream marks.
+        gaussians.last_batch_stats = dict(n_union=n_union, n_visible=[f.shape[0] for f in filters],
+                                          n_isects=n_isects_log)
+        return losses, ordered_cams, sparsity
     import time as _t
     comm_stream.synchronize()
     flush_stream.synchronize()

@@ -46,6 +46,7 @@ class TrainArgs:
     densification_stats: bool = False  # accumulate max_radii2D / xyz_gradient_accum / denom per camera (A17)
     cpu_adam_threads: int = 0  # 0 = all hardware threads
     final_flush_chunks: int = 8  # last camera: flush + host Adam pipelined in this many pieces
+    pipeline_host_adam: bool = False  # opt-in: return before the host Adam finished; the next call overlaps it
     rows_lookahead: int = 2  # SH-row prefetches issued this many cameras ahead on the copy stream
     geometry_lookahead: int = 3  # cameras whose projection/tile sort is issued ahead of their SH rows
 
@@ -98,12 +99,13 @@ class CpuAdam:
         # 16 spinning workers)
         self.n_threads = n_threads if n_threads > 0 else max(1, (os.cpu_count() or 2) - 1)
 
-    def batched_sparse_step(self, grad, rows, seg_begin, seg_end, seg_signal, signal_tensor_pinned, scale):
+    def batched_sparse_step(self, grad, rows, seg_begin, seg_end, seg_signal, signal_tensor_pinned, scale,
+                            progress=None):
         """engine.py:320-327.  Blocking; run it on a worker thread (ctypes drops the GIL)."""
         self.step_count += 1
         ops.cpu_adam_batched_sparse_step(self.param, grad, self.exp_avg, self.exp_avg_sq, self.columns_lr, rows,
                                          seg_begin, seg_end, seg_signal, signal_tensor_pinned, self.betas[0],
-                                         self.betas[1], self.eps, self.step_count, scale, self.n_threads)
+                                         self.betas[1], self.eps, self.step_count, scale, self.n_threads, progress)
 
 
 class UnifiedAdam:

@@ -375,7 +375,7 @@ def adam_dense(param, grad, exp_avg, exp_avg_sq, lr, b1, b2, eps, step, grad_sca
 
 
 def cpu_adam_batched_sparse_step(param, grad, exp_avg, exp_avg_sq, col_lr, rows, seg_begin, seg_end, seg_signal,
-                                 signal, b1, b2, eps, step, scale, n_threads=0):
+                                 signal, b1, b2, eps, step, scale, n_threads=0, progress=None):
     """All arguments are HOST tensors/arrays (pinned where the GPU also touches them).  Blocking.
     Segment s = rows[seg_begin[s]:seg_end[s]], processed after signal[seg_signal[s]] != 0 (no wait if < 0)."""
     import numpy as np
@@ -384,7 +384,7 @@ def cpu_adam_batched_sparse_step(param, grad, exp_avg, exp_avg_sq, col_lr, rows,
     seg_signal = np.ascontiguousarray(seg_signal, np.int32)
     call("clmgs_cpu_adam_batched_sparse_step", param, grad, exp_avg, exp_avg_sq, int(param.shape[1]), col_lr, rows,
          seg_begin, seg_end, seg_signal, len(seg_begin), signal, float(b1), float(b2), float(eps), int(step),
-         float(scale), int(n_threads))
+         float(scale), int(n_threads), progress)
 
 
 def sh_colors_fwd(degree, means, campos, coeffs):

@@ -10,6 +10,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <thread>
 #include <vector>
 
@@ -68,7 +69,8 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
                                                     const int32_t *host_rows, const int64_t *seg_begin,
                                                     const int64_t *seg_end, const int32_t *seg_signal, int n_segments,
                                                     const volatile int32_t *h_signal, float b1, float b2, float eps,
-                                                    int64_t step, float scale, int n_threads) {
+                                                    int64_t step, float scale, int n_threads,
+                                                    volatile int64_t *host_progress) {
     if (cols <= 0 || n_segments < 0 || step < 1) {
         clmgs_set_error("cpu_adam: bad arguments (cols=%d n_segments=%d step=%lld)", cols, n_segments, (long long)step);
         return CLMGS_ERR_INVALID;
@@ -79,6 +81,9 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
     c.b1 = b1; c.b2 = b2; c.eps = eps; c.scale = scale;
     c.inv_bc1 = (float)(1.0 / (1.0 - pow((double)b1, (double)step)));
     c.bc2_rsqrt = (float)(1.0 / sqrt(1.0 - pow((double)b2, (double)step)));
+    std::vector<std::atomic<int>> seg_done(n_segments > 0 ? n_segments : 1);
+    for (auto &d : seg_done) d.store(0);
+    if (host_progress) *host_progress = 0;
     auto worker = [&](int tid) {
         for (int m = 0; m < n_segments; ++m) {
             if (seg_signal[m] >= 0 && h_signal) wait_flag(h_signal + seg_signal[m]);  // these gradients have landed
@@ -95,6 +100,12 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
                 }
                 adam_row(host_param + base, host_grad + base, host_exp_avg + base, host_exp_avg_sq + base, col_lr,
                          cols, c);
+            }
+            // the last thread to finish segment m publishes "segments 0..m are done" (threads run the
+            // segments in order, so completion is monotonic)
+            if (seg_done[m].fetch_add(1, std::memory_order_acq_rel) + 1 == n_threads && host_progress) {
+                __atomic_thread_fence(__ATOMIC_RELEASE);
+                *host_progress = m + 1;
             }
         }
     };
