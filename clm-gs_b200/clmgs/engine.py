@@ -294,6 +294,8 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     chunk_edges = [n_last * j // J for j in range(J + 1)]
     seg_begin, seg_end, seg_signal = [], [], []
     if not args.sparse_adam:
+        # rows no camera touched: dense Adam still decays their moments; their gradient rows are zero by the
+        # table's invariant, so the update skips reading / re-zeroing them (seg_zero_grad)
         seg_begin.append(int(rb[0])); seg_end.append(int(re_[0])); seg_signal.append(-1)
     for m in range(1, bsz):
         seg_begin.append(int(rb[m])); seg_end.append(int(re_[m])); seg_signal.append(m - 1)
@@ -311,7 +313,8 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
         t0 = _t.perf_counter()
         try:
             cpu_adam.batched_sparse_step(h_grad, oc["rows_host"], seg_begin, seg_end, seg_signal, signal, 1.0 / bsz,
-                                         progress)
+                                         progress, [1 if (s_ == -1 and not args.sparse_adam and i_ == 0) else 0
+                                                    for i_, s_ in enumerate(seg_signal)])
         except Exception as e:  # surfaced after join
             worker_err.append(e)
         worker_times["cpu_adam_thread_ms"] = (_t.perf_counter() - t0) * 1e3

@@ -100,12 +100,13 @@ class CpuAdam:
         self.n_threads = n_threads if n_threads > 0 else max(1, (os.cpu_count() or 2) - 1)
 
     def batched_sparse_step(self, grad, rows, seg_begin, seg_end, seg_signal, signal_tensor_pinned, scale,
-                            progress=None):
+                            progress=None, seg_zero_grad=None):
         """engine.py:320-327.  Blocking; run it on a worker thread (ctypes drops the GIL)."""
         self.step_count += 1
         ops.cpu_adam_batched_sparse_step(self.param, grad, self.exp_avg, self.exp_avg_sq, self.columns_lr, rows,
                                          seg_begin, seg_end, seg_signal, signal_tensor_pinned, self.betas[0],
-                                         self.betas[1], self.eps, self.step_count, scale, self.n_threads, progress)
+                                         self.betas[1], self.eps, self.step_count, scale, self.n_threads, progress,
+                                         seg_zero_grad)
 
 
 class UnifiedAdam:

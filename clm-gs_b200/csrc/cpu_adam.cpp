@@ -26,6 +26,7 @@ struct AdamConst {
 };
 
 // one row of `cols` floats; cols % 8 == 0 fast path (48 = 6 x __m256)
+template <bool ZERO_GRAD>  // ZERO_GRAD: the gradient row is known to be zero -- neither read nor re-zeroed
 inline void adam_row(float *p, float *g, float *m, float *v, const float *col_lr, int cols, const AdamConst &c) {
     int k = 0;
     const __m256 b1 = _mm256_set1_ps(c.b1), omb1 = _mm256_set1_ps(1.0f - c.b1);
@@ -33,7 +34,7 @@ inline void adam_row(float *p, float *g, float *m, float *v, const float *col_lr
     const __m256 eps = _mm256_set1_ps(c.eps), sc = _mm256_set1_ps(c.scale);
     const __m256 ibc1 = _mm256_set1_ps(-c.inv_bc1), bc2r = _mm256_set1_ps(c.bc2_rsqrt);
     for (; k + 8 <= cols; k += 8) {
-        __m256 gg = _mm256_mul_ps(_mm256_loadu_ps(g + k), sc);
+        __m256 gg = ZERO_GRAD ? _mm256_setzero_ps() : _mm256_mul_ps(_mm256_loadu_ps(g + k), sc);
         __m256 mm = _mm256_add_ps(_mm256_mul_ps(b1, _mm256_loadu_ps(m + k)), _mm256_mul_ps(omb1, gg));
         __m256 vv = _mm256_add_ps(_mm256_mul_ps(b2, _mm256_loadu_ps(v + k)), _mm256_mul_ps(omb2, _mm256_mul_ps(gg, gg)));
         __m256 denom = _mm256_add_ps(_mm256_mul_ps(_mm256_sqrt_ps(vv), bc2r), eps);
@@ -41,15 +42,16 @@ inline void adam_row(float *p, float *g, float *m, float *v, const float *col_lr
         _mm256_storeu_ps(p + k, _mm256_add_ps(_mm256_loadu_ps(p + k), step));
         _mm256_storeu_ps(m + k, mm);
         _mm256_storeu_ps(v + k, vv);
-        _mm256_storeu_ps(g + k, _mm256_setzero_ps());  // version 3: zero the consumed gradient in place
+        if (!ZERO_GRAD) _mm256_storeu_ps(g + k, _mm256_setzero_ps());  // version 3: zero the consumed gradient in place
     }
     for (; k < cols; ++k) {
-        float gg = g[k] * c.scale;
+        float gg = ZERO_GRAD ? 0.f : g[k] * c.scale;
         float mm = c.b1 * m[k] + (1.0f - c.b1) * gg;
         float vv = c.b2 * v[k] + (1.0f - c.b2) * gg * gg;
         float denom = sqrtf(vv) * c.bc2_rsqrt + c.eps;
         p[k] += -(col_lr[k] * c.inv_bc1) * (mm / denom);
-        m[k] = mm; v[k] = vv; g[k] = 0.f;
+        m[k] = mm; v[k] = vv;
+        if (!ZERO_GRAD) g[k] = 0.f;
     }
 }
 
@@ -67,7 +69,8 @@ inline void wait_flag(const volatile int32_t *flag) {
 CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, float *host_exp_avg,
                                                     float *host_exp_avg_sq, int cols, const float *col_lr,
                                                     const int32_t *host_rows, const int64_t *seg_begin,
-                                                    const int64_t *seg_end, const int32_t *seg_signal, int n_segments,
+                                                    const int64_t *seg_end, const int32_t *seg_signal,
+                                                    const int32_t *seg_zero_grad, int n_segments,
                                                     const volatile int32_t *h_signal, float b1, float b2, float eps,
                                                     int64_t step, float scale, int n_threads,
                                                     volatile int64_t *host_progress) {
@@ -88,18 +91,19 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
         for (int m = 0; m < n_segments; ++m) {
             if (seg_signal[m] >= 0 && h_signal) wait_flag(h_signal + seg_signal[m]);  // these gradients have landed
             const int64_t lo = seg_begin[m], hi = seg_end[m], n = hi - lo;
+            const bool zg = seg_zero_grad && seg_zero_grad[m];
             const int64_t a = lo + n * tid / n_threads, b = lo + n * (tid + 1) / n_threads;
             for (int64_t r = a; r < b; ++r) {
                 const int64_t base = (int64_t)host_rows[r] * cols;
                 if (r + 4 < b) {
                     const int64_t nb = (int64_t)host_rows[r + 4] * cols;
                     _mm_prefetch((const char *)(host_param + nb), _MM_HINT_T0);
-                    _mm_prefetch((const char *)(host_grad + nb), _MM_HINT_T0);
+                    if (!zg) _mm_prefetch((const char *)(host_grad + nb), _MM_HINT_T0);
                     _mm_prefetch((const char *)(host_exp_avg + nb), _MM_HINT_T0);
                     _mm_prefetch((const char *)(host_exp_avg_sq + nb), _MM_HINT_T0);
                 }
-                adam_row(host_param + base, host_grad + base, host_exp_avg + base, host_exp_avg_sq + base, col_lr,
-                         cols, c);
+                if (zg) adam_row<true>(host_param + base, host_grad + base, host_exp_avg + base, host_exp_avg_sq + base, col_lr, cols, c);
+                else adam_row<false>(host_param + base, host_grad + base, host_exp_avg + base, host_exp_avg_sq + base, col_lr, cols, c);
             }
             // the last thread to finish segment m publishes "segments 0..m are done" (threads run the
             // segments in order, so completion is monotonic)

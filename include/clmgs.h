@@ -388,6 +388,9 @@ int clmgs_adam_dense(float *param, const float *grad, float *exp_avg, float *exp
  * the last camera so that the update overlaps the final gradient flush).
  * Gradients are multiplied by `scale`, and zeroed in place afterwards
  * (the reference's version=3).  n_threads <= 0 picks hardware concurrency.
+ * seg_zero_grad (optional): non-zero marks a segment whose gradient rows are known to be
+ * zero (rows no camera touched, in dense mode): the same update is applied without reading
+ * or re-zeroing the gradient table (a quarter less DRAM traffic for those rows).
  * host_progress (optional): set to s+1 once segments 0..s are complete, so another
  * host thread can follow the update (used to start loading a batch's rows while the
  * previous batch's update is still running).
@@ -396,7 +399,8 @@ int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, floa
                                        float *host_exp_avg_sq, int cols, const float *col_lr,
                                        const int32_t *host_rows, const int64_t *seg_begin,
                                        const int64_t *seg_end, const int32_t *seg_signal,
-                                       int n_segments, const volatile int32_t *h_signal, float b1,
+                                       const int32_t *seg_zero_grad, int n_segments,
+                                       const volatile int32_t *h_signal, float b1,
                                        float b2, float eps, int64_t step, float scale,
                                        int n_threads, volatile int64_t *host_progress);
 

@@ -76,8 +76,10 @@ def test_cpu_adam_matches_oracle_and_waits_for_signals():
         first = 1 if sparse else 0   # sparse_adam: the untouched group is simply not passed
         seg_b, seg_e = offs[first:-1], offs[first + 1:]
         seg_sig = np.arange(first, bsz + 1) - 1   # group m waits on flag m-1; group 0 (-1) does not wait
+        prog = np.zeros(1, np.int64)
         ops.cpu_adam_batched_sparse_step(pp, gg, mm, vv, col_lr, rows, seg_b, seg_e, seg_sig, signal, 0.9 ** 4,
-                                         0.999 ** 4, 1e-15 / 2, 2, 0.25, n_threads=3)
+                                         0.999 ** 4, 1e-15 / 2, 2, 0.25, n_threads=3, progress=prog)
+        assert prog[0] == len(seg_b)
         dt = time.time() - t0
         th.join()
         assert dt > 0.06, "did not wait for the per-camera signals"
@@ -101,3 +103,23 @@ def test_tsp_tour_is_a_permutation_and_not_worse_than_identity():
         cost = lambda t: sum(d[t[i], t[(i + 1) % n]] for i in range(n))
         assert cost(tour) <= cost(list(range(n)))
     assert ops.tsp_tour(np.zeros((1, 1), np.int32)) == [0]
+
+
+def test_cpu_adam_zero_grad_segments_match_reading_zero_rows():
+    from clmgs import ops
+    rng = np.random.default_rng(3)
+    N = 2000
+    p = rng.standard_normal((N, 48)).astype(np.float32)
+    m = rng.standard_normal((N, 48)).astype(np.float32) * 0.1
+    v = rng.random((N, 48)).astype(np.float32) * 0.01
+    col_lr = np.full(48, 1e-3, np.float32)
+    rows = np.arange(N, dtype=np.int32)
+    sig = np.zeros(1, np.int32)
+    outs = []
+    for zg in (None, [1]):
+        pp, mm, vv, gg = p.copy(), m.copy(), v.copy(), np.zeros((N, 48), np.float32)
+        ops.cpu_adam_batched_sparse_step(pp, gg, mm, vv, col_lr, rows, [0], [N], [-1], sig, 0.9, 0.999, 1e-15, 5, 0.25,
+                                         n_threads=2, seg_zero_grad=zg)
+        outs.append((pp, mm, vv))
+    for a, b in zip(outs[0], outs[1]):
+        np.testing.assert_array_equal(a, b)
