@@ -51,6 +51,7 @@ def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters
     h_params, h_grad = gaussians._parameters, parameters_grad_buffer[: ctx.hi - ctx.lo]
     assert h_params.shape[0] == ctx.hi - ctx.lo, "SH table must be this rank's shard"
 
+    compute = torch.cuda.current_stream()
     with torch.no_grad():
         filters, cull = calculate_filters(local_cameras, gaussians, timer)
         # local order: keep input order (TSP only matters for per-camera retention, which the cache replaces)
@@ -58,33 +59,49 @@ def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters
         sparsity = [f.shape[0] / float(N) for f in filters]
         with timer("need_ids"):
             need_ids = torch.nonzero(cull["bitmap"]).flatten()  # union of this rank's cameras, ascending
-        with timer("rows_exchange_in"):
-            plan = ctx.exchange.plan(need_ids)
+        # geometry of the local cameras needs no SH rows: queue it on the compute stream, then run the row
+        # exchange on the copy stream so that NVLink / PCIe traffic overlaps projection + tile sort
+        geoms = [geometry_one_camera(gaussians, local_cameras[k], filters[k], timer) for k in ordered]
+        ready = torch.cuda.Event()
+        ready.record(compute)
+        with torch.cuda.stream(comm_stream):
+            comm_stream.wait_event(ready)
+            with timer("rows_exchange_in", comm_stream):
+                plan = ctx.exchange.plan(need_ids)
 
-            def gather_local(local_idx):
-                out = ops._empty((local_idx.shape[0], 48), torch.float32, dev)
-                ops.rows_gather(out, h_params, local_idx)  # zero-copy read of my pinned shard
-                return out
+                def gather_local(local_idx):
+                    # several ranks usually ask for the same row: read each requested row from pinned host ONCE
+                    # (PCIe), then serve every requester from device memory
+                    uniq, inv = torch.unique(local_idx, return_inverse=True)
+                    rows_u = ops._empty((uniq.shape[0], 48), torch.float32, dev)
+                    ops.rows_gather(rows_u, h_params, uniq)           # zero-copy read of my pinned shard
+                    out = ops._empty((local_idx.shape[0], 48), torch.float32, dev)
+                    ops.rows_gather(out, rows_u, inv)                 # device -> device fan-out
+                    return out
 
-            cache = ctx.exchange.fetch(plan, gather_local)
+                cache = ctx.exchange.fetch(plan, gather_local)
+            cache.record_stream(compute)
+            cache_ready = torch.cuda.Event()
+            cache_ready.record(comm_stream)
+        need_ids.record_stream(comm_stream)
+        # the cache is a slot table: row of Gaussian id = its rank in need_ids (same kernels as the single-GPU engine)
+        slot_of = torch.empty(N, dtype=torch.int32, device=dev)
+        ops.slot_map(need_ids.to(torch.int32), slot_of)
         cache_grad = ops._zeros((need_ids.shape[0], 48), torch.float32, dev)
         grads = dict(xyz=torch.zeros_like(gaussians._xyz), opacity=torch.zeros_like(gaussians._opacity),
                      scaling=torch.zeros_like(gaussians._scaling), rotation=torch.zeros_like(gaussians._rotation))
         losses, n_isects = [], []
+        compute.wait_event(cache_ready)
         for k in ordered:
             cam, ids = local_cameras[k], filters[k]
-            pos = torch.searchsorted(need_ids, ids)          # rank of each visible Gaussian in the cache
-            shs = ops._empty((ids.shape[0], 48), torch.float32, dev)
-            ops.rows_gather(shs, cache, pos)                  # device -> device
-            fw = geometry_one_camera(gaussians, cam, ids, timer)
-            fw = shade_one_camera(gaussians, cam, fw, shs, background, timer)
+            fw = shade_one_camera(gaussians, cam, geoms[k], cache, background, timer, ids=ids, slot_of=slot_of)
+            geoms[k] = None
             with timer("loss"):
                 loss_vec, v_render = ops.loss_fwd_bwd(fw["render"][0], cam.original_image, args.lambda_dssim, hwc=True)
             losses.append(loss_vec[0])
-            shs_grad = ops._zeros((ids.shape[0], 48), torch.float32, dev)
-            backward_one_camera(gaussians, cam, ids, shs, shs_grad, fw, v_render[None], grads, timer)
-            ops.rows_accumulate(cache_grad, shs_grad, pos)
+            backward_one_camera(gaussians, cam, ids, cache, cache_grad, fw, v_render[None], grads, timer, slot_of=slot_of)
             n_isects.append(fw["n_isects"])
+            del fw, v_render
 
         # replicated attributes: sum gradients over ranks, same Adam everywhere
         with timer("allreduce_dense"):
@@ -111,12 +128,21 @@ def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters
             ctx.exchange.return_grads(plan, cache_grad, accumulate_local)
         torch.cuda.synchronize()
     n_local = ctx.hi - ctx.lo
+    t_rows = touched["rows"]
     if args.sparse_adam:
-        rows = touched["rows"].to(torch.int32).cpu().numpy()
+        rows = t_rows.to(torch.int32).cpu().numpy()
+        seg_b, seg_e, seg_zg = [0], [len(rows)], [0]
     else:
-        rows = np.arange(n_local, dtype=np.int32)
+        # dense Adam also decays the moments of the rows nobody touched; their gradient rows are zero, so that
+        # segment skips the gradient table
+        mask = torch.ones(n_local, dtype=torch.bool, device=dev)
+        mask[t_rows] = False
+        unt = torch.nonzero(mask).flatten()
+        rows = torch.cat([unt, t_rows]).to(torch.int32).cpu().numpy()
+        seg_b, seg_e, seg_zg = [0, int(unt.shape[0])], [int(unt.shape[0]), len(rows)], [1, 0]
     sig = np.zeros(1, np.int32)
-    gaussians.optimizer.cpu_adam.batched_sparse_step(h_grad, rows, [0], [len(rows)], [-1], sig, 1.0 / bsz_global)
+    gaussians.optimizer.cpu_adam.batched_sparse_step(h_grad, rows, seg_b, seg_e, [-1] * len(seg_b), sig, 1.0 / bsz_global,
+                                                     None, seg_zg)
     if timer.enabled:
         timer.collect()
     gaussians.last_batch_stats = dict(n_visible=[f.shape[0] for f in filters], n_isects=n_isects,

@@ -234,11 +234,23 @@ CLMGS_EXPORT int clmgs_sh_fwd(int64_t N, int K, int degree, const float *dirs, c
     return CLMGS_OK;
 }
 
+__global__ void sh_colors_fwd_lanes_kernel(int64_t N, int degree, const float *__restrict__ means,
+                                           const float *__restrict__ campos, const float4 *__restrict__ coeffs,
+                                           const int64_t *__restrict__ ids, const int32_t *__restrict__ slot_of,
+                                           float *__restrict__ colors);
+
 CLMGS_EXPORT int clmgs_sh_colors_fwd(int64_t N, int K, int degree, const float *means, const float *campos,
                                      const float *coeffs, float *colors, void *stream) {
     CLMGS_REQUIRE(degree >= 0 && degree <= 4, "sh_colors_fwd: degree %d not in [0,4]", degree);
     CLMGS_REQUIRE(K >= (degree + 1) * (degree + 1) && K <= 25, "sh_colors_fwd: K=%d too small for degree %d (or > 25)", K, degree);
     if (N == 0) return CLMGS_OK;
+    if (K == 16 && degree <= 3 && (((uintptr_t)coeffs) & 15) == 0) {
+        // same 4-lane evaluation order as the backward kernel, so both agree on the clamp mask bit for bit
+        sh_colors_fwd_lanes_kernel<<<(unsigned)ceil_div64(N * 4, 256), 256, 0, as_stream(stream)>>>(
+            N, degree, means, campos, reinterpret_cast<const float4 *>(coeffs), nullptr, nullptr, colors);
+        CLMGS_LAUNCH_OK();
+        return CLMGS_OK;
+    }
     size_t smem = (size_t)kShRows * ((K * 3) | 1) * sizeof(float);
     sh_fwd_kernel<true><<<(unsigned)ceil_div64(N, kShRows), kShRows, smem, as_stream(stream)>>>(
         N, K, degree, means, campos, coeffs, nullptr, colors);
