@@ -185,6 +185,9 @@ def run_ours(a):
                                                                  g["opacity_logit"], sh_host).training_setup(args)
 
     def train_step(cams, timer=None):
+        if a.strategy == "naive":
+            return engine.naive_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None, comm, gen,
+                                                        timer=timer)
         if ctx is None:
             return engine.clm_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None, comm, gen,
                                                       timer=timer)
@@ -319,7 +322,7 @@ def run_ours(a):
                    ms_per_step=round(ms_per_step, 3), higher_is_better=True, scaling="weak", vs_baseline=None,
                    dtype="f32", data="synthetic",
                    config=dict(workload="%s: %d Gaussians, %dx%d, batch %d cameras/iteration, SH degree 3, "
-                               "clm_offload (48-float SH rows + Adam state in pinned host memory)" % (spec.name, N, W, H, bsz),
+                               "%s_offload (48-float SH rows + Adam state in pinned host memory)" % (spec.name, N, W, H, bsz, a.strategy),
                                parallelism=("dp%d over cameras: global batch %d cameras/step (counted as %d iterations of %d), SH rows + "
                                             "host Adam sharded by Gaussian id, NCCL all-to-all-v + all-reduce" % (world, bsz * world, world, bsz))
                                if world > 1 else "1 GPU",
@@ -425,6 +428,8 @@ def main():
     ap.add_argument("--bsz", type=int, default=0)
     ap.add_argument("--sparse-adam", action="store_true")
     ap.add_argument("--cpu-threads", type=int, default=0)
+    ap.add_argument("--strategy", default="clm", choices=["clm", "naive"],
+                    help="naive = bulk-transfer baseline built from the same kernels (BASELINE.json configs[2] comparison)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--pipeline", action="store_true",
                     help="opt-in engine mode: defer the host-Adam join to the next call (reported in the extra "

@@ -491,6 +491,62 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
 
 
 @torch.no_grad()
+def naive_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_grad_buffer, background, pipe_args,
+                                  comm_stream=None, perm_generator=None, timer=None):
+    """Minimal ZeRO-offload-style baseline for BASELINE.json's "clm_offload vs naive_offload" comparison
+    (strategies/naive_offload/engine.py: load ALL offloaded parameters to the GPU in one transfer, render the
+    cameras, send ALL gradients back in one transfer, then update on the CPU -- no selection, no overlap).
+    Built from the same kernels; only the SH table is offloaded here (the reference's naive mode also keeps
+    xyz/opacity/scale/rotation on the host, i.e. it moves 59 instead of 48 floats per Gaussian).
+    Same math as clm_offload_train_one_batch; cameras are processed in input order."""
+    timer = timer or _NULL_TIMER
+    args = gaussians.args
+    bsz = len(batched_cameras)
+    N = gaussians.n_gaussians
+    dev = gaussians._xyz.device
+    h_params, h_grad = gaussians._parameters, parameters_grad_buffer[:N]
+    filters, cull = calculate_filters(batched_cameras, gaussians, timer)
+    sparsity = [f.shape[0] / float(N) for f in filters]
+    with timer("bulk_load"):
+        d_rows = ops._empty((N, 48), torch.float32, dev)
+        d_rows.copy_(h_params, non_blocking=True)
+    d_grad = ops._zeros((N, 48), torch.float32, dev)
+    ident = getattr(gaussians, "_identity_slots", None)
+    if ident is None or ident.shape[0] != N:
+        ident = gaussians._identity_slots = torch.arange(N, dtype=torch.int32, device=dev)
+    grads = dict(xyz=torch.zeros_like(gaussians._xyz), opacity=torch.zeros_like(gaussians._opacity),
+                 scaling=torch.zeros_like(gaussians._scaling), rotation=torch.zeros_like(gaussians._rotation))
+    losses, n_isects = [], []
+    for k in range(bsz):
+        cam, ids = batched_cameras[k], filters[k]
+        fw = geometry_one_camera(gaussians, cam, ids, timer)
+        fw = shade_one_camera(gaussians, cam, fw, d_rows, background, timer, ids=ids, slot_of=ident)
+        with timer("loss"):
+            loss_vec, v_render = ops.loss_fwd_bwd(fw["render"][0], cam.original_image, args.lambda_dssim, hwc=True)
+        losses.append(loss_vec[0])
+        backward_one_camera(gaussians, cam, ids, d_rows, d_grad, fw, v_render[None], grads, timer, slot_of=ident)
+        n_isects.append(fw["n_isects"])
+        del fw, v_render
+    with timer("gpu_adam"):
+        vis = (cull["bitmap"] != 0).to(torch.uint8) if args.sparse_adam else None
+        gaussians.optimizer.gpu_adam.step(grads, visibility=vis, grad_scale=1.0 / bsz)
+    with timer("bulk_store"):
+        h_grad.copy_(d_grad, non_blocking=True)
+    if args.sparse_adam:
+        rows = torch.nonzero(cull["bitmap"]).flatten().to(torch.int32).cpu().numpy()
+    else:
+        rows = np.arange(N, dtype=np.int32)
+    torch.cuda.synchronize()
+    gaussians.optimizer.cpu_adam.batched_sparse_step(h_grad, rows, [0], [len(rows)], [-1], np.zeros(1, np.int32), 1.0 / bsz)
+    if args.sparse_adam:
+        h_grad.zero_()  # rows outside `rows` hold zeros already; keep the table's invariant explicit
+    if timer.enabled:
+        timer.collect()
+    gaussians.last_batch_stats = dict(n_visible=[f.shape[0] for f in filters], n_isects=n_isects, n_union=N)
+    return losses, list(range(bsz)), sparsity
+
+
+@torch.no_grad()
 def clm_offload_eval_one_cam(camera, gaussians, background, scene=None):
     """engine.py:928-979, with the SH rows fetched by the zero-copy gather kernel instead of a
     CPU-side torch.gather + .to('cuda').  Returns the [3,H,W] image."""

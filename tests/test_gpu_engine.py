@@ -119,3 +119,15 @@ def test_pipelined_host_adam_gives_the_same_training():
     well = m_ref > 1e-2 * m_ref.max()
     d = np.abs((gm._parameters.numpy() - p0) - (st["sh"] - p0))[well].max() / np.abs(st["sh"] - p0).max()
     assert d < 5e-3, d
+
+
+def test_naive_offload_baseline_matches_oracle():
+    W, H, bsz = 112, 80, 4
+    spec, g, V, K, P, gts, args, gm, cams, st = _setup(20_000, W, H, bsz, False)
+    args.densification_stats = False
+    losses, order, _ = engine.naive_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None)
+    ref_losses, _, _ = TS.train_one_batch(st, V, K, P, gts, W, H, args, order)
+    np.testing.assert_allclose([float(l) for l in losses], ref_losses, rtol=2e-5, atol=2e-6)
+    assert not gm.parameters_grad_buffer.numpy().any()
+    _close(gm.optimizer.cpu_adam.exp_avg.numpy(), st["m_sh"], 1e-3, "m_sh")
+    _close(gm.optimizer.gpu_adam.state["scaling"]["exp_avg"].cpu().numpy(), st["m_log_scale"], 1e-3, "m_scale")
