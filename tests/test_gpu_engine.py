@@ -131,3 +131,27 @@ def test_naive_offload_baseline_matches_oracle():
     assert not gm.parameters_grad_buffer.numpy().any()
     _close(gm.optimizer.cpu_adam.exp_avg.numpy(), st["m_sh"], 1e-3, "m_sh")
     _close(gm.optimizer.gpu_adam.state["scaling"]["exp_avg"].cpu().numpy(), st["m_log_scale"], 1e-3, "m_scale")
+
+
+def test_camera_feed_matches_direct_cameras():
+    """the double-buffered feed hands the engine the same cameras as per-field uploads."""
+    from clmgs import feed
+    W, H, bsz = 112, 80, 4
+    spec, g, V, K, P, gts, args, gm, cams, st = _setup(20_000, W, H, bsz, False)
+    V2 = np.concatenate([V, V[::-1]]); K2 = np.concatenate([K, K[::-1]]); gts2 = np.concatenate([gts, gts[::-1]])
+    fd = feed.CameraFeed(V2, K2, torch.from_numpy(gts2), bsz)
+    for b in (0, 1, 2):  # batch 2 wraps to batch 0
+        got = fd.get(b)
+        idx = [(b % 2) * bsz + i for i in range(bsz)]
+        for c, j in zip(got, idx):
+            ref = model.Camera(V2[j], K2[j], gts2[j], uid=j)
+            assert c.uid == j and (c.image_height, c.image_width) == (H, W)
+            assert torch.equal(c.original_image, ref.original_image)
+            assert torch.equal(c.viewmat, ref.viewmat) and torch.equal(c.K, ref.K)
+            assert torch.equal(c.world_view_transform, ref.world_view_transform)
+            torch.testing.assert_close(c.camtoworlds, ref.camtoworlds, rtol=1e-6, atol=1e-6)
+            torch.testing.assert_close(c.campos, ref.campos, rtol=1e-6, atol=1e-6)
+    losses, order, _ = engine.clm_offload_train_one_batch(gm, None, fd.get(0), gm.parameters_grad_buffer, None, None,
+                                                          torch.cuda.Stream(), torch.Generator().manual_seed(0))
+    ref_losses, _, _ = TS.train_one_batch(st, V, K, P, gts, W, H, args, order)
+    np.testing.assert_allclose([float(l) for l in losses], ref_losses, rtol=2e-5, atol=2e-6)
