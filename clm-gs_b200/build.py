@@ -23,6 +23,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
           "--expt-relaxed-constexpr", "-Xptxas", "-v"]
 PER_FILE = {
     "proj.cu": ["-fmad=false"],
+    "densify.cu": ["-fmad=false"],
     "cpu_adam.cpp": ["-Xcompiler", "-mavx2", "-Xcompiler", "-mfma", "-Xcompiler", "-pthread"],
 }
 

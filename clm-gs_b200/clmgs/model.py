@@ -49,6 +49,15 @@ class TrainArgs:
     pipeline_host_adam: bool = False  # opt-in: return before the host Adam finished; the next call overlaps it
     rows_lookahead: int = 2  # SH-row prefetches issued this many cameras ahead on the copy stream
     geometry_lookahead: int = 3  # cameras whose projection/tile sort is issued ahead of their SH rows
+    # densification schedule (arguments/__init__.py:216-225)
+    percent_dense: float = 0.01
+    densification_interval: int = 100
+    opacity_reset_interval: int = 3000
+    densify_from_iter: int = 500
+    densify_until_iter: int = 15_000
+    densify_grad_threshold: float = 0.0002
+    min_opacity: float = 0.005
+    disable_auto_densification: bool = False
 
 
 class _Group(dict):
@@ -87,13 +96,17 @@ class CpuAdam:
     """Host Adam over the pinned [N,48] SH table (the reference's cpu_adam.FusedCPUAdam,
     optimizer.py:130-142): per-column learning rates, bias correction on."""
 
-    def __init__(self, param, columns_sizes, columns_lr, betas, eps, n_threads=0):
+    def __init__(self, param, columns_sizes, columns_lr, betas, eps, n_threads=0, capacity=None):
         self.param = param
         self.columns_lr = np.repeat(np.asarray(columns_lr, np.float32), columns_sizes).astype(np.float32)
         self.betas = list(betas)
         self.eps = eps
-        self.exp_avg = _pinned_zeros(param.shape)
-        self.exp_avg_sq = _pinned_zeros(param.shape)
+        # moments are sized like the parameter buffer (capacity rows) so that densification can grow in place
+        rows = max(capacity or 0, param.shape[0])
+        self.exp_avg_buffer = _pinned_zeros((rows,) + tuple(param.shape[1:]))
+        self.exp_avg_sq_buffer = _pinned_zeros((rows,) + tuple(param.shape[1:]))
+        self.exp_avg = self.exp_avg_buffer[:param.shape[0]]
+        self.exp_avg_sq = self.exp_avg_sq_buffer[:param.shape[0]]
         self.step_count = 0
         # default: all cores but one (the thread that launches kernels must not be time-sliced against
         # 16 spinning workers)
@@ -107,6 +120,12 @@ class CpuAdam:
                                          seg_begin, seg_end, seg_signal, signal_tensor_pinned, self.betas[0],
                                          self.betas[1], self.eps, self.step_count, scale, self.n_threads, progress,
                                          seg_zero_grad)
+
+    def resize(self, param):
+        """After densify / prune: the parameter view changed length; the moment buffers were compacted in place."""
+        self.param = param
+        self.exp_avg = self.exp_avg_buffer[:param.shape[0]]
+        self.exp_avg_sq = self.exp_avg_sq_buffer[:param.shape[0]]
 
 
 class UnifiedAdam:
@@ -198,13 +217,88 @@ class GaussianModelCLMOffload:
             g["eps"] = eps / lr_scale
             g["betas"] = [b ** bsz for b in betas]
         cpu = CpuAdam(self._parameters, [3, 45], columns_lr * lr_scale, [b ** bsz for b in betas], eps / lr_scale,
-                      args.cpu_adam_threads)
+                      args.cpu_adam_threads, capacity=self.parameters_buffer.shape[0])
+        self.percent_dense = args.percent_dense
         self.optimizer = UnifiedAdam(GpuAdam(groups, args.sparse_adam), cpu)
         self.xyz_scheduler_args = get_expon_lr_func(
             lr_init=args.position_lr_init * args.spatial_lr_scale * lr_scale,
             lr_final=args.position_lr_final * args.spatial_lr_scale * lr_scale,
             lr_delay_mult=args.position_lr_delay_mult, max_steps=args.position_lr_max_steps)
         return self
+
+    # -- densify / prune / opacity reset ----------------------------
+    _GPU_NAMES = ("xyz", "opacity", "scaling", "rotation")
+
+    def _gpu_tensors(self):
+        st = self.optimizer.gpu_adam.state
+        p = [self._xyz, self._opacity, self._scaling, self._rotation]
+        return p + [st[n]["exp_avg"] for n in self._GPU_NAMES] + [st[n]["exp_avg_sq"] for n in self._GPU_NAMES]
+
+    @torch.no_grad()
+    def _restructure(self, cls, noise=None, generator=None):
+        """classify bytes -> new state.  One plan, one gather kernel for the GPU tensors and their moments, one in-place
+        compaction of the pinned tables (strategies/clm_offload/gaussian_model.py:522-739 re-concatenates every
+        tensor three times and compacts the pinned table with a temporary of the whole kept set)."""
+        from . import engine
+        engine.wait_host_adam(self)  # a pipelined host update may still be writing the pinned tables
+        dev = self._xyz.device
+        n_old = self.n_gaussians
+        src, noise_row, (nA, nB, nS, nC) = ops.densify_plan(cls)
+        n_new = nA + nB + 2 * nC
+        cap = self.parameters_buffer.shape[0]
+        if n_new > cap:
+            raise RuntimeError("densification needs %d rows but the pinned buffers hold %d "
+                               "(the reference pre-allocates them too: gaussian_model.py:33-44)" % (n_new, cap))
+        if nC > 0:
+            if noise is None:
+                noise = torch.randn((2 * nS, 3), device=dev, generator=generator)
+            noise = noise.to(dev, torch.float32).contiguous()
+            assert tuple(noise.shape) == (2 * nS, 3), (noise.shape, nS)
+        widths = (3, 1, 3, 4) * 3
+        outs = [torch.empty((n_new, w), dtype=torch.float32, device=dev) for w in widths]
+        ops.densify_apply((nA, nB, nS, nC), src, noise_row, noise, self._gpu_tensors(), outs)
+        src_host = src.cpu().numpy()
+        ops.host_rows_densify(self.parameters_buffer, self.optimizer.cpu_adam.exp_avg_buffer,
+                              self.optimizer.cpu_adam.exp_avg_sq_buffer, n_old, src_host, nA, nB + 2 * nC,
+                              self.optimizer.cpu_adam.n_threads)
+        self._xyz, self._opacity, self._scaling, self._rotation = outs[:4]
+        for g, p in zip(self.optimizer.gpu_adam.param_groups, outs[:4]):
+            g["params"][0] = p
+        for k, n in enumerate(self._GPU_NAMES):
+            self.optimizer.gpu_adam.state[n] = dict(exp_avg=outs[4 + k], exp_avg_sq=outs[8 + k])
+        self._parameters = self.parameters_buffer[:n_new]
+        self.optimizer.cpu_adam.resize(self._parameters)
+        # densification_postfix (GM:728-738): the statistics restart from zero
+        self.max_radii2D = torch.zeros(n_new, device=dev)
+        self.xyz_gradient_accum = torch.zeros(n_new, 1, device=dev)
+        self.denom = torch.zeros(n_new, 1, device=dev)
+        self._identity_slots = None
+        return dict(n_before=n_old, n_after=n_new, n_cloned=nB, n_split_parents=nS, n_children=2 * nC,
+                    n_pruned=n_old - nA - nS)
+
+    def densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, noise=None, generator=None):
+        """strategies/base_gaussian_model.py:364-388 (clone + split + prune as one restructuring).
+        ``noise`` [2 * n_split_parents, 3] standard normal replaces the internal torch.randn draw (tests)."""
+        cls = ops.densify_classify(self.xyz_gradient_accum, self.denom, self._scaling, self._opacity, max_grad,
+                                   self.percent_dense * extent, min_opacity,
+                                   0.1 * extent if max_screen_size else None)
+        return self._restructure(cls, noise, generator)
+
+    def count_split_parents(self, max_grad, extent):
+        """How many rows densify_and_prune would split now (sizes an externally supplied noise tensor)."""
+        cls = ops.densify_classify(self.xyz_gradient_accum, self.denom, self._scaling, self._opacity, max_grad,
+                                   self.percent_dense * extent, 0.0, None)
+        return int(((cls & 2) != 0).sum().item())
+
+    def prune_points(self, mask):
+        """GM:578-611."""
+        return self._restructure(ops.prune_mask_to_class(mask.to(self._xyz.device)))
+
+    @torch.no_grad()
+    def reset_opacity(self):
+        """GM:488-520."""
+        st = self.optimizer.gpu_adam.state["opacity"]
+        ops.reset_opacity(self._opacity, st["exp_avg"], st["exp_avg_sq"], 0.01)
 
     def update_learning_rate(self, iteration):
         for g in self.optimizer.gpu_adam.param_groups:

@@ -441,3 +441,60 @@ def sh_colors_fwd_slots(degree, means, campos, d_rows, ids, slot_of):
 def sh_colors_bwd_slots(degree, means, campos, d_rows, v_colors, d_grad_rows, ids, slot_of, v_means):
     call("clmgs_sh_colors_bwd_slots", means.shape[0], int(degree), means, campos, d_rows, _f32c(v_colors), d_grad_rows,
          ids, slot_of, v_means, _st())
+
+
+# --------------------------------------------------------------------------- densify / prune / opacity reset
+def densify_classify(grad_accum, denom, log_scale, opacity_logit, grad_threshold, dense_threshold, min_opacity,
+                     world_size_threshold=None):
+    N = log_scale.shape[0]
+    cls = torch.empty(N, dtype=torch.uint8, device=log_scale.device)
+    use_ws = world_size_threshold is not None
+    call("clmgs_densify_classify", N, _f32c(grad_accum), _f32c(denom), _f32c(log_scale), _f32c(opacity_logit),
+         float(grad_threshold), float(dense_threshold), float(min_opacity), float(world_size_threshold or 0.0),
+         int(use_ws), cls, _st())
+    return cls
+
+
+def prune_mask_to_class(mask):
+    m = mask.to(torch.uint8).contiguous()
+    cls = torch.empty_like(m)
+    call("clmgs_prune_mask_to_class", m.shape[0], m, cls, _st())
+    return cls
+
+
+def densify_plan(cls):
+    """-> (src int32 [nA+nB+2nC] device, noise_row int32 [nC] device, (nA, nB, nS, nC) host ints).  Synchronises."""
+    N, dev = cls.shape[0], cls.device
+    totals = torch.zeros(4, dtype=torch.int64, device=dev)
+    src = torch.empty(max(3 * N, 1), dtype=torch.int32, device=dev)  # worst case: every row cloned + split
+    noise_row = torch.empty(max(N, 1), dtype=torch.int32, device=dev)
+    nbytes = call("clmgs_densify_plan_scratch_bytes", N)
+    scratch = _scratch(nbytes, dev)
+    call("clmgs_densify_plan", N, cls, src, noise_row, totals, scratch, scratch.numel(), _st())
+    nA, nB, nS, nC = (int(x) for x in totals.cpu().tolist())
+    return src[:nA + nB + 2 * nC], noise_row[:nC], (nA, nB, nS, nC)
+
+
+def densify_apply(counts, src, noise_row, noise, tensors_in, tensors_out):
+    """tensors_in / tensors_out: 12 tensors {xyz, opacity, log_scale, quat, exp_avg x4, exp_avg_sq x4}."""
+    import numpy as np
+    nA, nB, nS, nC = counts
+    assert len(tensors_in) == 12 and len(tensors_out) == 12
+    for t in list(tensors_in) + list(tensors_out):
+        assert t.dtype == torch.float32 and t.is_contiguous()
+    pin = np.array([t.data_ptr() for t in tensors_in], np.uint64)
+    pout = np.array([t.data_ptr() for t in tensors_out], np.uint64)
+    call("clmgs_densify_apply", nA, nB, nC, nS, src, noise_row, noise, pin, pout, _st())
+
+
+def host_rows_densify(param_buffer, exp_avg_buffer, exp_avg_sq_buffer, n_old, src_host, nA, n_tail, n_threads=0):
+    import numpy as np
+    src_host = np.ascontiguousarray(src_host, np.int32)
+    cols, cap = param_buffer.shape[1], param_buffer.shape[0]
+    assert exp_avg_buffer.shape[0] >= cap and exp_avg_sq_buffer.shape[0] >= cap
+    call("clmgs_host_rows_densify", param_buffer, exp_avg_buffer, exp_avg_sq_buffer, cols, int(n_old), int(cap),
+         src_host, int(nA), int(n_tail), int(n_threads))
+
+
+def reset_opacity(opacity_logit, exp_avg, exp_avg_sq, max_opacity=0.01):
+    call("clmgs_reset_opacity", opacity_logit.shape[0], opacity_logit, exp_avg, exp_avg_sq, float(max_opacity), _st())

@@ -11,6 +11,8 @@
 
 #include <algorithm>
 #include <atomic>
+#include <memory>
+#include <new>
 #include <thread>
 #include <vector>
 
@@ -117,6 +119,117 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
     std::vector<std::thread> th;
     th.reserve(n_threads);
     for (int t = 0; t < n_threads; ++t) th.emplace_back(worker, t);
+    for (auto &t : th) t.join();
+    return CLMGS_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Densify / prune on the pinned tables.  The reference compacts the pinned SH table with
+// torch fancy indexing on the CPU (strategies/clm_offload/gaussian_model.py:566-570: a temporary of the whole
+// kept set, then a copy back) and re-allocates both Adam moments (:534-537, :640-655).  Here the three tables
+// [capacity, cols] are compacted IN PLACE with all host threads: host_src[0..nA) are the kept rows (strictly
+// ascending, so src >= dst), host_src[nA..nA+n_tail) the rows whose SH coefficients the appended rows (clones,
+// split children) copy; appended rows get zero moments.  Kept rows move in waves through a bounce buffer: every
+// thread first reads its share of the wave, all meet at a barrier, then every thread writes -- later waves only read rows
+// at or above their own destination, so nothing is overwritten before it is read.
+namespace {
+
+template <class F>
+void parallel_ranges(int64_t n, int n_threads, F f) {
+    if (n <= 0) return;
+    int T = (int)std::min<int64_t>(n_threads, std::max<int64_t>(1, n / 1024));
+    if (T <= 1) { f((int64_t)0, n); return; }
+    std::vector<std::thread> th;
+    th.reserve(T);
+    for (int t = 0; t < T; ++t) th.emplace_back([=] { f(n * t / T, n * (t + 1) / T); });
+    for (auto &t : th) t.join();
+}
+
+}  // namespace
+
+CLMGS_EXPORT int clmgs_host_rows_densify(float *host_param, float *host_exp_avg, float *host_exp_avg_sq, int cols,
+                                         int64_t n_old, int64_t capacity, const int32_t *host_src, int64_t nA,
+                                         int64_t n_tail, int n_threads) {
+    if (cols <= 0 || n_old < 0 || nA < 0 || n_tail < 0 || nA > n_old || nA + n_tail > capacity) {
+        clmgs_set_error("host_rows_densify: bad sizes (cols=%d n_old=%lld nA=%lld n_tail=%lld capacity=%lld)", cols,
+                        (long long)n_old, (long long)nA, (long long)n_tail, (long long)capacity);
+        return CLMGS_ERR_INVALID;
+    }
+    if (!host_param || !host_exp_avg || !host_exp_avg_sq || (!host_src && nA + n_tail > 0)) {
+        clmgs_set_error("host_rows_densify: null pointer");
+        return CLMGS_ERR_INVALID;
+    }
+    if (n_threads <= 0) n_threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    n_threads = std::min(n_threads, 256);
+    std::atomic<int> bad(0);
+    parallel_ranges(nA + n_tail, n_threads, [&](int64_t a, int64_t b) {
+        for (int64_t j = a; j < b; ++j) {
+            int64_t s = host_src[j];
+            if (s < 0 || s >= n_old || (j < nA && (s < j || (j > 0 && host_src[j - 1] >= s)))) bad.store(1);
+        }
+    });
+    if (bad.load()) {
+        clmgs_set_error("host_rows_densify: source list is not strictly ascending / out of range");
+        return CLMGS_ERR_INVALID;
+    }
+    const size_t row_bytes = (size_t)cols * sizeof(float);
+    int64_t first = 0;  // the untouched prefix (src == dst) is skipped
+    while (first < nA && host_src[first] == first) ++first;
+    // waves small enough that the bounce buffer stays in the last-level cache
+    const int64_t wave = 65536;
+    const int T = (int)std::max<int64_t>(1, std::min<int64_t>(n_threads, (nA - first + n_tail) / 4096 + 1));
+    std::unique_ptr<float[]> tail(new (std::nothrow) float[(size_t)std::max<int64_t>(n_tail, 1) * cols]);
+    std::unique_ptr<float[]> bounce(new (std::nothrow) float[(size_t)wave * cols]);
+    if (!tail || !bounce) {
+        clmgs_set_error("host_rows_densify: out of host memory for %lld staged rows", (long long)(n_tail + wave));
+        return CLMGS_ERR_INVALID;
+    }
+    float *tables[3] = {host_param, host_exp_avg, host_exp_avg_sq};
+    // persistent workers + a sense-reversing barrier: ~100 waves x 3 tables x 2 phases would otherwise pay a
+    // thread spawn each
+    std::atomic<int> arrived(0), sense(0);
+    auto barrier = [&](int &local) {
+        local ^= 1;
+        if (arrived.fetch_add(1, std::memory_order_acq_rel) + 1 == T) {
+            arrived.store(0, std::memory_order_relaxed);
+            sense.store(local, std::memory_order_release);
+        } else {
+            int spins = 0;
+            while (sense.load(std::memory_order_acquire) != local) {
+                _mm_pause();
+                if (++spins > 2000) { std::this_thread::yield(); spins = 0; }
+            }
+        }
+    };
+    auto worker = [&](int tid) {
+        int local = 0;
+        // 1. coefficients of the appended rows, read before anything moves
+        for (int64_t r = n_tail * tid / T; r < n_tail * (tid + 1) / T; ++r)
+            memcpy(tail.get() + r * cols, host_param + (int64_t)host_src[nA + r] * cols, row_bytes);
+        barrier(local);
+        // 2. kept rows, in place
+        for (float *tab : tables) {
+            for (int64_t w0 = first; w0 < nA; w0 += wave) {
+                const int64_t n = std::min(wave, nA - w0), a = n * tid / T, b = n * (tid + 1) / T;
+                for (int64_t r = a; r < b; ++r)
+                    memcpy(bounce.get() + r * cols, tab + (int64_t)host_src[w0 + r] * cols, row_bytes);
+                barrier(local);  // every read of this wave happened
+                if (b > a) memcpy(tab + (w0 + a) * cols, bounce.get() + a * cols, (size_t)(b - a) * row_bytes);
+                barrier(local);  // bounce buffer free again
+            }
+        }
+        // 3. appended rows: copied coefficients, zero moments
+        const int64_t a = n_tail * tid / T, b = n_tail * (tid + 1) / T;
+        if (b > a) {
+            memcpy(host_param + (nA + a) * cols, tail.get() + a * cols, (size_t)(b - a) * row_bytes);
+            memset(host_exp_avg + (nA + a) * cols, 0, (size_t)(b - a) * row_bytes);
+            memset(host_exp_avg_sq + (nA + a) * cols, 0, (size_t)(b - a) * row_bytes);
+        }
+    };
+    if (T == 1) { worker(0); return CLMGS_OK; }
+    std::vector<std::thread> th;
+    th.reserve(T);
+    for (int t = 0; t < T; ++t) th.emplace_back(worker, t);
     for (auto &t : th) t.join();
     return CLMGS_OK;
 }

@@ -42,6 +42,30 @@ __device__ __forceinline__ float det_expf(float x) {
 
 __device__ __forceinline__ float det_sigmoidf(float x) { return 1.0f / (1.0f + det_expf(-x)); }
 
+// Deterministic natural log (only integer ops, +, *, /, fma): x = m 2^e with m in [sqrt(1/2), sqrt(2)),
+// log m = 2 atanh(s), s = (m-1)/(m+1), odd series to s^9 (|s| <= 0.1716 -> truncation < 1e-9).  ~2 ulp.
+// Same operation order as orc_logf in oracle/clmgs_oracle.c.
+__device__ __forceinline__ float det_logf(float x) {
+    if (!(x >= 0.0f)) return CUDART_NAN_F;  // negative or NaN
+    if (x == 0.0f) return -CUDART_INF_F;
+    if (x == CUDART_INF_F) return x;
+    int bias = 0;
+    if (x < 1.17549435e-38f) { x *= 8388608.0f; bias = -23; }  // subnormal
+    int ix = __float_as_int(x);
+    int e = (ix - 0x3f3504f3) >> 23;
+    float m = __int_as_float(ix - (e << 23));
+    float f = m - 1.0f;
+    float s = f / (2.0f + f);
+    float z = s * s;
+    float p = 0.22222222f;
+    p = fmaf(p, z, 0.2857143f);
+    p = fmaf(p, z, 0.4f);
+    p = fmaf(p, z, 0.6666667f);
+    float logm = fmaf(s * z, p, 2.0f * s);
+    float fe = (float)(e + bias);
+    return fmaf(fe, 0.693145751953125f, fmaf(fe, 1.428606765330187e-06f, logm));
+}
+
 // F.normalize(q, dim=-1) with eps 1e-12 (strategies/base_gaussian_model.py:50)
 __device__ __forceinline__ void normalize_quat(const float q[4], float out[4]) {
     float nn = sqrtf(((q[0] * q[0] + q[1] * q[1]) + q[2] * q[2]) + q[3] * q[3]);

@@ -404,6 +404,65 @@ int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, floa
                                        float b2, float eps, int64_t step, float scale,
                                        int n_threads, volatile int64_t *host_progress);
 
+/* ---------------------------------------------------------------------------
+ * Densify / prune / opacity reset (the non-iteration step
+ * that runs every densification_interval iterations, densification.py:5-56).
+ * Replaces GaussianModelCLMOffload.densify_and_prune (strategies/
+ * base_gaussian_model.py:364-388), densify_and_clone / densify_and_split
+ * (strategies/clm_offload/gaussian_model.py:801-831, 741-799), prune_points
+ * (:578-611, _prune_unified_adam :522-576), cat_tensors_to_unified_adam
+ * (:613-700) and reset_opacity (:488-520).
+ * ------------------------------------------------------------------------- */
+
+/* One pass over the N current rows -> class byte per row: bit0 clone (|grad| >=
+ * grad_threshold and max(exp(log_scale)) <= dense_threshold), bit1 split (grad >=
+ * grad_threshold and max scale > dense_threshold), bit2 "this row and its clone are
+ * pruned" (sigmoid(opacity) < min_opacity, or use_world_size and max scale >
+ * world_size_threshold), bit3 "its split children are pruned" (same test on the
+ * children's scale exp(log(s / 1.6))).  grad = grad_accum / denom with NaN -> 0. */
+int clmgs_densify_classify(int64_t N, const float *grad_accum, const float *denom, const float *log_scale,
+                           const float *opacity_logit, float grad_threshold, float dense_threshold,
+                           float min_opacity, float world_size_threshold, int use_world_size,
+                           uint8_t *cls, void *stream);
+
+/* prune_points(mask) alone: class byte = "pruned" where prune_mask[i] != 0. */
+int clmgs_prune_mask_to_class(int64_t N, const uint8_t *prune_mask, uint8_t *cls, void *stream);
+
+/* Class bytes -> the final row order.  totals[4] (device) = {nA kept rows, nB kept
+ * clones, nS split parents, nC split parents whose children are kept}.
+ * src[nA + nB + 2 nC] (caller sizes it N + N + 2 N at most, or reads totals first):
+ * source row of every output row, in the reference's order (kept originals, clones,
+ * children copy 0, children copy 1; each ascending).  noise_row[nC]: rank of each
+ * kept split parent among ALL split parents (the reference draws one normal sample
+ * per split parent and copy, GM:761-763: child (copy w, kept parent r) uses
+ * noise[w * nS + noise_row[r]]). */
+size_t clmgs_densify_plan_scratch_bytes(int64_t N);
+int clmgs_densify_plan(int64_t N, const uint8_t *cls, int32_t *src, int32_t *noise_row, int64_t *totals,
+                       void *scratch, size_t scratch_bytes, void *stream);
+
+/* Builds the new GPU-resident tensors and their Adam moments out of place.
+ * in12 / out12: HOST arrays of 12 device pointers {xyz[.,3], opacity[.,1],
+ * log_scale[.,3], quat[.,4], then exp_avg of the four, then exp_avg_sq of the four}.
+ * Kept rows carry their moments, appended rows start at zero.  Children: xyz =
+ * R(quat) (exp(log_scale) * noise) + xyz, log_scale = log(exp(log_scale) / 1.6),
+ * opacity and quat copied (GM:761-776).  noise [2 nS, 3] standard normal. */
+int clmgs_densify_apply(int64_t nA, int64_t nB, int64_t nC, int64_t nS, const int32_t *src,
+                        const int32_t *noise_row, const float *noise, const float *const *in12,
+                        float *const *out12, void *stream);
+
+/* Pinned tables [capacity, cols] (SH coefficients + both host Adam moments) compacted in
+ * place on the host threads: rows host_src[0..nA) kept (strictly ascending), then n_tail
+ * appended rows copying the coefficients of host_src[nA..nA+n_tail) with zero moments.
+ * HOST function (no stream); the caller has copied src to the host. */
+int clmgs_host_rows_densify(float *host_param, float *host_exp_avg, float *host_exp_avg_sq, int cols,
+                            int64_t n_old, int64_t capacity, const int32_t *host_src, int64_t nA,
+                            int64_t n_tail, int n_threads);
+
+/* reset_opacity (GM:488-520): opacity_logit <- logit(min(sigmoid(opacity_logit), max_opacity)),
+ * Adam moments of the opacity <- 0. */
+int clmgs_reset_opacity(int64_t N, float *opacity_logit, float *exp_avg, float *exp_avg_sq,
+                        float max_opacity, void *stream);
+
 /* fast_tsp.find_tour(dist, 0.001) (engine.py:179; submodule TarzanZhao/fast-tsp
  * @ 069eb3d, source not in the mount): deterministic greedy + 2-opt/Or-opt
  * open... closed tour over n <= 64 cameras, int32 dist [n*n]; writes tour[n]. */

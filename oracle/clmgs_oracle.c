@@ -67,6 +67,34 @@ ORC_API float orc_expf(float x) {
 
 ORC_API float orc_sigmoidf(float x) { return 1.0f / (1.0f + orc_expf(-x)); }
 
+/* deterministic log shared with csrc/gs_math.cuh det_logf (stands in for torch.log in the
+ * densification step: utils/general_utils.py:145 inverse_sigmoid, scaling_inverse_activation) */
+ORC_API float orc_logf(float x) {
+    if (!(x >= 0.0f)) return NAN;
+    if (x == 0.0f) return -INFINITY;
+    if (x == INFINITY) return x;
+    int bias = 0;
+    if (x < 1.17549435e-38f) { x *= 8388608.0f; bias = -23; }
+    union { int32_t i; float f; } u, m;
+    u.f = x;
+    int32_t e = (u.i - 0x3f3504f3) >> 23;
+    m.i = u.i - (e << 23);
+    float f = m.f - 1.0f;
+    float s = f / (2.0f + f);
+    float z = s * s;
+    float p = 0.22222222f;
+    p = fmaf(p, z, 0.2857143f);
+    p = fmaf(p, z, 0.4f);
+    p = fmaf(p, z, 0.6666667f);
+    float logm = fmaf(s * z, p, 2.0f * s);
+    float fe = (float)(e + bias);
+    return fmaf(fe, 0.693145751953125f, fmaf(fe, 1.428606765330187e-06f, logm));
+}
+
+ORC_API void orc_logf_array(int64_t n, const float *x, float *y) {
+    for (int64_t i = 0; i < n; ++i) y[i] = orc_logf(x[i]);
+}
+
 ORC_API void orc_activate(int64_t n, const float *log_scale, const float *raw_quat,
                           const float *opacity_logit, float *scale, float *quat,
                           float *opacity) {
