@@ -44,7 +44,7 @@ __device__ __forceinline__ float det_sigmoidf(float x) { return 1.0f / (1.0f + d
 
 // Deterministic natural log (only integer ops, +, *, /, fma): x = m 2^e with m in [sqrt(1/2), sqrt(2)),
 // log m = 2 atanh(s), s = (m-1)/(m+1), odd series to s^9 (|s| <= 0.1716 -> truncation < 1e-9).  ~2 ulp.
-// Same operation order as orc_logf in oracle/clmgs_oracle.c.
+// The test oracle restates the same operation order on the CPU.
 __device__ __forceinline__ float det_logf(float x) {
     if (!(x >= 0.0f)) return CUDART_NAN_F;  // negative or NaN
     if (x == 0.0f) return -CUDART_INF_F;
