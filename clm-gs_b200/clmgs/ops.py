@@ -498,3 +498,15 @@ def host_rows_densify(param_buffer, exp_avg_buffer, exp_avg_sq_buffer, n_old, sr
 
 def reset_opacity(opacity_logit, exp_avg, exp_avg_sq, max_opacity=0.01):
     call("clmgs_reset_opacity", opacity_logit.shape[0], opacity_logit, exp_avg, exp_avg_sq, float(max_opacity), _st())
+
+
+def radix_sort_pairs_u32(keys, vals, end_bit=32):
+    """Stable sort of (uint32-as-int32 tensor keys, int32 vals) on the low end_bit bits -> (keys_sorted, vals_sorted)."""
+    import numpy as np
+    n, dev = keys.shape[0], keys.device
+    k0, v0 = keys.contiguous().clone(), vals.contiguous().clone()
+    k1, v1 = torch.empty_like(k0), torch.empty_like(v0)
+    sc = _scratch(call("clmgs_radix_sort_pairs_u32_scratch_bytes", n), dev)
+    flag = np.zeros(1, np.int32)
+    call("clmgs_radix_sort_pairs_u32", n, k0, k1, v0, v1, int(end_bit), sc, sc.numel(), flag, _st())
+    return (k1, v1) if flag[0] else (k0, v0)

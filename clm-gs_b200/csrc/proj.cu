@@ -479,12 +479,12 @@ isect_emit_kernel(int64_t total, int64_t N, const int64_t *__restrict__ camera_i
         }
 }
 
-int clmgs_radix_sort_pairs(int64_t n, int64_t *keys, int32_t *vals, int end_bit, void *scratch,
-                           size_t scratch_bytes, cudaStream_t st);  // sort.cu
-size_t clmgs_radix_sort_scratch(int64_t n);
-size_t clmgs_sort_u32_temp_bytes(int64_t n);
-int clmgs_sort_pairs_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t *vals, int32_t *vals_alt, int end_bit,
-                         void *tmp, size_t tmp_bytes, cudaStream_t st, uint32_t **keys_out, int32_t **vals_out);
+// radix.cu: hand-written stable LSD radix sort of (u32, i32) pairs with an optional fused last pass
+size_t clmgs_radix_u32_scratch(int64_t n);
+int clmgs_radix_passes(int end_bit);
+int clmgs_radix_sort_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t *vals, int32_t *vals_alt, int end_bit,
+                         void *scratch, size_t scratch_bytes, cudaStream_t st, uint32_t **keys_out, int32_t **vals_out,
+                         int64_t *isect_ids, int32_t *flatten_ids, const float *depths);
 
 static int n_bits_of(int64_t v) {  // floor(log2(v)) + 1, CSRC/isect_tiles.cu:143-144
     int b = 0;
@@ -499,7 +499,8 @@ static int n_bits_of(int64_t v) {  // floor(log2(v)) + 1, CSRC/isect_tiles.cu:14
 // emitting intersections in that order and (3) one STABLE sort on the (cam | tile) bits alone
 // (13-14 bits = 2 passes over 8-byte pairs): within a tile the entries keep the order of step (1),
 // i.e. ascending depth with ties in ascending flatten index -- exactly what the 64-bit stable sort
-// leaves.  Traffic per intersection drops from ~6 x 24 B to ~2 x 16 B + 20 B.
+// leaves.  Traffic per intersection drops from ~6 x 24 B to ~2 x 20 B + 12 B: the last pass of (3) writes
+// isect_ids / flatten_ids itself (radix.cu), there is no separate finalize kernel.
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 depth_keys_kernel(int64_t total, const int32_t *__restrict__ radii, const float *__restrict__ depths,
@@ -547,17 +548,6 @@ perm_emit_kernel(int64_t total, int64_t N, const int64_t *__restrict__ camera_id
         }
 }
 
-__global__ void __launch_bounds__(256)
-isect_finalize_kernel(int64_t n_isects, const uint32_t *__restrict__ tkeys, const int32_t *__restrict__ vals,
-                      const float *__restrict__ depths, int64_t *__restrict__ isect_ids,
-                      int32_t *__restrict__ flatten_ids) {
-    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n_isects) return;
-    const int32_t g = vals[p];
-    isect_ids[p] = ((int64_t)tkeys[p] << 32) | (int64_t)(uint32_t)__float_as_int(depths[g]);
-    if (flatten_ids != vals) flatten_ids[p] = g;
-}
-
 static inline size_t a256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct TwoLevelLayout {
@@ -572,7 +562,7 @@ static TwoLevelLayout two_level_layout(int64_t total, int64_t n_isects) {
     L.block_sums = take(8 * (size_t)ceil_div64(total > 0 ? total : 1, kScanThreads));
     L.tkeys = take(4 * (size_t)n_isects); L.tkeys_alt = take(4 * (size_t)n_isects);
     L.vals_alt = take(4 * (size_t)n_isects);
-    size_t t1 = clmgs_sort_u32_temp_bytes(total), t2 = clmgs_sort_u32_temp_bytes(n_isects);
+    size_t t1 = clmgs_radix_u32_scratch(total), t2 = clmgs_radix_u32_scratch(n_isects);
     L.tmp_bytes = t1 > t2 ? t1 : t2;
     L.tmp = take(L.tmp_bytes);
     L.total_bytes = o;
@@ -621,7 +611,8 @@ CLMGS_EXPORT int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_i
     depth_keys_kernel<<<(unsigned)ceil_div64(total, 256), 256, 0, st>>>(total, radii, depths, dkeys, perm);
     CLMGS_LAUNCH_OK();
     uint32_t *dk_sorted; int32_t *perm_sorted;
-    if (int rc = clmgs_sort_pairs_u32(total, dkeys, dkeys_alt, perm, perm_alt, 32, tmp, L.tmp_bytes, st, &dk_sorted, &perm_sorted)) return rc;
+    if (int rc = clmgs_radix_sort_u32(total, dkeys, dkeys_alt, perm, perm_alt, 32, tmp, L.tmp_bytes, st, &dk_sorted,
+                                      &perm_sorted, nullptr, nullptr, nullptr)) return rc;
     // (2) offsets in depth order, emission
     const int64_t nblocks = ceil_div64(total, kScanThreads);
     perm_count_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(total, perm_sorted, means2d, radii, tile_size, tile_width,
@@ -629,18 +620,18 @@ CLMGS_EXPORT int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_i
     CLMGS_LAUNCH_OK();
     scan_block_sums_kernel<<<1, kScanThreads, 0, st>>>(bs, nblocks);
     CLMGS_LAUNCH_OK();
+    // the last pass of (3) writes flatten_ids, so it must not read it: with an even number of passes the
+    // emission goes to flatten_ids (A -> alt -> A), with an odd number to the scratch buffer
+    const int end_bit = tile_n_bits + cam_n_bits;
+    int32_t *v_first = (clmgs_radix_passes(end_bit) % 2 == 0) ? flatten_ids : vals_alt;
+    int32_t *v_other = (v_first == flatten_ids) ? vals_alt : flatten_ids;
     perm_emit_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(total, N, camera_ids, perm_sorted, means2d, radii, bs,
                                                                 tile_size, tile_width, tile_height, tile_n_bits, tkeys,
-                                                                flatten_ids);
+                                                                v_first);
     CLMGS_LAUNCH_OK();
-    // (3) stable partition by (cam | tile)
-    uint32_t *tk_sorted; int32_t *val_sorted;
-    if (int rc = clmgs_sort_pairs_u32(n_isects, tkeys, tkeys_alt, flatten_ids, vals_alt, tile_n_bits + cam_n_bits, tmp,
-                                      L.tmp_bytes, st, &tk_sorted, &val_sorted)) return rc;
-    isect_finalize_kernel<<<(unsigned)ceil_div64(n_isects, 256), 256, 0, st>>>(n_isects, tk_sorted, val_sorted, depths,
-                                                                              isect_ids, flatten_ids);
-    CLMGS_LAUNCH_OK();
-    return CLMGS_OK;
+    // (3) stable partition by (cam | tile); its last pass emits isect_ids / flatten_ids at the sorted positions
+    return clmgs_radix_sort_u32(n_isects, tkeys, tkeys_alt, v_first, v_other, end_bit, tmp, L.tmp_bytes, st, nullptr,
+                                nullptr, isect_ids, flatten_ids, depths);
 }
 
 __global__ void __launch_bounds__(256)

@@ -404,6 +404,16 @@ int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, floa
                                        float b2, float eps, int64_t step, float scale,
                                        int n_threads, volatile int64_t *host_progress);
 
+/* Stable LSD radix sort of (uint32 key, int32 value) pairs on key bits [0, end_bit), 8-bit digits,
+ * hand-written (csrc/radix.cu) -- the sort under clmgs_isect_emit_sort, which replaces the reference's
+ * cub::DeviceRadixSort::SortPairs call (CSRC/isect_tiles.cu:186-229).  Ping-pongs between the two buffer
+ * pairs; *result_in_alt = 1 if the sorted pairs ended up in (keys_alt, vals_alt).  Scratch holds the per-tile
+ * digit histograms. */
+size_t clmgs_radix_sort_pairs_u32_scratch_bytes(int64_t n);
+int clmgs_radix_sort_pairs_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t *vals,
+                               int32_t *vals_alt, int end_bit, void *scratch, size_t scratch_bytes,
+                               int32_t *result_in_alt, void *stream);
+
 /* ---------------------------------------------------------------------------
  * Densify / prune / opacity reset (the non-iteration step
  * that runs every densification_interval iterations, densification.py:5-56).

@@ -159,3 +159,17 @@ def test_rasterize_fwd_vs_oracle(W, H, n, bg):
     assert np.abs(ra - ra_r).max() < 1e-2 and (np.abs(ra - ra_r) > 1e-4).mean() <= 1e-4
     assert (last != last_r).mean() <= 1e-4
     assert np.median(ra_r) > 0.5  # the scene actually covers the image
+
+
+@pytest.mark.parametrize("n,end_bit,key_bits", [(0, 32, 32), (1, 32, 32), (4095, 32, 32), (4096, 13, 13), (4097, 8, 8),
+                                                 (100_003, 32, 32), (1_000_003, 13, 12), (3_000_000, 5, 3),
+                                                 (2_000_000, 32, 2), (500_000, 16, 32)])
+def test_radix_sort_pairs_is_a_stable_sort(n, end_bit, key_bits):
+    """csrc/radix.cu against numpy's stable argsort on the sorted bit range (ties keep their input order)."""
+    rng = np.random.default_rng(n + end_bit)
+    keys = rng.integers(0, 1 << key_bits, n, dtype=np.uint64).astype(np.uint32)
+    vals = rng.integers(-2**31, 2**31 - 1, n, dtype=np.int64).astype(np.int32)
+    k, v = ops.radix_sort_pairs_u32(torch.from_numpy(keys.view(np.int32)).to(DEV), torch.from_numpy(vals).to(DEV), end_bit)
+    order = np.argsort(keys & np.uint32((1 << end_bit) - 1 if end_bit < 32 else 0xffffffff), kind="stable")
+    np.testing.assert_array_equal(k.cpu().numpy().view(np.uint32), keys[order])
+    np.testing.assert_array_equal(v.cpu().numpy(), vals[order])
