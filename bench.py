@@ -89,8 +89,6 @@ class ClockSampler:
                     reasons=sorted(reasons), samples=len(sm))
 
 
-# kernels launched per C-ABI call (static table; the radix sort is CUB: 1 histogram + 1 scan-free
-# onesweep pass per 8 key bits for 46-bit keys -> 7 launches, + 2 copy-back memcpys not counted)
 # kernels of OUR library per entry point (all hand-written; clmgs_isect_emit_sort is set per config in main():
 # depth keys + 4 radix passes x 3 kernels + count/scan/emit + 3 kernels per tile-key radix pass)
 LAUNCHES = dict(clmgs_cull_count=2, clmgs_cull_emit=1, clmgs_gather_activate=1, clmgs_projection_fwd=1,
