@@ -92,7 +92,7 @@ class ClockSampler:
 # kernels of OUR library per entry point (all hand-written; clmgs_isect_emit_sort is set per config in main():
 # depth keys + 4 radix passes x 3 kernels + count/scan/emit + 3 kernels per tile-key radix pass)
 LAUNCHES = dict(clmgs_cull_count=2, clmgs_cull_emit=1, clmgs_gather_activate=1, clmgs_projection_fwd=1,
-                clmgs_sh_colors_fwd=1, clmgs_isect_count=3, clmgs_isect_emit_sort=5, clmgs_isect_offset_encode=1,
+                clmgs_sh_colors_fwd=1, clmgs_isect_count=3, clmgs_isect_emit_sort=5, clmgs_isect_sorted_offsets=5, clmgs_isect_offset_encode=1,
                 clmgs_rasterize_fwd=1, clmgs_loss_fwd_bwd=3, clmgs_rasterize_bwd=1, clmgs_projection_bwd=1,
                 clmgs_sh_colors_bwd=1, clmgs_activate_bwd_scatter=1, clmgs_rows_gather_i64=1,
                 clmgs_rows_prefetch_next=2, clmgs_rows_grad_handoff=2, clmgs_set_signal=1,
@@ -173,6 +173,7 @@ def run_ours(a):
     W, H = spec.width, spec.height
     _tile_bits = (((W + 15) // 16) * ((H + 15) // 16)).bit_length() + 1  # tile_n_bits + cam_n_bits (C = 1)
     LAUNCHES["clmgs_isect_emit_sort"] = 1 + 3 * 4 + 3 + 3 * ((_tile_bits + 7) // 8)
+    LAUNCHES["clmgs_isect_sorted_offsets"] = LAUNCHES["clmgs_isect_emit_sort"] + 2  # + offsets fill and suffix-min
     t0 = time.time()
     # N > 1: one global batch of world x bsz cameras per step, cameras data-parallel, SH rows + host Adam
     # state sharded by Gaussian id, NCCL all-to-all-v for rows/gradients and all-reduce for the replicated

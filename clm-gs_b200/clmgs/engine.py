@@ -182,9 +182,8 @@ def geometry_one_camera(gaussians, camera, ids, timer=_NULL_TIMER):
         radii, means2d, depths, conics, _ = ops.projection_fwd(means, quats, scales, camera.viewmat[None],
                                                                camera.K[None], W, H)
     with timer("isect_sort"):
-        _, isect_ids, flatten_ids = ops.isect_tiles(means2d, radii, depths, TILE_SIZE, tw, th)
-        offsets = ops.isect_offset_encode(isect_ids, 1, tw, th)
-    del isect_ids, depths
+        flatten_ids, offsets, _ = ops.isect_sorted_offsets(means2d, radii, depths, TILE_SIZE, tw, th)
+    del depths
     return dict(means=means, scales=scales, quats=quats, opac=opac, radii=radii, means2d=means2d, conics=conics,
                 offsets=offsets, flatten_ids=flatten_ids, n_isects=flatten_ids.shape[0])
 

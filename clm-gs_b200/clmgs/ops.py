@@ -204,6 +204,29 @@ def isect_tiles(means2d, radii, depths, tile_size, tile_width, tile_height, sort
     return tpg, ids, flat
 
 
+def isect_sorted_offsets(means2d, radii, depths, tile_size, tile_width, tile_height):
+    """The engine's tile stage: depth-sorted flatten_ids per tile + tile offsets, without materialising the
+    64-bit isect_ids (same flatten_ids / offsets as isect_tiles + isect_offset_encode).
+    -> (flatten_ids [n_isects] int32, offsets [C, th, tw] int32, n_isects)."""
+    means2d, depths = _f32c(means2d), _f32c(depths)
+    radii = radii.contiguous()
+    dev = means2d.device
+    C, N = radii.shape
+    total = C * N
+    tpg = _empty((max(total, 1),), torch.int32, dev)
+    cum = _empty((max(total, 1),), torch.int64, dev)
+    sc = _scratch(call("clmgs_isect_count_scratch_bytes", total), dev)
+    call("clmgs_isect_count", total, means2d, radii, int(tile_size), int(tile_width), int(tile_height),
+         tpg, cum, sc, sc.numel(), _st())
+    n_isects = int(cum[total - 1].item()) if total > 0 else 0
+    flat = _empty((n_isects,), torch.int32, dev)
+    off = torch.empty(C, tile_height, tile_width, dtype=torch.int32, device=dev)
+    sc2 = _scratch(call("clmgs_isect_sort_scratch_bytes", total, n_isects), dev)
+    call("clmgs_isect_sorted_offsets", C, N, None, means2d, radii, depths, cum, int(tile_size), int(tile_width),
+         int(tile_height), n_isects, flat, off, sc2, sc2.numel(), _st())
+    return flat, off, n_isects
+
+
 def isect_offset_encode(isect_ids, n_cameras, tile_width, tile_height):
     off = torch.empty(n_cameras, tile_height, tile_width, dtype=torch.int32, device=isect_ids.device)
     call("clmgs_isect_offset_encode", isect_ids.shape[0], isect_ids.contiguous(), int(n_cameras),

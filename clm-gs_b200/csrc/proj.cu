@@ -484,7 +484,8 @@ size_t clmgs_radix_u32_scratch(int64_t n);
 int clmgs_radix_passes(int end_bit);
 int clmgs_radix_sort_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t *vals, int32_t *vals_alt, int end_bit,
                          void *scratch, size_t scratch_bytes, cudaStream_t st, uint32_t **keys_out, int32_t **vals_out,
-                         int64_t *isect_ids, int32_t *flatten_ids, const float *depths);
+                         int64_t *isect_ids, int32_t *flatten_ids, const float *depths, int32_t *offsets,
+                         int64_t n_slots, int tile_n_bits, int n_tiles);
 
 static int n_bits_of(int64_t v) {  // floor(log2(v)) + 1, CSRC/isect_tiles.cu:143-144
     int b = 0;
@@ -574,13 +575,17 @@ CLMGS_EXPORT size_t clmgs_isect_sort_scratch_bytes(int64_t total, int64_t n_isec
     return two_level_layout(total, n_isects).total_bytes;
 }
 
-CLMGS_EXPORT int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_ids, const float *means2d,
-                                       const int32_t *radii, const float *depths, const int64_t *cum_tiles,
-                                       int tile_size, int tile_width, int tile_height, int64_t n_isects, int sort,
-                                       int64_t *isect_ids, int32_t *flatten_ids, void *scratch,
-                                       size_t scratch_bytes, void *stream) {
+static int isect_emit_sort_impl(int C, int64_t N, const int64_t *camera_ids, const float *means2d,
+                                const int32_t *radii, const float *depths, const int64_t *cum_tiles,
+                                int tile_size, int tile_width, int tile_height, int64_t n_isects, int sort,
+                                int64_t *isect_ids, int32_t *flatten_ids, int32_t *tile_offsets, void *scratch,
+                                size_t scratch_bytes, void *stream) {
     int64_t total = camera_ids ? N : (int64_t)C * N;
-    if (total == 0 || n_isects == 0) return CLMGS_OK;
+    if (total == 0 || n_isects == 0) {
+        if (tile_offsets)  // every tile is empty
+            CLMGS_CUDA(cudaMemsetAsync(tile_offsets, 0, sizeof(int32_t) * (size_t)C * tile_width * tile_height, as_stream(stream)));
+        return CLMGS_OK;
+    }
     CLMGS_REQUIRE(n_isects < ((int64_t)1 << 31) && total < ((int64_t)1 << 31),
                   "isect: n_isects=%lld / total=%lld do not fit int32 indices", (long long)n_isects, (long long)total);
     int tile_n_bits = n_bits_of((int64_t)tile_width * tile_height);
@@ -612,7 +617,7 @@ CLMGS_EXPORT int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_i
     CLMGS_LAUNCH_OK();
     uint32_t *dk_sorted; int32_t *perm_sorted;
     if (int rc = clmgs_radix_sort_u32(total, dkeys, dkeys_alt, perm, perm_alt, 32, tmp, L.tmp_bytes, st, &dk_sorted,
-                                      &perm_sorted, nullptr, nullptr, nullptr)) return rc;
+                                      &perm_sorted, nullptr, nullptr, nullptr, nullptr, 0, 0, 0)) return rc;
     // (2) offsets in depth order, emission
     const int64_t nblocks = ceil_div64(total, kScanThreads);
     perm_count_kernel<<<(unsigned)nblocks, kScanThreads, 0, st>>>(total, perm_sorted, means2d, radii, tile_size, tile_width,
@@ -631,7 +636,28 @@ CLMGS_EXPORT int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_i
     CLMGS_LAUNCH_OK();
     // (3) stable partition by (cam | tile); its last pass emits isect_ids / flatten_ids at the sorted positions
     return clmgs_radix_sort_u32(n_isects, tkeys, tkeys_alt, v_first, v_other, end_bit, tmp, L.tmp_bytes, st, nullptr,
-                                nullptr, isect_ids, flatten_ids, depths);
+                                nullptr, isect_ids, flatten_ids, depths, tile_offsets,
+                                (int64_t)C * tile_width * tile_height, tile_n_bits, tile_width * tile_height);
+}
+
+CLMGS_EXPORT int clmgs_isect_emit_sort(int C, int64_t N, const int64_t *camera_ids, const float *means2d,
+                                       const int32_t *radii, const float *depths, const int64_t *cum_tiles,
+                                       int tile_size, int tile_width, int tile_height, int64_t n_isects, int sort,
+                                       int64_t *isect_ids, int32_t *flatten_ids, void *scratch,
+                                       size_t scratch_bytes, void *stream) {
+    CLMGS_REQUIRE(n_isects == 0 || (isect_ids && flatten_ids), "isect_emit_sort: null output");
+    return isect_emit_sort_impl(C, N, camera_ids, means2d, radii, depths, cum_tiles, tile_size, tile_width, tile_height,
+                                n_isects, sort, isect_ids, flatten_ids, nullptr, scratch, scratch_bytes, stream);
+}
+
+CLMGS_EXPORT int clmgs_isect_sorted_offsets(int C, int64_t N, const int64_t *camera_ids, const float *means2d,
+                                            const int32_t *radii, const float *depths, const int64_t *cum_tiles,
+                                            int tile_size, int tile_width, int tile_height, int64_t n_isects,
+                                            int32_t *flatten_ids, int32_t *tile_offsets, void *scratch,
+                                            size_t scratch_bytes, void *stream) {
+    CLMGS_REQUIRE(tile_offsets && (n_isects == 0 || flatten_ids), "isect_sorted_offsets: null output");
+    return isect_emit_sort_impl(C, N, camera_ids, means2d, radii, depths, cum_tiles, tile_size, tile_width, tile_height,
+                                n_isects, 1, nullptr, flatten_ids, tile_offsets, scratch, scratch_bytes, stream);
 }
 
 __global__ void __launch_bounds__(256)

@@ -96,10 +96,14 @@ radix_scan_kernel(uint32_t *__restrict__ hist, int64_t ntiles, uint32_t *__restr
 }
 
 struct FinalOut {  // last pass of the tile sort: write the stage outputs instead of pairs
-    int64_t *isect_ids;
-    int32_t *flatten_ids;
-    const float *depths;
+    int64_t *isect_ids;    // mode 1
+    int32_t *flatten_ids;  // modes 1, 2
+    const float *depths;   // mode 1
+    int32_t *offsets;      // mode 2: [C * n_tiles], pre-filled with n; receives the first position of every key
+    int tile_n_bits, n_tiles;
 };
+// MODE 0: (key, value) pairs.  1: isect_ids + flatten_ids.  2: flatten_ids + tile offsets (what the rasteriser
+// consumes; no 8-byte keys are written and no separate offsets pass reads them back).
 
 __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc));
@@ -116,7 +120,7 @@ constexpr size_t kScatterDynSmem = 2 * kStageBytes;          // double buffered:
 // already streaming into the other shared-memory stage (cp.async, no registers) while the current tile is ranked,
 // permuted IN PLACE in its stage and written out, so the load latency that dominated a one-tile-per-block version
 // (ncu: 50 % of the stall samples were long-scoreboard waits on the tile's own loads) overlaps the rest.
-template <bool FINAL>
+template <int MODE>
 __global__ void __launch_bounds__(kThreads, kScatterBlocksPerSM)
 radix_scatter_kernel(int64_t n, const uint32_t *__restrict__ keys_in, const int32_t *__restrict__ vals_in,
                      uint32_t *__restrict__ keys_out, int32_t *__restrict__ vals_out, int shift, uint32_t digit_mask,
@@ -251,9 +255,18 @@ radix_scatter_kernel(int64_t n, const uint32_t *__restrict__ keys_in, const int3
             const uint32_t k = sk[i];
             const int32_t v = sv[i];
             const uint32_t pos = s_global[(k >> shift) & digit_mask] + (uint32_t)i;
-            if (FINAL) {
+            if (MODE == 1) {
                 fin.isect_ids[pos] = ((int64_t)k << 32) | (int64_t)(uint32_t)__float_as_int(fin.depths[v]);
                 fin.flatten_ids[pos] = v;
+            } else if (MODE == 2) {
+                fin.flatten_ids[pos] = v;
+                // The tile holds a contiguous chunk of a list already sorted on the lower digits, so after the stable
+                // permutation equal full keys are adjacent: the first of each run is a candidate for the key's first
+                // position overall (other tiles may hold the same key: min over candidates).
+                if (i == 0 || sk[i - 1] != k) {
+                    const uint32_t cam = k >> fin.tile_n_bits, t = k & ((1u << fin.tile_n_bits) - 1u);
+                    atomicMin(fin.offsets + (int64_t)cam * fin.n_tiles + t, (int32_t)pos);
+                }
             } else {
                 keys_out[pos] = k;
                 vals_out[pos] = v;
@@ -264,7 +277,7 @@ radix_scatter_kernel(int64_t n, const uint32_t *__restrict__ keys_in, const int3
     }
 }
 
-template <bool FINAL>
+template <int MODE>
 int launch_scatter(int64_t n, const uint32_t *keys, const int32_t *vals, uint32_t *keys_out, int32_t *vals_out, int shift,
                    uint32_t mask, const uint32_t *hist, int64_t ntiles, uint32_t *totals, FinalOut fin,
                    cudaStream_t st) {
@@ -272,17 +285,54 @@ int launch_scatter(int64_t n, const uint32_t *keys, const int32_t *vals, uint32_
     int dev = 0;
     CLMGS_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !configured[dev]) {
-        CLMGS_CUDA(cudaFuncSetAttribute(radix_scatter_kernel<FINAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        CLMGS_CUDA(cudaFuncSetAttribute(radix_scatter_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)kScatterDynSmem));
         if (dev >= 0 && dev < 64) configured[dev] = true;
     }
     const int aligned16 = (((uintptr_t)keys | (uintptr_t)vals) & 15) == 0;
     int64_t grid = (int64_t)kNumSMs * kScatterBlocksPerSM;
     if (grid > ntiles) grid = ntiles;
-    radix_scatter_kernel<FINAL><<<(unsigned)grid, kThreads, kScatterDynSmem, st>>>(n, keys, vals, keys_out, vals_out, shift,
+    radix_scatter_kernel<MODE><<<(unsigned)grid, kThreads, kScatterDynSmem, st>>>(n, keys, vals, keys_out, vals_out, shift,
                                                                                   mask, hist, ntiles, totals, aligned16, fin);
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
+}
+
+__global__ void __launch_bounds__(256)
+fill_i32_kernel(int32_t *__restrict__ p, int64_t n, int32_t v) {
+    int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// offsets[t] = min(offsets[t], offsets[t+1], ...): keys without entries start where the next key starts.
+// One block walks the (<= a few 10^4) slots from the top in chunks of 1024.
+__global__ void __launch_bounds__(1024)
+suffix_min_kernel(int32_t *__restrict__ offsets, int64_t n_slots) {
+    __shared__ int32_t s_warp[32];
+    __shared__ int32_t s_carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int32_t carry = 0x7fffffff;
+    for (int64_t hi = n_slots; hi > 0; hi -= 1024) {
+        const int64_t j = hi - 1 - threadIdx.x;  // thread 0 takes the top slot of the chunk
+        int32_t v = j >= 0 ? offsets[j] : 0x7fffffff;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int32_t t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v = min(v, t); }
+        if (lane == 31) s_warp[warp] = v;
+        __syncthreads();
+        if (warp == 0) {
+            int32_t w = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { int32_t t = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w = min(w, t); }
+            s_warp[lane] = w;
+            if (lane == 31) s_carry = w;
+        }
+        __syncthreads();
+        if (warp > 0) v = min(v, s_warp[warp - 1]);
+        v = min(v, carry);
+        if (j >= 0) offsets[j] = v;
+        carry = min(carry, s_carry);
+        __syncthreads();
+    }
 }
 
 inline size_t a256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -301,7 +351,8 @@ int clmgs_radix_passes(int end_bit) { return end_bit <= 0 ? 0 : (end_bit + 7) / 
 
 int clmgs_radix_sort_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t *vals, int32_t *vals_alt, int end_bit,
                          void *scratch, size_t scratch_bytes, cudaStream_t st, uint32_t **keys_out, int32_t **vals_out,
-                         int64_t *isect_ids, int32_t *flatten_ids, const float *depths) {
+                         int64_t *isect_ids, int32_t *flatten_ids, const float *depths, int32_t *offsets,
+                         int64_t n_slots, int tile_n_bits, int n_tiles) {
     CLMGS_REQUIRE(n >= 0 && n < ((int64_t)1 << 31), "radix sort: n=%lld out of range", (long long)n);
     CLMGS_REQUIRE(end_bit >= 0 && end_bit <= 32, "radix sort: end_bit=%d", end_bit);
     if (keys_out) *keys_out = keys;
@@ -312,12 +363,12 @@ int clmgs_radix_sort_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t 
     const int64_t ntiles = ceil_div64(n, kTile);
     uint32_t *hist = (uint32_t *)scratch;
     uint32_t *totals = (uint32_t *)((char *)scratch + a256((size_t)ntiles * kBins * sizeof(uint32_t)));
-    FinalOut fin{isect_ids, flatten_ids, depths};
-    if (passes == 0 && isect_ids) {  // nothing to sort on: one pass over a zero-width digit still writes the outputs
-        CLMGS_REQUIRE(vals != flatten_ids, "radix sort: final pass would read the buffer it writes");
-        radix_hist_kernel<<<(unsigned)ntiles, kThreads, 0, st>>>(n, keys, 0, 0u, hist, ntiles);
-        radix_scan_kernel<<<kBins, 1024, 0, st>>>(hist, ntiles, totals);
-        return launch_scatter<true>(n, keys, vals, nullptr, nullptr, 0, 0u, hist, ntiles, totals, fin, st);
+    FinalOut fin{isect_ids, flatten_ids, depths, offsets, tile_n_bits, n_tiles};
+    const int mode = isect_ids ? 1 : (offsets ? 2 : 0);
+    CLMGS_REQUIRE(mode == 0 || passes > 0, "radix sort: fused outputs need at least one key bit");
+    if (mode == 2) {
+        fill_i32_kernel<<<(unsigned)ceil_div64(n_slots, 256), 256, 0, st>>>(offsets, n_slots, (int32_t)n);
+        CLMGS_LAUNCH_OK();
     }
     for (int p = 0; p < passes; ++p) {
         const int shift = 8 * p;
@@ -328,11 +379,17 @@ int clmgs_radix_sort_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t 
         CLMGS_LAUNCH_OK();
         radix_scan_kernel<<<kBins, 1024, 0, st>>>(hist, ntiles, totals);
         CLMGS_LAUNCH_OK();
-        if (last && isect_ids) {
+        if (last && mode != 0) {
             CLMGS_REQUIRE(vals != flatten_ids, "radix sort: final pass would read the buffer it writes");
-            if (int rc = launch_scatter<true>(n, keys, vals, nullptr, nullptr, shift, mask, hist, ntiles, totals, fin, st)) return rc;
+            if (mode == 1) {
+                if (int rc = launch_scatter<1>(n, keys, vals, nullptr, nullptr, shift, mask, hist, ntiles, totals, fin, st)) return rc;
+            } else {
+                if (int rc = launch_scatter<2>(n, keys, vals, nullptr, nullptr, shift, mask, hist, ntiles, totals, fin, st)) return rc;
+                suffix_min_kernel<<<1, 1024, 0, st>>>(offsets, n_slots);
+                CLMGS_LAUNCH_OK();
+            }
         } else {
-            if (int rc = launch_scatter<false>(n, keys, vals, keys_alt, vals_alt, shift, mask, hist, ntiles, totals, fin, st)) return rc;
+            if (int rc = launch_scatter<0>(n, keys, vals, keys_alt, vals_alt, shift, mask, hist, ntiles, totals, fin, st)) return rc;
         }
         uint32_t *tk = keys; keys = keys_alt; keys_alt = tk;
         int32_t *tv = vals; vals = vals_alt; vals_alt = tv;
@@ -352,7 +409,7 @@ CLMGS_EXPORT int clmgs_radix_sort_pairs_u32(int64_t n, uint32_t *keys, uint32_t 
     uint32_t *ko = keys;
     int32_t *vo = vals;
     int rc = clmgs_radix_sort_u32(n, keys, keys_alt, vals, vals_alt, end_bit, scratch, scratch_bytes, as_stream(stream),
-                                  &ko, &vo, nullptr, nullptr, nullptr);
+                                  &ko, &vo, nullptr, nullptr, nullptr, nullptr, 0, 0, 0);
     if (rc) return rc;
     if (result_in_alt) *result_in_alt = (ko == keys_alt) ? 1 : 0;
     return CLMGS_OK;

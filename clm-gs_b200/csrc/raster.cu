@@ -10,10 +10,18 @@
 //  * a batch of 256 Gaussians is staged in shared memory as two float4 + one
 //    float per Gaussian INCLUDING its colour, so the inner loop touches no
 //    global memory (the reference fetches colours from global per hit);
+//  * while a batch is staged, every Gaussian is tested against the tile exactly (minimum of its quadratic
+//    form over the tile's pixel-centre rectangle vs ln(255 * opacity)): the reference's tile lists come from
+//    the square of the 3-sigma radius, so for anisotropic or faint Gaussians most (tile, Gaussian) pairs can
+//    never reach alpha >= 1/255 at any pixel of the tile.  Those are dropped during staging (stable
+//    ballot compaction in shared memory) and the survivors carry the image rows they can touch, which lets
+//    each warp (2 rows) skip the rest with one compare.  The test is conservative (tolerances cover the
+//    rounding of the per-pixel evaluation), so images, last_ids and gradients are unchanged;
 //  * backward: the 9 per-Gaussian partial gradients of a warp are reduced with
 //    a multi-value butterfly (14 shuffles instead of 45) and the 8 finished
 //    sums are added by 8 different lanes in parallel.
 #include "common.cuh"
+#include <math_constants.h>
 
 constexpr int kTile = 16;
 constexpr int kBlock = kTile * kTile;
@@ -32,6 +40,61 @@ __device__ __forceinline__ void tile_range(const RasterArgs &a, const int32_t *t
     end = (t == (int64_t)a.C * a.tile_width * a.tile_height - 1) ? (int)a.n_isects : tile_offsets[t + 1];
 }
 
+
+// Can a Gaussian (mean, conic a/b/c, opacity) reach alpha = min(0.999, o exp(-sigma)) >= 1/255 at ANY pixel centre
+// of the rectangle [xmin,xmax] x [ymin,ymax]?  sigma(d) = 0.5 (a dx^2 + c dy^2) + b dx dy must get below
+// tau = ln(255 o).  Conservative: slack covers the rounding of the per-pixel evaluation, degenerate conics are kept.
+// ylo / yhi bound the rows where sigma <= tau is possible at all (|dy| <= sqrt(2 tau a / det)).
+__device__ __forceinline__ bool tile_touch(float mx, float my, float ca, float cb, float cc, float opac, float xmin,
+                                           float xmax, float ymin, float ymax, float &ylo, float &yhi) {
+    ylo = -CUDART_INF_F; yhi = CUDART_INF_F;
+    const float o255 = opac * 255.0f;
+    if (o255 < 0.999f) return false;  // alpha <= opacity < 1/255 everywhere (NaN opacities fall through)
+    // det = a c - b^2 cancels badly for elongated Gaussians: compensated product difference (error ~1 ulp of det)
+    const float bb = cb * cb;
+    const float det = fmaf(ca, cc, -bb) - fmaf(cb, cb, -bb);
+    if (!(ca > 0.f && cc > 0.f && det > 0.f) || !(o255 < CUDART_INF_F)) return true;
+    const float tau = __logf(o255) * 1.001f + 0.05f;
+    const float ey = sqrtf(2.f * tau * ca / det) * 1.001f + 0.01f;
+    const float ex = sqrtf(2.f * tau * cc / det) * 1.001f + 0.01f;
+    if (!(ey < CUDART_INF_F) || !(ex < CUDART_INF_F)) return true;
+    ylo = my - ey; yhi = my + ey;
+    if (mx + ex < xmin || mx - ex > xmax || yhi < ymin || ylo > ymax) return false;
+    const float dx0 = xmin - mx, dx1 = xmax - mx, dy0 = ymin - my, dy1 = ymax - my;
+    if (dx0 <= 0.f && dx1 >= 0.f && dy0 <= 0.f && dy1 >= 0.f) return true;  // the mean is inside
+    float best = CUDART_INF_F;  // min over the 4 edges of (sigma - rounding allowance)
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+        const float X = e ? dx1 : dx0;
+        const float y = fminf(fmaxf(-cb * X / cc, dy0), dy1);
+        const float q = 0.5f * (ca * X * X + cc * y * y), m = cb * X * y;
+        best = fminf(best, (q + m) - 1e-5f * (q + fabsf(m)));
+        const float Y = e ? dy1 : dy0;
+        const float x = fminf(fmaxf(-cb * Y / ca, dx0), dx1);
+        const float q2 = 0.5f * (ca * x * x + cc * Y * Y), m2 = cb * x * Y;
+        best = fminf(best, (q2 + m2) - 1e-5f * (q2 + fabsf(m2)));
+    }
+    return !(best > tau);
+}
+
+// Stable compaction of the staged batch: thread tr holds one candidate; survivors are written to consecutive
+// slots of the shared arrays in list order.  Returns the number of survivors (same value in every thread).
+__device__ __forceinline__ int stage_compact(bool keep, int tr, int *s_wcnt, int &slot) {
+    const int lane = tr & 31, warp = tr >> 5;
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_wcnt[warp] = __popc(bal);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kBlock / 32; ++w) {
+        const int c = s_wcnt[w];
+        if (w < warp) before += c;
+        total += c;
+    }
+    slot = before + __popc(bal & ((1u << lane) - 1u));
+    return total;
+}
+
 template <bool HAS_BG>
 __global__ void __launch_bounds__(kBlock)
 raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float *__restrict__ conics,
@@ -41,7 +104,8 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
                   float *__restrict__ render_alphas, int32_t *__restrict__ last_ids) {
     __shared__ float4 s_a[kBlock];  // x, y, conic.x, conic.y
     __shared__ float4 s_b[kBlock];  // conic.z, opacity, r, g
-    __shared__ float s_c[kBlock];   // b
+    __shared__ float4 s_c[kBlock];  // b, first row, last row (pixel-centre y), position in the batch
+    __shared__ int s_wcnt[kBlock / 32];
     const int cam = blockIdx.z;
     const int tile_id = blockIdx.y * a.tile_width + blockIdx.x;
     const int i = blockIdx.y * kTile + threadIdx.y;
@@ -53,6 +117,10 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
     int start, end;
     tile_range(a, tile_offsets, cam, tile_id, start, end);
     const int num_batches = (end - start + kBlock - 1) / kBlock;
+    // pixel centres of this tile / of this warp's two rows
+    const float txmin = (float)(blockIdx.x * kTile) + 0.5f, txmax = (float)min(blockIdx.x * kTile + kTile - 1, a.width - 1) + 0.5f;
+    const float tymin = (float)(blockIdx.y * kTile) + 0.5f, tymax = (float)min(blockIdx.y * kTile + kTile - 1, a.height - 1) + 0.5f;
+    const float wy0 = (float)(blockIdx.y * kTile + 2 * (tr >> 5)) + 0.5f, wy1 = wy0 + 1.0f;
 
     float T = 1.0f, r = 0.f, g = 0.f, b = 0.f;
     int cur_idx = 0;
@@ -60,18 +128,26 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
         if (__syncthreads_count(done) >= kBlock) break;
         const int batch_start = start + kBlock * bt;
         const int idx = batch_start + tr;
+        bool keep = false;
+        float4 A, Bv, Cv;
         if (idx < end) {
             const int gid = flatten_ids[idx];
             const float2 xy = means2d[gid];
             const float *cn = conics + 3 * (int64_t)gid;
             const float *cl = colors + 3 * (int64_t)gid;
-            s_a[tr] = make_float4(xy.x, xy.y, cn[0], cn[1]);
-            s_b[tr] = make_float4(cn[2], opacities[gid], cl[0], cl[1]);
-            s_c[tr] = cl[2];
+            A = make_float4(xy.x, xy.y, cn[0], cn[1]);
+            Bv = make_float4(cn[2], opacities[gid], cl[0], cl[1]);
+            float ylo, yhi;
+            keep = tile_touch(A.x, A.y, A.z, A.w, Bv.x, Bv.y, txmin, txmax, tymin, tymax, ylo, yhi);
+            Cv = make_float4(cl[2], ylo, yhi, __int_as_float(tr));
         }
+        int slot;
+        const int batch_size = stage_compact(keep, tr, s_wcnt, slot);
+        if (keep) { s_a[slot] = A; s_b[slot] = Bv; s_c[slot] = Cv; }
         __syncthreads();
-        const int batch_size = min(kBlock, end - batch_start);
         for (int t = 0; t < batch_size && !done; ++t) {
+            const float4 Cc = s_c[t];
+            if (wy1 < Cc.y || wy0 > Cc.z) continue;  // cannot reach 1/255 on this warp's rows (warp-uniform)
             const float4 A = s_a[t];
             const float4 Bv = s_b[t];
             const float dx = A.x - px, dy = A.y - py;
@@ -81,8 +157,8 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
             const float next_T = T * (1.0f - alpha);
             if (next_T <= 1e-4f) { done = true; break; }
             const float vis = alpha * T;
-            r += Bv.z * vis; g += Bv.w * vis; b += s_c[t] * vis;
-            cur_idx = batch_start + t;
+            r += Bv.z * vis; g += Bv.w * vis; b += Cc.x * vis;
+            cur_idx = batch_start + __float_as_int(Cc.w);
             T = next_T;
         }
     }
@@ -162,7 +238,7 @@ __device__ __forceinline__ int inside_any(int warp_bin_final, int start) {
 }
 
 template <bool HAS_BG, bool ABSGRAD>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, 4)
 raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float *__restrict__ conics,
                   const float *__restrict__ colors, const float *__restrict__ opacities,
                   const float *__restrict__ backgrounds, const int32_t *__restrict__ tile_offsets,
@@ -174,7 +250,8 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
     __shared__ int s_id[kBlock];
     __shared__ float4 s_a[kBlock];  // x, y, conic.x, conic.y
     __shared__ float4 s_b[kBlock];  // conic.z, opacity, r, g
-    __shared__ float s_c[kBlock];   // b
+    __shared__ float4 s_c[kBlock];  // b, first row, last row (pixel-centre y), position in the batch
+    __shared__ int s_wcnt[kBlock / 32];
     const int cam = blockIdx.z;
     const int tile_id = blockIdx.y * a.tile_width + blockIdx.x;
     const int i = blockIdx.y * kTile + threadIdx.y;
@@ -216,29 +293,42 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
     const int tile_last = s_tile_last;
     if (tile_last < start) return;  // nothing was blended anywhere in this tile
     const int first_batch = (end - 1 - tile_last) / kBlock;
+    const float txmin = (float)(blockIdx.x * kTile) + 0.5f, txmax = (float)min(blockIdx.x * kTile + kTile - 1, a.width - 1) + 0.5f;
+    const float tymin = (float)(blockIdx.y * kTile) + 0.5f, tymax = (float)min(blockIdx.y * kTile + kTile - 1, a.height - 1) + 0.5f;
+    const float wy0 = (float)(blockIdx.y * kTile + 2 * (tr >> 5)) + 0.5f, wy1 = wy0 + 1.0f;
 
     for (int bt = first_batch; bt < num_batches; ++bt) {
         __syncthreads();
         const int batch_end = end - 1 - kBlock * bt;  // absolute index of the back-most entry of this batch
-        const int batch_size = min(kBlock, batch_end + 1 - start);
         const int idx = batch_end - tr;
+        bool keep = false;
+        float4 sA, sB, sC;
+        int gid_s = 0;
         if (idx >= start) {
-            const int gid = flatten_ids[idx];
-            s_id[tr] = gid;
-            const float2 xy = means2d[gid];
-            const float *cn = conics + 3 * (int64_t)gid;
-            const float *cl = colors + 3 * (int64_t)gid;
-            s_a[tr] = make_float4(xy.x, xy.y, cn[0], cn[1]);
-            s_b[tr] = make_float4(cn[2], opacities[gid], cl[0], cl[1]);
-            s_c[tr] = cl[2];
+            gid_s = flatten_ids[idx];
+            const float2 xy = means2d[gid_s];
+            const float *cn = conics + 3 * (int64_t)gid_s;
+            const float *cl = colors + 3 * (int64_t)gid_s;
+            sA = make_float4(xy.x, xy.y, cn[0], cn[1]);
+            sB = make_float4(cn[2], opacities[gid_s], cl[0], cl[1]);
+            float ylo, yhi;
+            keep = tile_touch(sA.x, sA.y, sA.z, sA.w, sB.x, sB.y, txmin, txmax, tymin, tymax, ylo, yhi);
+            sC = make_float4(cl[2], ylo, yhi, __int_as_float(tr));
         }
+        int slot;
+        const int batch_size = stage_compact(keep, tr, s_wcnt, slot);
+        if (keep) { s_id[slot] = gid_s; s_a[slot] = sA; s_b[slot] = sB; s_c[slot] = sC; }
         __syncthreads();
-        for (int t = max(0, batch_end - warp_bin_final); t < batch_size; ++t) {
+        const int t_lo = batch_end - warp_bin_final;  // entries with a smaller position are behind every pixel's last
+        for (int tc = 0; tc < batch_size; ++tc) {
+            const float4 Cc = s_c[tc];
+            const int t = __float_as_int(Cc.w);  // position in the (uncompacted) batch
+            if (t < t_lo || wy1 < Cc.y || wy0 > Cc.z) continue;  // warp-uniform
             bool valid = inside && (batch_end - t <= bin_final);
             float alpha = 0.f, opac = 0.f, vis = 0.f, dx = 0.f, dy = 0.f;
             float4 A, Bv;
             if (valid) {
-                A = s_a[t]; Bv = s_b[t];
+                A = s_a[tc]; Bv = s_b[tc];
                 opac = Bv.y;
                 dx = A.x - px; dy = A.y - py;
                 const float sigma = 0.5f * (A.z * dx * dx + Bv.x * dy * dy) + A.w * dx * dy;
@@ -250,7 +340,7 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
             float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // rgb, conic xyz, xy
             float v_opa = 0.f, v_ax = 0.f, v_ay = 0.f;
             if (valid) {
-                const float cb = s_c[t];
+                const float cb = Cc.x;
                 const float ra = 1.0f / (1.0f - alpha);
                 T *= ra;
                 const float fac = alpha * T;
@@ -273,7 +363,7 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
             const float red = butterfly8(v, lane);
             v_opa = warp_sum(v_opa);
             if (ABSGRAD) { v_ax = warp_sum(v_ax); v_ay = warp_sum(v_ay); }
-            const int64_t gid = s_id[t];
+            const int64_t gid = s_id[tc];
             if ((lane & 3) == 0) {
                 const int k = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
                 float *dst = k < 3 ? v_colors + 3 * gid + k : (k < 6 ? v_conics + 3 * gid + (k - 3) : v_means2d + 2 * gid + (k - 6));

@@ -404,6 +404,16 @@ int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, floa
                                        float b2, float eps, int64_t step, float scale,
                                        int n_threads, volatile int64_t *host_progress);
 
+/* What the rasteriser consumes, in one call: clmgs_isect_emit_sort (sorted) + clmgs_isect_offset_encode
+ * without materialising the 64-bit isect_ids -- the last radix pass writes flatten_ids [n_isects] at the
+ * sorted positions and marks the first position of every (camera, tile) key; tile_offsets [C, th, tw] is
+ * identical to isect_offset_encode's (CSRC/isect_tiles.cu:234-301).  Scratch as clmgs_isect_emit_sort. */
+int clmgs_isect_sorted_offsets(int C, int64_t N, const int64_t *camera_ids, const float *means2d,
+                               const int32_t *radii, const float *depths, const int64_t *cum_tiles,
+                               int tile_size, int tile_width, int tile_height, int64_t n_isects,
+                               int32_t *flatten_ids, int32_t *tile_offsets, void *scratch,
+                               size_t scratch_bytes, void *stream);
+
 /* Stable LSD radix sort of (uint32 key, int32 value) pairs on key bits [0, end_bit), 8-bit digits,
  * hand-written (csrc/radix.cu) -- the sort under clmgs_isect_emit_sort, which replaces the reference's
  * cub::DeviceRadixSort::SortPairs call (CSRC/isect_tiles.cu:186-229).  Ping-pongs between the two buffer

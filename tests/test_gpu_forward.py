@@ -173,3 +173,21 @@ def test_radix_sort_pairs_is_a_stable_sort(n, end_bit, key_bits):
     order = np.argsort(keys & np.uint32((1 << end_bit) - 1 if end_bit < 32 else 0xffffffff), kind="stable")
     np.testing.assert_array_equal(k.cpu().numpy().view(np.uint32), keys[order])
     np.testing.assert_array_equal(v.cpu().numpy(), vals[order])
+
+
+@pytest.mark.parametrize("n,W,H", [(30_000, 320, 208), (5000, 1237, 822), (2000, 16, 16), (300, 3840, 2160), (0, 64, 64)])
+def test_isect_sorted_offsets_equals_sort_plus_offset_encode(n, W, H):
+    """The engine's fused tile stage (no isect_ids) must give the same flatten_ids and offsets as the
+    reference-shaped pair isect_tiles + isect_offset_encode, which is checked against the oracle above."""
+    rng = np.random.default_rng(n + W)
+    tw, th = (W + 15) // 16, (H + 15) // 16
+    means2d = (rng.random((1, n, 2)) * np.array([W, H]) * 1.2 - 0.1 * np.array([W, H])).astype(np.float32)
+    radii = rng.integers(0, 40, (1, n)).astype(np.int32)
+    depths = rng.choice(rng.random(max(n // 3, 1)).astype(np.float32) * 10 + 0.1, (1, n)).astype(np.float32)  # ties
+    m, r, d = (torch.from_numpy(x).to(DEV) for x in (means2d, radii, depths))
+    _, ids, flat = ops.isect_tiles(m, r, d, 16, tw, th)
+    off = ops.isect_offset_encode(ids, 1, tw, th)
+    flat2, off2, n_isects = ops.isect_sorted_offsets(m, r, d, 16, tw, th)
+    assert n_isects == flat.shape[0]
+    assert torch.equal(flat, flat2)
+    assert torch.equal(off, off2)
