@@ -537,16 +537,35 @@ perm_emit_kernel(int64_t total, int64_t N, const int64_t *__restrict__ camera_id
         tile_rect(means2d[2 * (int64_t)idx], means2d[2 * (int64_t)idx + 1], radii[idx], tile_size, tw, th, x0, y0, x1, y1);
         v = (int64_t)(y1 - y0) * (x1 - x0);
     }
-    int64_t cur = block_sums[blockIdx.x] + block_excl_scan_1024<int64_t>(v, s_warp, &tot);
-    if (v == 0) return;
-    const uint32_t cid = (uint32_t)(camera_ids ? camera_ids[idx] : idx / N);
+    const int64_t cur = block_sums[blockIdx.x] + block_excl_scan_1024<int64_t>(v, s_warp, &tot);
+    // Warp-cooperative expansion: the 32 runs of a warp are consecutive in the output, so the warp writes them as
+    // one stream -- entry e of the warp goes to lane e % 32 (coalesced 128-byte stores) and finds its Gaussian by
+    // a 5-step search over the lanes' start offsets.  (One thread per run wrote 2 x 4 bytes at 32 scattered places.)
+    const int lane = threadIdx.x & 31;
+    const int64_t warp_base = __shfl_sync(0xffffffffu, cur, 0);
+    const int p = (int)(cur - warp_base);                       // start of this lane's run inside the warp's stream
+    const int total_w = __shfl_sync(0xffffffffu, p + (int)v, 31);
+    const uint32_t cid = (j < total && v > 0) ? (uint32_t)(camera_ids ? camera_ids[idx] : idx / N) : 0u;
     const uint32_t cid_enc = cid << tile_n_bits;
-    for (int i = y0; i < y1; ++i)
-        for (int jj = x0; jj < x1; ++jj) {
-            tkeys[cur] = cid_enc | (uint32_t)(i * tw + jj);
-            vals[cur] = idx;
-            ++cur;
+    const int wdt = x1 - x0;
+    for (int e0 = 0; e0 < total_w; e0 += 32) {
+        const int e = e0 + lane;
+        int owner = 0, p_owner = __shfl_sync(0xffffffffu, p, 0);
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {  // largest lane whose run starts at or before e
+            const int cand = owner + step;
+            const int pc = __shfl_sync(0xffffffffu, p, cand & 31);
+            if (cand < 32 && pc <= e) { owner = cand; p_owner = pc; }
         }
+        const int ox0 = __shfl_sync(0xffffffffu, x0, owner), oy0 = __shfl_sync(0xffffffffu, y0, owner);
+        const int ow = __shfl_sync(0xffffffffu, wdt, owner), oidx = __shfl_sync(0xffffffffu, idx, owner);
+        const uint32_t oenc = __shfl_sync(0xffffffffu, cid_enc, owner);
+        if (e < total_w) {
+            const int r = e - p_owner, row = r / ow, colm = r - row * ow;
+            tkeys[warp_base + e] = oenc | (uint32_t)((oy0 + row) * tw + (ox0 + colm));
+            vals[warp_base + e] = oidx;
+        }
+    }
 }
 
 static inline size_t a256(size_t x) { return (x + 255) & ~(size_t)255; }
