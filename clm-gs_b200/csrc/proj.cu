@@ -37,7 +37,8 @@ __device__ __forceinline__ void camera_from_smem(const float *s, Camera &cam) {
 }
 
 __device__ __forceinline__ void load_gaussian(const float *means, const float *scales, const float *quats,
-                                              int activated, int64_t i, float mean[3], float covar[9]) {
+                                              int activated, int64_t i, float mean[3], float covar[9],
+                                              float *smax2 = nullptr) {
     float s[3], q[4];
 #pragma unroll
     for (int k = 0; k < 3; ++k) { mean[k] = __ldg(means + 3 * i + k); s[k] = __ldg(scales + 3 * i + k); }
@@ -52,6 +53,40 @@ __device__ __forceinline__ void load_gaussian(const float *means, const float *s
         for (int k = 0; k < 4; ++k) q[k] = qn[k];
     }
     quat_scale_to_covar(q, s, covar);
+    if (smax2) { float m = fmaxf(fmaxf(fabsf(s[0]), fabsf(s[1])), fabsf(s[2])); *smax2 = m * m; }
+}
+
+// Cheap sufficient condition for project_one<true>() == false, evaluated before the covariance is carried
+// into the camera frame (most (camera, Gaussian) pairs of a large scene fail here: ~98 % at C4).  It rejects only
+// what the full test rejects: behind / beyond the planes (the same comparison on the same depth), or the disc
+// test with an upper bound R on the radius.  lambda_max(J cov_c J^T + eps I) <= |J|_F^2 smax^2 + eps, the packed
+// radius rule uses at most lambda_max + sqrt(0.1), radius = ceil(3 sqrt(.)) <= 3 sqrt(.) + 1; 2 % slack covers
+// rounding (the view rotation is assumed rigid up to a uniform scale).  mean2d is computed with the operations of project_one, so "mean2d + R <= 0" implies the full
+// test's "mean2d + radius <= 0".  Non-finite values fall through to the full test.
+__device__ __forceinline__ bool surely_culled(const float mean[3], float smax2, const Camera &cam, int width, int height,
+                                              float eps2d, float near_plane, float far_plane) {
+    const float *R = cam.R;
+    float mc[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+        mc[r] = ((R[r * 3 + 0] * mean[0] + R[r * 3 + 1] * mean[1]) + R[r * 3 + 2] * mean[2]) + cam.t[r];
+    if (mc[2] < near_plane || mc[2] > far_plane) return true;
+    const float fx = cam.fx, fy = cam.fy, x = mc[0], y = mc[1], z = mc[2];
+    const float lim_x = 1.3f * (0.5f * (float)width / fx), lim_y = 1.3f * (0.5f * (float)height / fy);
+    const float rz = 1.f / z, rz2 = rz * rz;
+    const float tx = z * fminf(lim_x, fmaxf(-lim_x, x * rz));
+    const float ty = z * fminf(lim_y, fmaxf(-lim_y, y * rz));
+    const float J00 = fx * rz, J11 = fy * rz, J02 = (-fx * tx) * rz2, J12 = (-fy * ty) * rz2;
+    const float jf2 = (J00 * J00 + J11 * J11) + (J02 * J02 + J12 * J12);
+    // world->camera rotation taken as a similarity (|R|_F^2 / 3 = its squared scale, 1 for a rigid camera)
+    float rs = 0.f;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) rs += R[k] * R[k];
+    rs *= (1.0f / 3.0f);
+    const float Rb = 3.06f * sqrtf(jf2 * (smax2 * rs) + eps2d + 0.32f) + 1.02f;
+    const float mx = (fx * x) * rz + cam.cx, my = (fy * y) * rz + cam.cy;
+    if (!(Rb < 1e30f)) return false;
+    return mx + Rb <= 0.f || mx - Rb >= (float)width || my + Rb <= 0.f || my - Rb >= (float)height;
 }
 
 // ---------------------------------------------------------------------------
@@ -72,11 +107,12 @@ cull_count_kernel(const float *__restrict__ means, const float *__restrict__ sca
     int64_t i = (int64_t)blockIdx.x * kCullThreads + threadIdx.x;
     uint64_t word = 0;
     if (i < N) {
-        float mean[3], covar[9];
-        load_gaussian(means, scales, quats, activated, i, mean, covar);
+        float mean[3], covar[9], smax2;
+        load_gaussian(means, scales, quats, activated, i, mean, covar, &smax2);
         for (int c = 0; c < B; ++c) {
             Camera cam;
             camera_from_smem(s_cam + c * 16, cam);
+            if (surely_culled(mean, smax2, cam, p.width, p.height, p.eps2d, p.near_plane, p.far_plane)) continue;
             Projected o;
             bool ok = project_one<true>(mean, covar, cam, p.width, p.height, p.eps2d, p.near_plane,
                                         p.far_plane, p.radius_clip, o);
