@@ -63,8 +63,9 @@ __device__ __forceinline__ void load_gaussian(const float *means, const float *s
 // radius rule uses at most lambda_max + sqrt(0.1), radius = ceil(3 sqrt(.)) <= 3 sqrt(.) + 1; 2 % slack covers
 // rounding (the view rotation is assumed rigid up to a uniform scale).  mean2d is computed with the operations of project_one, so "mean2d + R <= 0" implies the full
 // test's "mean2d + radius <= 0".  Non-finite values fall through to the full test.
-__device__ __forceinline__ bool surely_culled(const float mean[3], float smax2, const Camera &cam, int width, int height,
-                                              float eps2d, float near_plane, float far_plane) {
+__device__ __forceinline__ bool surely_culled(const float mean[3], float smax2, const Camera &cam, float lim_x,
+                                              float lim_y, float rs, int width, int height, float eps2d,
+                                              float near_plane, float far_plane) {
     const float *R = cam.R;
     float mc[3];
 #pragma unroll
@@ -72,17 +73,12 @@ __device__ __forceinline__ bool surely_culled(const float mean[3], float smax2, 
         mc[r] = ((R[r * 3 + 0] * mean[0] + R[r * 3 + 1] * mean[1]) + R[r * 3 + 2] * mean[2]) + cam.t[r];
     if (mc[2] < near_plane || mc[2] > far_plane) return true;
     const float fx = cam.fx, fy = cam.fy, x = mc[0], y = mc[1], z = mc[2];
-    const float lim_x = 1.3f * (0.5f * (float)width / fx), lim_y = 1.3f * (0.5f * (float)height / fy);
     const float rz = 1.f / z, rz2 = rz * rz;
     const float tx = z * fminf(lim_x, fmaxf(-lim_x, x * rz));
     const float ty = z * fminf(lim_y, fmaxf(-lim_y, y * rz));
     const float J00 = fx * rz, J11 = fy * rz, J02 = (-fx * tx) * rz2, J12 = (-fy * ty) * rz2;
     const float jf2 = (J00 * J00 + J11 * J11) + (J02 * J02 + J12 * J12);
-    // world->camera rotation taken as a similarity (|R|_F^2 / 3 = its squared scale, 1 for a rigid camera)
-    float rs = 0.f;
-#pragma unroll
-    for (int k = 0; k < 9; ++k) rs += R[k] * R[k];
-    rs *= (1.0f / 3.0f);
+    // rs: world->camera rotation taken as a similarity (|R|_F^2 / 3 = its squared scale, 1 for a rigid camera)
     const float Rb = 3.06f * sqrtf(jf2 * (smax2 * rs) + eps2d + 0.32f) + 1.02f;
     const float mx = (fx * x) * rz + cam.cx, my = (fy * y) * rz + cam.cy;
     if (!(Rb < 1e30f)) return false;
@@ -101,18 +97,40 @@ cull_count_kernel(const float *__restrict__ means, const float *__restrict__ sca
                   W *__restrict__ bitmap, int32_t *__restrict__ block_counts /* [B][gridDim.x] */) {
     __shared__ float s_cam[kMaxCams * 16];
     __shared__ int s_cnt[kMaxCams];
+    __shared__ float s_pre[kMaxCams * 4];  // per camera: 1.3 tan(fov/2) in x and y, squared scale of the rotation
     stage_cameras(s_cam, viewmats, Ks, B);
     if (threadIdx.x < kMaxCams) s_cnt[threadIdx.x] = 0;
+    if (threadIdx.x < B) {
+        const int c = threadIdx.x;
+        s_pre[4 * c] = 1.3f * (0.5f * (float)p.width / Ks[c * 9 + 0]);
+        s_pre[4 * c + 1] = 1.3f * (0.5f * (float)p.height / Ks[c * 9 + 4]);
+        float rs = 0.f;
+        for (int r = 0; r < 3; ++r)
+            for (int k = 0; k < 3; ++k) rs += viewmats[c * 16 + r * 4 + k] * viewmats[c * 16 + r * 4 + k];
+        s_pre[4 * c + 2] = rs * (1.0f / 3.0f);
+    }
     __syncthreads();
     int64_t i = (int64_t)blockIdx.x * kCullThreads + threadIdx.x;
     uint64_t word = 0;
     if (i < N) {
         float mean[3], covar[9], smax2;
         load_gaussian(means, scales, quats, activated, i, mean, covar, &smax2);
+        // Pass 1 (no divergence): cheap sufficient rejection for every camera.  Pass 2: the full test only for
+        // the candidates, each lane walking its OWN candidate list -- with a few per cent of the pairs surviving,
+        // running the full test whenever any lane of the warp survives would still execute it for half the pairs.
+        uint64_t cand = 0;
         for (int c = 0; c < B; ++c) {
             Camera cam;
             camera_from_smem(s_cam + c * 16, cam);
-            if (surely_culled(mean, smax2, cam, p.width, p.height, p.eps2d, p.near_plane, p.far_plane)) continue;
+            if (!surely_culled(mean, smax2, cam, s_pre[4 * c], s_pre[4 * c + 1], s_pre[4 * c + 2], p.width, p.height,
+                               p.eps2d, p.near_plane, p.far_plane))
+                cand |= (uint64_t)1 << c;
+        }
+        while (cand) {
+            const int c = __ffsll((long long)cand) - 1;
+            cand &= cand - 1;
+            Camera cam;
+            camera_from_smem(s_cam + c * 16, cam);
             Projected o;
             bool ok = project_one<true>(mean, covar, cam, p.width, p.height, p.eps2d, p.near_plane,
                                         p.far_plane, p.radius_clip, o);
