@@ -415,8 +415,11 @@ def run_reference(a):
     return dict(impl="reference", metric=METRIC, value=v, unit=UNIT, n_gpus=a.gpus, steps=a.steps, warmup=a.warmup,
                 ms_per_step=round(1000.0 / v, 1), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
                 data="synthetic",
-                config=dict(workload="%s: %d Gaussians, %dx%d, batch %d (CPU, bounded sample extrapolated)"
-                            % (spec.name, N, spec.width, spec.height, bsz)),
+                config=dict(workload="%s: %d Gaussians, %dx%d, batch %d cameras/iteration, SH degree 3, "
+                                     "clm_offload (48-float SH rows + Adam state in pinned host memory)"
+                                     % (spec.name, N, spec.width, spec.height, bsz),
+                            note="reference arm: CPU port on the host cores, bounded sample extrapolated to this workload "
+                                 "(see cpu_baseline.sample)"),
                 cpu_baseline=cb, e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
 
 
