@@ -73,8 +73,7 @@ ssim_pass1_kernel(int H, int W, const float *img, int64_t img_plane_stride, int6
                   float *maps /* [P][3][H][W] */, double *sums /* [0]=ssim, [1]=l1 */, int want_maps) {
     __shared__ float s1[TS][TS + 1];
     __shared__ float s2[TS][TS + 1];
-    __shared__ float sp[TS][TS + 1];
-    __shared__ float tmp[TS][TB + 1];
+    __shared__ float tmp5[5][TS][TB + 1];
     __shared__ float red[2][32];
     const int tid = threadIdx.y * TB + threadIdx.x;
     const int plane = blockIdx.z;
@@ -92,17 +91,30 @@ ssim_pass1_kernel(int H, int W, const float *img, int64_t img_plane_stride, int6
         s1[ly][lx] = a;
         s2[ly][lx] = b;
     }
-    const float mu1 = sep_conv(s1, tmp, tid);
-    const float mu2 = sep_conv(s2, tmp, tid);
+    // all five moments in ONE separable pass: the horizontal sweep forms x1^2, x2^2, x1 x2 on the fly (same
+    // operations, same order per map as five separate convolutions, so results are unchanged), two barriers in all
     __syncthreads();
-    for (int e = tid; e < TS * TS; e += TB * TB) { int ly = e / TS, lx = e - ly * TS; sp[ly][lx] = s1[ly][lx] * s1[ly][lx]; }
-    const float e11 = sep_conv(sp, tmp, tid);
+    for (int e = tid; e < TS * TB; e += TB * TB) {
+        const int y = e / TB, x = e - y * TB;
+        float h1 = 0.f, h2 = 0.f, h11 = 0.f, h22 = 0.f, h12 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 11; ++k) {
+            const float a = s1[y][x + k], b = s2[y][x + k], w = c_gauss[k];
+            h1 += w * a; h2 += w * b; h11 += w * (a * a); h22 += w * (b * b); h12 += w * (a * b);
+        }
+        tmp5[0][y][x] = h1; tmp5[1][y][x] = h2; tmp5[2][y][x] = h11; tmp5[3][y][x] = h22; tmp5[4][y][x] = h12;
+    }
     __syncthreads();
-    for (int e = tid; e < TS * TS; e += TB * TB) { int ly = e / TS, lx = e - ly * TS; sp[ly][lx] = s2[ly][lx] * s2[ly][lx]; }
-    const float e22 = sep_conv(sp, tmp, tid);
-    __syncthreads();
-    for (int e = tid; e < TS * TS; e += TB * TB) { int ly = e / TS, lx = e - ly * TS; sp[ly][lx] = s1[ly][lx] * s2[ly][lx]; }
-    const float e12 = sep_conv(sp, tmp, tid);
+    float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+    {
+        const int ty = threadIdx.y, tx = threadIdx.x;
+#pragma unroll
+        for (int k = 0; k < 11; ++k) {
+            const float w = c_gauss[k];
+            mu1 += w * tmp5[0][ty + k][tx]; mu2 += w * tmp5[1][ty + k][tx]; e11 += w * tmp5[2][ty + k][tx];
+            e22 += w * tmp5[3][ty + k][tx]; e12 += w * tmp5[4][ty + k][tx];
+        }
+    }
 
     const int py = blockIdx.y * TB + threadIdx.y, px = blockIdx.x * TB + threadIdx.x;
     const bool inside = py < H && px < W;
@@ -139,14 +151,14 @@ __global__ void __launch_bounds__(TB *TB)
 ssim_pass2_kernel(int H, int W, const float *img, int64_t img_plane_stride, int64_t img_row_stride,
                   int img_pix_stride, const GT *gt, const float *maps, float l1w, float *v_img) {
     __shared__ float sm[TS][TS + 1];
-    __shared__ float tmp[TS][TB + 1];
+    __shared__ float tmp3[3][TS][TB + 1];
     const int tid = threadIdx.y * TB + threadIdx.x;
     const int plane = blockIdx.z;
     const int y0 = blockIdx.y * TB - HALO, x0 = blockIdx.x * TB - HALO;
     const int64_t HW = (int64_t)H * W;
     float acc[3];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
+    for (int k = 0; k < 3; ++k) {  // horizontal sweeps share one staging tile; one vertical sweep for all three
         const float *mp = maps + ((int64_t)plane * 3 + k) * HW;
         __syncthreads();
         for (int e = tid; e < TS * TS; e += TB * TB) {
@@ -154,7 +166,19 @@ ssim_pass2_kernel(int H, int W, const float *img, int64_t img_plane_stride, int6
             int y = y0 + ly, x = x0 + lx;
             sm[ly][lx] = (y >= 0 && y < H && x >= 0 && x < W) ? mp[(int64_t)y * W + x] : 0.f;
         }
-        acc[k] = sep_conv(sm, tmp, tid);
+        __syncthreads();
+        for (int e = tid; e < TS * TB; e += TB * TB) {
+            const int y = e / TB, x = e - y * TB;
+            tmp3[k][y][x] = conv_h(sm, y, x);
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float v = 0.f;
+#pragma unroll
+        for (int t = 0; t < 11; ++t) v += c_gauss[t] * tmp3[k][threadIdx.y + t][threadIdx.x];
+        acc[k] = v;
     }
     const int py = blockIdx.y * TB + threadIdx.y, px = blockIdx.x * TB + threadIdx.x;
     if (py >= H || px >= W) return;
