@@ -3,7 +3,8 @@
 // C2=9e-4: the fused kernels of clm_kernels (CK/ssim.cu:187-366) plus the
 // torch.compile'd loss_combined (strategies/base_engine.py:79-94) in one place.
 //
-// Pass 1 (per plane, 32x32 output tile + 5-pixel halo in shared memory):
+// Pass 1 (per plane, 32x32 output tile + 5-pixel halo in shared memory; all five moments in one horizontal and
+//   one vertical sweep):
 //   mu1, mu2, E[x^2], E[y^2], E[xy] -> ssim value and the three partial
 //   derivative maps, already multiplied by d loss / d ssim_map; block-reduced
 //   SSIM and L1 sums go to two double accumulators.
@@ -37,22 +38,6 @@ __device__ __forceinline__ float conv_h(const float (*tile)[TS + 1], int y, int 
     float v = 0.f;
 #pragma unroll
     for (int k = 0; k < 11; ++k) v += c_gauss[k] * tile[y][x + k];
-    return v;
-}
-
-// separable conv of the 42x42 smem tile `src` (already loaded); tmp is 42x32.
-// returns the value at this thread's output pixel (ty, tx).
-__device__ __forceinline__ float sep_conv(const float (*src)[TS + 1], float (*tmp)[TB + 1], int tid) {
-    __syncthreads();  // src complete / previous tmp consumers done
-    for (int e = tid; e < TS * TB; e += TB * TB) {
-        int y = e / TB, x = e - y * TB;
-        tmp[y][x] = conv_h(src, y, x);
-    }
-    __syncthreads();
-    int ty = tid / TB, tx = tid - ty * TB;
-    float v = 0.f;
-#pragma unroll
-    for (int k = 0; k < 11; ++k) v += c_gauss[k] * tmp[ty + k][tx];
     return v;
 }
 

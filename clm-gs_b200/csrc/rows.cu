@@ -119,14 +119,6 @@ template <typename W>
 __device__ __forceinline__ bool test_bit(const void *bitmap, int64_t i, int bit) {
     return (((const W *)bitmap)[i] >> bit) & 1;
 }
-__device__ __forceinline__ bool test_bit_any(const void *bitmap, int wb, int64_t i, int bit) {
-    switch (wb) {
-        case 1: return test_bit<uint8_t>(bitmap, i, bit);
-        case 2: return test_bit<uint16_t>(bitmap, i, bit);
-        case 4: return test_bit<uint32_t>(bitmap, i, bit);
-        default: return test_bit<uint64_t>(bitmap, i, bit);
-    }
-}
 
 // position of `id` in the ascending array ids[0..n) (it is known to be present)
 __device__ __forceinline__ int32_t rank_of(const int64_t *__restrict__ ids, int64_t n, int64_t id) {
