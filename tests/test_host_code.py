@@ -123,3 +123,30 @@ def test_cpu_adam_zero_grad_segments_match_reading_zero_rows():
         outs.append((pp, mm, vv))
     for a, b in zip(outs[0], outs[1]):
         np.testing.assert_array_equal(a, b)
+
+
+def test_new_entry_points_validate_arguments_without_a_gpu():
+    """Argument checks come before any CUDA call, so they can be exercised on a machine without a GPU."""
+    from clmgs import _lib
+    import pytest
+    L = _lib.lib()
+    with pytest.raises(_lib.ClmgsError, match="out of range"):
+        L.call("clmgs_densify_classify", -1, None, None, None, None, 0.0, 0.0, 0.0, 0.0, 0, None, None)
+    with pytest.raises(_lib.ClmgsError, match="null pointer"):
+        L.call("clmgs_densify_classify", 10, None, None, None, None, 0.0, 0.0, 0.0, 0.0, 0, None, None)
+    with pytest.raises(_lib.ClmgsError, match="totals"):
+        L.call("clmgs_densify_plan", 10, None, None, None, None, None, 0, None)
+    with pytest.raises(_lib.ClmgsError, match="bad counts"):
+        L.call("clmgs_densify_apply", 1, 0, 2, 1, None, None, None, None, None, None)  # more kept parents than parents
+    with pytest.raises(_lib.ClmgsError, match="max_opacity"):
+        L.call("clmgs_reset_opacity", 4, np.zeros(4, np.float32), np.zeros(4, np.float32), np.zeros(4, np.float32),
+               1.5, None)
+    with pytest.raises(_lib.ClmgsError, match="null pointer"):
+        L.call("clmgs_radix_sort_pairs_u32", 8, None, None, None, None, 32, None, 0, None, None)
+    with pytest.raises(_lib.ClmgsError, match="null output"):
+        L.call("clmgs_isect_sorted_offsets", 1, 8, None, None, None, None, None, 16, 2, 2, 4, None, None, None, 0, None)
+    # sizes that need no device work succeed without touching the GPU
+    assert L.call("clmgs_densify_classify", 0, None, None, None, None, 0.0, 0.0, 0.0, 0.0, 0, None, None) == 0
+    assert L.call("clmgs_radix_sort_pairs_u32", 0, None, None, None, None, 32, None, 0, None, None) == 0
+    assert L.call("clmgs_densify_plan_scratch_bytes", 1_000_000) > 0
+    assert L.call("clmgs_radix_sort_pairs_u32_scratch_bytes", 46_000_000) >= (46_000_000 // 4096) * 256 * 4
