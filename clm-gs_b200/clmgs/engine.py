@@ -268,6 +268,17 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     cams = [batched_cameras[i] for i in ordered_cams]
     bitmap = oc["ordered_bitmap"]
 
+    # Lazy dense Adam (opt-in): rows no camera touches skip this step's zero-gradient update; the rows this batch
+    # does touch first replay whatever they skipped earlier -- before their coefficients are read by the GPU.
+    lazy = bool(getattr(args, "lazy_dense_adam", False)) and not args.sparse_adam
+    if lazy:
+        assert not pipe, "lazy_dense_adam and pipeline_host_adam are not combined"
+        ca = gaussians.optimizer.cpu_adam
+        if not ca.lazy_pending:
+            ca.last_step[:N] = ca.step_count
+        ca.catch_up(oc["rows_host"][int(oc["row_end"][0]):N], include_this_step=True)
+        ca.lazy_pending = True
+
     # ---- stage 2: host Adam thread --------------------------------------------------------------
     # flags 0..bsz-2: cameras 0..bsz-2 done; flags bsz-1..: pieces of the last camera's flush
     n_last = filters[-1].shape[0]
@@ -292,7 +303,7 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     assert int(re_[bsz] - rb[bsz]) == n_last, "last-use group of the final camera must equal its filter"
     chunk_edges = [n_last * j // J for j in range(J + 1)]
     seg_begin, seg_end, seg_signal = [], [], []
-    if not args.sparse_adam:
+    if not args.sparse_adam and not lazy:
         # rows no camera touched: dense Adam still decays their moments; their gradient rows are zero by the
         # table's invariant, so the update skips reading / re-zeroing them (seg_zero_grad)
         seg_begin.append(int(rb[0])); seg_end.append(int(re_[0])); seg_signal.append(-1)
@@ -549,6 +560,8 @@ def naive_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_
 def clm_offload_eval_one_cam(camera, gaussians, background, scene=None):
     """engine.py:928-979, with the SH rows fetched by the zero-copy gather kernel instead of a
     CPU-side torch.gather + .to('cuda').  Returns the [3,H,W] image."""
+    if hasattr(gaussians, "materialize_host_rows"):
+        gaussians.materialize_host_rows()  # postponed (lazy) host updates, a pipelined host Adam
     filters, _ = calculate_filters([camera], gaussians)
     ids = filters[0]
     shs = torch.empty(ids.shape[0], 48, device=ids.device)

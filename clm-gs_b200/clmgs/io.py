@@ -149,8 +149,15 @@ def _host(t):
     return t.detach().cpu().numpy()
 
 
+def _current(gaussians):
+    """The pinned SH table may lag behind (pipelined host Adam, lazy dense Adam): bring it up to date before reading."""
+    if getattr(gaussians, "optimizer", None) is not None and hasattr(gaussians, "materialize_host_rows"):
+        gaussians.materialize_host_rows()
+
+
 def save_ply(gaussians, path):
     """strategies/base_gaussian_model.py:189-247."""
+    _current(gaussians)
     _write_ply(path, _host(gaussians._xyz), gaussians._parameters.detach().numpy(), _host(gaussians._opacity),
                _host(gaussians._scaling), _host(gaussians._rotation))
 
@@ -158,6 +165,7 @@ def save_ply(gaussians, path):
 def save_sub_plys(gaussians, path, n_split, split_size):
     """gaussian_model.py:292-361: ``<path>_rk<i>_ws<n_split>.ply`` holding rows [i*split_size, (i+1)*split_size)."""
     assert path.endswith(".ply")
+    _current(gaussians)
     n = gaussians._xyz.shape[0]
     written = []
     for i in range(n_split):
@@ -184,6 +192,7 @@ def save_tensors(gaussians, parent_path):
     """gaussian_model.py:236-244.  The SH rows are cloned first: saving the [:N] view would write the whole
     pre-allocated pinned buffer."""
     os.makedirs(parent_path, exist_ok=True)
+    _current(gaussians)
     torch.save(gaussians._xyz.detach(), os.path.join(parent_path, "xyz.pt"))
     torch.save(gaussians._opacity.detach(), os.path.join(parent_path, "opacity.pt"))
     torch.save(gaussians._scaling.detach(), os.path.join(parent_path, "scaling.pt"))

@@ -47,6 +47,7 @@ class TrainArgs:
     cpu_adam_threads: int = 0  # 0 = all hardware threads
     final_flush_chunks: int = 8  # last camera: flush + host Adam pipelined in this many pieces
     pipeline_host_adam: bool = False  # opt-in: return before the host Adam finished; the next call overlaps it
+    lazy_dense_adam: bool = False  # opt-in (dense Adam only): postpone the zero-gradient updates of untouched rows
     rows_lookahead: int = 2  # SH-row prefetches issued this many cameras ahead on the copy stream
     geometry_lookahead: int = 3  # cameras whose projection/tile sort is issued ahead of their SH rows
     # densification schedule (arguments/__init__.py:216-225)
@@ -107,6 +108,9 @@ class CpuAdam:
         self.exp_avg_sq_buffer = _pinned_zeros((rows,) + tuple(param.shape[1:]))
         self.exp_avg = self.exp_avg_buffer[:param.shape[0]]
         self.exp_avg_sq = self.exp_avg_sq_buffer[:param.shape[0]]
+        # lazy dense Adam: step through which each row is up to date (all rows current while lazy mode is unused)
+        self.last_step = np.zeros(rows, np.int32)
+        self.lazy_pending = False
         self.step_count = 0
         # default: all cores but one (the thread that launches kernels must not be time-sliced against
         # 16 spinning workers)
@@ -121,11 +125,23 @@ class CpuAdam:
                                          self.betas[1], self.eps, self.step_count, scale, self.n_threads, progress,
                                          seg_zero_grad)
 
+    def catch_up(self, rows=None, include_this_step=False):
+        """Lazy dense Adam: replay the postponed zero-gradient steps of `rows` (int32 ids; None = every row) through
+        the last finished step.  include_this_step: the caller is about to apply the next real step to exactly these
+        rows, so they are marked as current through it."""
+        n = self.param.shape[0]
+        ops.cpu_adam_lazy_catch_up(self.param, self.exp_avg, self.exp_avg_sq, self.columns_lr, rows,
+                                   self.last_step[:n], self.step_count, self.step_count + (1 if include_this_step else 0),
+                                   self.betas[0], self.betas[1], self.eps, self.n_threads)
+        if rows is None:
+            self.lazy_pending = False
+
     def resize(self, param):
         """After densify / prune: the parameter view changed length; the moment buffers were compacted in place."""
         self.param = param
         self.exp_avg = self.exp_avg_buffer[:param.shape[0]]
         self.exp_avg_sq = self.exp_avg_sq_buffer[:param.shape[0]]
+        self.last_step[:] = self.step_count  # callers materialise before restructuring: every row is current
 
 
 class UnifiedAdam:
@@ -234,13 +250,22 @@ class GaussianModelCLMOffload:
         p = [self._xyz, self._opacity, self._scaling, self._rotation]
         return p + [st[n]["exp_avg"] for n in self._GPU_NAMES] + [st[n]["exp_avg_sq"] for n in self._GPU_NAMES]
 
+    def materialize_host_rows(self):
+        """Lazy dense Adam (TrainArgs.lazy_dense_adam): bring every SH row and its moments up to the last finished
+        step.  Call before reading `_parameters` / the host moments outside the training iteration (evaluation,
+        densification and saving do it themselves).  No-op when nothing is postponed."""
+        from . import engine
+        engine.wait_host_adam(self)
+        cpu = self.optimizer.cpu_adam if self.optimizer is not None else None
+        if cpu is not None and cpu.lazy_pending:
+            cpu.catch_up(None)
+
     @torch.no_grad()
     def _restructure(self, cls, noise=None, generator=None):
         """classify bytes -> new state.  One plan, one gather kernel for the GPU tensors and their moments, one in-place
         compaction of the pinned tables (strategies/clm_offload/gaussian_model.py:522-739 re-concatenates every
         tensor three times and compacts the pinned table with a temporary of the whole kept set)."""
-        from . import engine
-        engine.wait_host_adam(self)  # a pipelined host update may still be writing the pinned tables
+        self.materialize_host_rows()  # joins a pipelined host update and replays postponed (lazy) updates
         dev = self._xyz.device
         n_old = self.n_gaussians
         src, noise_row, (nA, nB, nS, nC) = ops.densify_plan(cls)

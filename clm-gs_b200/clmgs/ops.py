@@ -533,3 +533,16 @@ def radix_sort_pairs_u32(keys, vals, end_bit=32):
     flag = np.zeros(1, np.int32)
     call("clmgs_radix_sort_pairs_u32", n, k0, k1, v0, v1, int(end_bit), sc, sc.numel(), flag, _st())
     return (k1, v1) if flag[0] else (k0, v0)
+
+
+def cpu_adam_lazy_catch_up(param, exp_avg, exp_avg_sq, col_lr, rows, last_step, through_step, mark_step, b1, b2, eps,
+                           n_threads=0):
+    """rows: int32 numpy / CPU tensor of row ids, or None for all rows of `param`."""
+    import numpy as np
+    if rows is None:
+        rows_arg, n = None, param.shape[0]
+    else:
+        rows_arg = rows if hasattr(rows, "data_ptr") else np.ascontiguousarray(rows, np.int32)
+        n = rows_arg.shape[0]
+    call("clmgs_cpu_adam_lazy_catch_up", param, exp_avg, exp_avg_sq, param.shape[1], np.ascontiguousarray(col_lr, np.float32),
+         rows_arg, int(n), last_step, int(through_step), int(mark_step), float(b1), float(b2), float(eps), int(n_threads))

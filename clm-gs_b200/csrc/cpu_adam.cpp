@@ -66,6 +66,18 @@ inline void wait_flag(const volatile int32_t *flag) {
     __atomic_thread_fence(__ATOMIC_ACQUIRE);
 }
 
+template <class F>
+void parallel_ranges(int64_t n, int n_threads, F f) {
+    if (n <= 0) return;
+    int T = (int)std::min<int64_t>(n_threads, std::max<int64_t>(1, n / 1024));
+    if (T <= 1) { f((int64_t)0, n); return; }
+    std::vector<std::thread> th;
+    th.reserve(T);
+    for (int t = 0; t < T; ++t) th.emplace_back([=] { f(n * t / T, n * (t + 1) / T); });
+    for (auto &t : th) t.join();
+}
+
+
 }  // namespace
 
 CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, float *host_exp_avg,
@@ -124,6 +136,61 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Lazy dense Adam.  With dense Adam every row is updated every step even when no camera saw it (its gradient is
+// zero, but the moments decay and the parameter still moves): at 28 M rows that is 30 GB of host DRAM traffic per
+// step for rows whose values nobody reads.  A zero-gradient step depends on nothing but the row itself, so it can be
+// postponed: last_step[r] records the step through which row r is up to date, and the postponed steps are replayed
+// -- the same adam_row<true> call with the same per-step bias corrections, hence bit-identical results -- right
+// before the row is next needed (before its SH coefficients are sent to the GPU, or when the whole table is
+// materialised for evaluation / densification / saving).  Rows: host_rows[0..n_rows), or all rows 0..n_rows if NULL.
+// Each row is brought to `through_step` and then marked `mark_step` (= through_step + 1 when the caller is about to
+// apply this batch's real step to exactly these rows, = through_step otherwise).
+CLMGS_EXPORT int clmgs_cpu_adam_lazy_catch_up(float *host_param, float *host_exp_avg, float *host_exp_avg_sq, int cols,
+                                              const float *col_lr, const int32_t *host_rows, int64_t n_rows,
+                                              int32_t *last_step, int64_t through_step, int64_t mark_step, float b1,
+                                              float b2, float eps, int n_threads) {
+    if (cols <= 0 || n_rows < 0 || through_step < 0 || mark_step < through_step || !host_param || !host_exp_avg ||
+        !host_exp_avg_sq || !col_lr || !last_step) {
+        clmgs_set_error("cpu_adam_lazy_catch_up: bad arguments (cols=%d n_rows=%lld through=%lld mark=%lld)", cols,
+                        (long long)n_rows, (long long)through_step, (long long)mark_step);
+        return CLMGS_ERR_INVALID;
+    }
+    if (n_threads <= 0) n_threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    n_threads = std::min(n_threads, 256);
+    // oldest state among the rows -> the range of steps whose constants are needed
+    std::atomic<int64_t> oldest_a(through_step);
+    parallel_ranges(n_rows, n_threads, [&](int64_t a, int64_t b) {
+        int64_t lo = through_step;
+        for (int64_t r = a; r < b; ++r) lo = std::min<int64_t>(lo, last_step[host_rows ? host_rows[r] : r]);
+        int64_t cur = oldest_a.load();
+        while (lo < cur && !oldest_a.compare_exchange_weak(cur, lo)) {}
+    });
+    const int64_t oldest = oldest_a.load();
+    if (oldest < 0) {
+        clmgs_set_error("cpu_adam_lazy_catch_up: negative last_step");
+        return CLMGS_ERR_INVALID;
+    }
+    std::vector<AdamConst> consts((size_t)(through_step - oldest) + 1);  // consts[s - oldest], s in (oldest, through]
+    for (int64_t st = oldest + 1; st <= through_step; ++st) {
+        AdamConst &c = consts[(size_t)(st - oldest)];
+        c.b1 = b1; c.b2 = b2; c.eps = eps; c.scale = 1.0f;
+        c.inv_bc1 = (float)(1.0 / (1.0 - pow((double)b1, (double)st)));
+        c.bc2_rsqrt = (float)(1.0 / sqrt(1.0 - pow((double)b2, (double)st)));
+    }
+    parallel_ranges(n_rows, n_threads, [&](int64_t a, int64_t b) {
+        for (int64_t r = a; r < b; ++r) {
+            const int64_t row = host_rows ? host_rows[r] : r;
+            const int64_t base = row * cols;
+            for (int64_t st = (int64_t)last_step[row] + 1; st <= through_step; ++st)
+                adam_row<true>(host_param + base, nullptr, host_exp_avg + base, host_exp_avg_sq + base, col_lr, cols,
+                               consts[(size_t)(st - oldest)]);
+            last_step[row] = (int32_t)mark_step;
+        }
+    });
+    return CLMGS_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // Densify / prune on the pinned tables.  The reference compacts the pinned SH table with
 // torch fancy indexing on the CPU (strategies/clm_offload/gaussian_model.py:566-570: a temporary of the whole
 // kept set, then a copy back) and re-allocates both Adam moments (:534-537, :640-655).  Here the three tables
@@ -132,20 +199,6 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
 // split children) copy; appended rows get zero moments.  Kept rows move in waves through a bounce buffer: every
 // thread first reads its share of the wave, all meet at a barrier, then every thread writes -- later waves only read rows
 // at or above their own destination, so nothing is overwritten before it is read.
-namespace {
-
-template <class F>
-void parallel_ranges(int64_t n, int n_threads, F f) {
-    if (n <= 0) return;
-    int T = (int)std::min<int64_t>(n_threads, std::max<int64_t>(1, n / 1024));
-    if (T <= 1) { f((int64_t)0, n); return; }
-    std::vector<std::thread> th;
-    th.reserve(T);
-    for (int t = 0; t < T; ++t) th.emplace_back([=] { f(n * t / T, n * (t + 1) / T); });
-    for (auto &t : th) t.join();
-}
-
-}  // namespace
 
 CLMGS_EXPORT int clmgs_host_rows_densify(float *host_param, float *host_exp_avg, float *host_exp_avg_sq, int cols,
                                          int64_t n_old, int64_t capacity, const int32_t *host_src, int64_t nA,

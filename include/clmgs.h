@@ -483,6 +483,16 @@ int clmgs_host_rows_densify(float *host_param, float *host_exp_avg, float *host_
 int clmgs_reset_opacity(int64_t N, float *opacity_logit, float *exp_avg, float *exp_avg_sq,
                         float max_opacity, void *stream);
 
+/* Lazy dense Adam -- a scheduling change on top of the reference's dense host Adam, which updates every row of the
+ * table at every step (optimizer.py:130-142 + engine.py:320-327): zero-gradient steps of rows no camera touched are postponed and
+ * replayed -- bit-identically, same per-step bias corrections -- when the row is next needed.  last_step[row] = the
+ * step through which the row is up to date.  Brings host_rows[0..n_rows) (all rows 0..n_rows if NULL) to
+ * through_step, then marks them mark_step.  HOST function. */
+int clmgs_cpu_adam_lazy_catch_up(float *host_param, float *host_exp_avg, float *host_exp_avg_sq, int cols,
+                                 const float *col_lr, const int32_t *host_rows, int64_t n_rows,
+                                 int32_t *last_step, int64_t through_step, int64_t mark_step, float b1,
+                                 float b2, float eps, int n_threads);
+
 /* fast_tsp.find_tour(dist, 0.001) (engine.py:179; submodule TarzanZhao/fast-tsp
  * @ 069eb3d, source not in the mount): deterministic greedy + 2-opt/Or-opt
  * open... closed tour over n <= 64 cameras, int32 dist [n*n]; writes tour[n]. */

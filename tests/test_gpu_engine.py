@@ -155,3 +155,37 @@ def test_camera_feed_matches_direct_cameras():
                                                           torch.cuda.Stream(), torch.Generator().manual_seed(0))
     ref_losses, _, _ = TS.train_one_batch(st, V, K, P, gts, W, H, args, order)
     np.testing.assert_allclose([float(l) for l in losses], ref_losses, rtol=2e-5, atol=2e-6)
+
+
+def test_lazy_dense_adam_engine_matches_default_engine():
+    """TrainArgs.lazy_dense_adam postpones the zero-gradient host updates of rows no camera touches.  After
+    materialising, the SH table must equal the default engine's: bit for bit on rows never touched (pure host
+    arithmetic), within the atomics' summation noise on touched rows."""
+    W, H, bsz = 112, 80, 4
+    out = []
+    for lazy in (False, True):
+        spec, g, V, K, P, gts, args, gm, cams, st = _setup(20_000, W, H, bsz, False, "aerial")
+        args.densification_stats = False
+        args.lazy_dense_adam = lazy
+        comm, gen = torch.cuda.Stream(), torch.Generator().manual_seed(0)
+        for it in range(3):
+            losses, order, _ = engine.clm_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None,
+                                                                  comm, gen)
+        if lazy:
+            assert gm.optimizer.cpu_adam.lazy_pending
+            img_before = engine.clm_offload_eval_one_cam(cams[0], gm, None)  # materialises on its own
+            assert not gm.optimizer.cpu_adam.lazy_pending
+        else:
+            img_before = engine.clm_offload_eval_one_cam(cams[0], gm, None)
+        out.append(dict(p=gm._parameters.numpy().copy(), m=gm.optimizer.cpu_adam.exp_avg.numpy().copy(),
+                        v=gm.optimizer.cpu_adam.exp_avg_sq.numpy().copy(), losses=[float(l) for l in losses],
+                        img=img_before.cpu().numpy(), p0=np.asarray(g["sh"], np.float32)))
+    a, b = out
+    np.testing.assert_allclose(b["losses"], a["losses"], rtol=1e-5)
+    never = (a["m"] == 0).all(1) & (b["m"] == 0).all(1)  # rows that never received a gradient
+    assert 100 < never.sum() < 19_900
+    np.testing.assert_array_equal(b["p"][never], a["p"][never])
+    np.testing.assert_array_equal(b["v"][never], a["v"][never])
+    _close(b["m"], a["m"], 1e-4, "exp_avg")
+    _close(b["v"], a["v"], 1e-4, "exp_avg_sq")
+    assert np.abs(b["img"] - a["img"]).max() < 2e-3

@@ -150,3 +150,57 @@ def test_new_entry_points_validate_arguments_without_a_gpu():
     assert L.call("clmgs_radix_sort_pairs_u32", 0, None, None, None, None, 32, None, 0, None, None) == 0
     assert L.call("clmgs_densify_plan_scratch_bytes", 1_000_000) > 0
     assert L.call("clmgs_radix_sort_pairs_u32_scratch_bytes", 46_000_000) >= (46_000_000 // 4096) * 256 * 4
+
+
+def test_lazy_dense_adam_is_bit_identical_to_dense():
+    """Postponing the zero-gradient updates of untouched rows and replaying them later must reproduce dense Adam
+    exactly: same parameters and moments, bit for bit, after every materialisation."""
+    import torch
+    from clmgs import model
+    rng = np.random.default_rng(5)
+    n, steps = 3000, 14
+    p0 = rng.standard_normal((n, 48)).astype(np.float32)
+
+    def make():
+        param = torch.from_numpy(p0.copy())
+        return model.CpuAdam(param, [3, 45], [2.5e-3, 1.25e-4], [0.9 ** 4, 0.999 ** 4], 5e-16, n_threads=3, capacity=n + 10)
+
+    dense, lazy = make(), make()
+    gd, gl = torch.zeros(n, 48), torch.zeros(n, 48)
+    sig = np.ones(1, np.int32)
+    for it in range(steps):
+        touched = np.nonzero(rng.random(n) < (0.05 if it % 5 else 0.6))[0].astype(np.int32)
+        untouched = np.setdiff1d(np.arange(n, dtype=np.int32), touched).astype(np.int32)
+        g = rng.standard_normal((len(touched), 48)).astype(np.float32)
+        gd[touched] = torch.from_numpy(g)
+        gl[touched] = torch.from_numpy(g)
+        # dense: untouched rows (zero gradient, not read) + touched rows
+        rows = np.concatenate([untouched, touched]).astype(np.int32)
+        dense.batched_sparse_step(gd, rows, [0, len(untouched)], [len(untouched), n], [-1, -1], sig, 0.25, None, [1, 0])
+        # lazy: replay what the touched rows skipped, then this step for them only
+        if not lazy.lazy_pending:
+            lazy.last_step[:n] = lazy.step_count
+        lazy.catch_up(touched, include_this_step=True)
+        lazy.lazy_pending = True
+        lazy.batched_sparse_step(gl, touched, [0], [len(touched)], [-1], sig, 0.25, None, [0])
+        assert not gl.numpy().any() and not gd.numpy().any()
+        if it in (3, steps - 1):  # evaluation / densification / saving points
+            lazy.catch_up(None)
+            assert not lazy.lazy_pending and (lazy.last_step[:n] == lazy.step_count).all()
+            np.testing.assert_array_equal(lazy.param.numpy(), dense.param.numpy())
+            np.testing.assert_array_equal(lazy.exp_avg.numpy(), dense.exp_avg.numpy())
+            np.testing.assert_array_equal(lazy.exp_avg_sq.numpy(), dense.exp_avg_sq.numpy())
+    assert np.abs(dense.param.numpy() - p0).max() > 1e-3  # the optimiser did move things
+
+
+def test_lazy_catch_up_rejects_bad_arguments():
+    from clmgs import _lib
+    import pytest
+    L = _lib.lib()
+    t = [np.zeros((4, 48), np.float32) for _ in range(3)]
+    lr, ls = np.zeros(48, np.float32), np.zeros(4, np.int32)
+    with pytest.raises(_lib.ClmgsError, match="bad arguments"):
+        L.call("clmgs_cpu_adam_lazy_catch_up", t[0], t[1], t[2], 48, lr, None, 4, ls, 3, 2, 0.9, 0.999, 1e-8, 1)
+    ls[1] = -5
+    with pytest.raises(_lib.ClmgsError, match="negative"):
+        L.call("clmgs_cpu_adam_lazy_catch_up", t[0], t[1], t[2], 48, lr, None, 4, ls, 3, 3, 0.9, 0.999, 1e-8, 1)
