@@ -498,6 +498,18 @@ int clmgs_cpu_adam_lazy_catch_up(float *host_param, float *host_exp_avg, float *
  * open... closed tour over n <= 64 cameras, int32 dist [n*n]; writes tour[n]. */
 int clmgs_tsp_tour(const int32_t *host_dist, int n, int32_t *host_tour);
 
+/* ---------------------------------------------------------------------------
+ * Measurement helpers (no counterpart in the reference; SURVEY.md 8d asks for the
+ * roofline denominators to be measured on the box): an FP32 FMA chain kernel
+ * (one launch = grid_ctas x 1024 threads x iters x 128 FMAs), a plain
+ * cudaMemcpyAsync (pinned host <-> device = the host-link peak) and a host STREAM
+ * triad a = b + s c over n floats on n_threads threads (blocking).  bench.py and
+ * tools/peaks.py time them; nothing on the training path calls them. */
+int clmgs_measure_fma(int grid_ctas, int iters, float *sink, void *stream);
+int clmgs_measure_memcpy(void *dst, const void *src, size_t bytes, void *stream);
+int clmgs_measure_host_triad(float *host_a, const float *host_b, const float *host_c, int64_t n, float s,
+                             int n_threads);
+
 #ifdef __cplusplus
 }
 #endif

@@ -189,3 +189,94 @@ def test_lazy_dense_adam_engine_matches_default_engine():
     _close(b["m"], a["m"], 1e-4, "exp_avg")
     _close(b["v"], a["v"], 1e-4, "exp_avg_sq")
     assert np.abs(b["img"] - a["img"]).max() < 2e-3
+
+
+def _c4_like_model(g, args):
+    gm = model.GaussianModelCLMOffload(3, DEV).create_from_arrays(g["xyz"], g["log_scale"], g["raw_quat"],
+                                                                 g["opacity_logit"], g["sh"])
+    return gm.training_setup(args)
+
+
+def test_c4_shaped_iteration_matches_golden():
+    """BASELINE.json configs[3] SHAPE end to end: aerial scene, 1920x1080 (8160 tiles), batch 64 -> 64-bit
+    visibility words, sparse (selective) Adam, 1 M Gaussians.  The oracle needs minutes for this, so its result is
+    a committed fixture (tests/golden/c4_iteration.npz, written by tests/golden/make_c4_iteration.py from the same
+    seeded inputs)."""
+    import importlib.util
+    import os
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    spec_ = importlib.util.spec_from_file_location("make_c4_iteration", os.path.join(here, "make_c4_iteration.py"))
+    mk = importlib.util.module_from_spec(spec_)
+    spec_.loader.exec_module(mk)
+    gold = dict(np.load(os.path.join(here, "c4_iteration.npz")))
+    spec, g, V, K, P, gts, args = mk.inputs()
+    N, W, H, bsz = mk.N, mk.W, mk.H, mk.BSZ
+    args.cpu_adam_threads = 8
+    p0 = {k: np.array(g[k], np.float32, copy=True).reshape(N, -1) for k in ("xyz", "log_scale", "raw_quat", "opacity_logit", "sh")}
+    gm = _c4_like_model(g, args)
+    cams = [model.Camera(V[i], K[i], gts[i % mk.N_GT], DEV, uid=i) for i in range(bsz)]
+    losses, ordered, sparsity = engine.clm_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None,
+                                                                   torch.cuda.Stream(), torch.Generator().manual_seed(0))
+    assert sorted(ordered) == list(range(bsz))
+    assert gm._parameters.shape == (N, 48)
+    # integer parity per camera (the engine reports in processed order)
+    inv = np.asarray(ordered)
+    assert gm.last_batch_stats["n_visible"] == gold["n_visible"][inv].tolist()
+    assert gm.last_batch_stats["n_isects"] == gold["n_isects"][inv].tolist()
+    assert gm.last_batch_stats["n_union"] == int(gold["n_touched"])
+    np.testing.assert_allclose([float(l) for l in losses], gold["losses"][inv], rtol=2e-5, atol=2e-6)
+    assert not gm.parameters_grad_buffer.numpy().any()
+    s = gold["sample"]
+    tch = gold["sample_touched"]
+    assert tch.sum() > 1000 and (~tch).sum() > 100
+    gpu = dict(xyz=("xyz", gm._xyz), log_scale=("scaling", gm._scaling), raw_quat=("rotation", gm._rotation),
+               opacity_logit=("opacity", gm._opacity))
+    for key, (name, t) in gpu.items():
+        stt = gm.optimizer.gpu_adam.state[name]
+        _close(stt["exp_avg"].cpu().numpy()[s], gold["m_" + key], 1e-3, ("m", key))
+        _close(stt["exp_avg_sq"].cpu().numpy()[s], gold["v_" + key], 2e-3, ("v", key))
+        got = t.cpu().numpy()[s]
+        # selective Adam never moves an untouched Gaussian (adam.cu:29)
+        np.testing.assert_array_equal(got[~tch], p0[key][s][~tch])
+        np.testing.assert_array_equal(gold[key][~tch], p0[key][s][~tch])
+        d_got, d_ref = got - p0[key][s], gold[key] - p0[key][s]
+        m_ref = np.abs(gold["m_" + key])
+        well = m_ref > 1e-2 * m_ref.max()
+        assert (np.abs(d_got - d_ref)[well] / np.abs(d_ref).max()).max() < 5e-3, key
+    _close(gm.optimizer.cpu_adam.exp_avg.numpy()[s], gold["m_sh"], 1e-3, "m_sh")
+    _close(gm.optimizer.cpu_adam.exp_avg_sq.numpy()[s], gold["v_sh"], 2e-3, "v_sh")
+    got = gm._parameters.numpy()[s]
+    np.testing.assert_array_equal(got[~tch], p0["sh"][s][~tch])
+    m_ref = np.abs(gold["m_sh"])
+    well = m_ref > 1e-2 * m_ref.max()
+    d_got, d_ref = got - p0["sh"][s], gold["sh"] - p0["sh"][s]
+    assert (np.abs(d_got - d_ref)[well] / np.abs(d_ref).max()).max() < 5e-3
+
+
+def test_c4_shaped_small_iteration_matches_live_oracle():
+    """Same shape class as above (aerial, batch 64, 64-bit words, sparse Adam) at a size the oracle runs live, with
+    the engine's own TSP order fed to the oracle; two consecutive steps."""
+    W, H, bsz, n = 480, 270, 64, 200_000
+    spec = S.SceneSpec("t", n, W, H, bsz, "aerial", 50.0, 3)
+    g = S.make_gaussians(spec)
+    V, K, P = S.make_cameras(spec, bsz, g["extent"])
+    gts = S.make_gt_images(spec, bsz)
+    args = model.TrainArgs(bsz=bsz, sparse_adam=True, cpu_adam_threads=8)
+    gm = _c4_like_model(g, args)
+    cams = [model.Camera(V[i], K[i], gts[i], DEV, uid=i) for i in range(bsz)]
+    st = TS.new_state(g)
+    comm, gen = torch.cuda.Stream(), torch.Generator().manual_seed(3)
+    for it in range(2):
+        losses, ordered, _ = engine.clm_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None,
+                                                                comm, gen)
+        ref_losses, ref_filters, stats = TS.train_one_batch(st, V, K, P, gts, W, H, args, ordered)
+        assert gm.last_batch_stats["n_visible"] == [s_["n_visible"] for s_ in stats]
+        assert gm.last_batch_stats["n_isects"] == [s_["n_isects"] for s_ in stats]
+        np.testing.assert_allclose([float(l) for l in losses], ref_losses, rtol=2e-5, atol=2e-6)
+        assert not gm.parameters_grad_buffer.numpy().any()
+        for name, key in (("xyz", "xyz"), ("scaling", "log_scale"), ("rotation", "raw_quat"), ("opacity", "opacity_logit")):
+            stt = gm.optimizer.gpu_adam.state[name]
+            _close(stt["exp_avg"].cpu().numpy(), st["m_" + key], 1e-3, (it, "m", key))
+            _close(stt["exp_avg_sq"].cpu().numpy(), st["v_" + key], 2e-3, (it, "v", key))
+        _close(gm.optimizer.cpu_adam.exp_avg.numpy(), st["m_sh"], 1e-3, (it, "m_sh"))
+        _close(gm.optimizer.cpu_adam.exp_avg_sq.numpy(), st["v_sh"], 2e-3, (it, "v_sh"))

@@ -1,0 +1,360 @@
+"""libclmgs.so against the REFERENCE's own CUDA kernels on the same B200, same inputs.
+
+`oracle/_ref/` holds the reference's gsplat.csrc and clm_kernels._C compiled for sm_100 with the reference's own
+flags (gsplat: --use_fast_math, submodules/gsplat/setup.py:81; clm_kernels: -O3, submodules/clm_kernels/setup.py:26)
+straight from the sources under /root/reference by `oracle/build_ref.py` (no source copied; the .so travels to
+the GPU box).  This pins to the reference itself what the CPU fixtures cannot: the packed cull rule
+(fully_fused_projection_packed_fwd.cu:52-131), rasterize_to_pixels fwd/bwd (rasterize_to_pixels_fwd.cu:88-159,
+rasterize_to_pixels_bwd.cu:105-248), the clm_kernels transfers / bitmaps / selective Adam / in-place SH backward
+(clm_kernels.cu:5-627, adam.cu:12-41, compute_sh_bwd.cu:276-344) and the fused SSIM (ssim.cu:187-366).
+
+north_star tolerances: culling masks, compacted indices, tile counts and sorted keys bit-exact; images within
+1e-4 absolute; gradients within 1e-3 relative.
+"""
+import importlib.util
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from clmgs import ops, scene as S
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _load(name, sub):
+    path = os.path.join(ROOT, "oracle", "_ref", sub, name + ".so")
+    if not os.path.exists(path):
+        pytest.skip("REFERENCE CUDA BUILD MISSING: %s (run `python oracle/build_ref.py` where /root/reference exists); "
+                    "parity against the reference's own kernels is NOT checked in this run" % path)
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+@pytest.fixture(scope="module")
+def G():
+    return _load("gsplat_ref_csrc", "gsplat")
+
+
+@pytest.fixture(scope="module")
+def CK():
+    return _load("clm_kernels_ref_C", "clm_kernels")
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def _rel(x, y):
+    return float((x - y).abs().max() / y.abs().max().clamp_min(1e-20))
+
+
+def _scene(config, n, bsz, cam_seed=0):
+    base = S.CONFIGS[config]
+    spec = S.SceneSpec(base.name, base.n_gaussians, base.width, base.height, bsz, base.shape, base.fovx_deg, base.index)
+    g = S.make_gaussians(spec, n=n)   # a prefix of the full scene: same spacing / extent / scales as the named config
+    V, K, P = S.make_cameras(spec, bsz, g["extent"], seed_offset=cam_seed)
+    return spec, g, V, K, P
+
+
+# ------------------------------------------------------------------------------------------------- S1 cull
+@pytest.mark.parametrize("config,n,bsz", [("c2_bicycle_6m", 6_000_000, 4), ("c4_bigcity_102m", 4_000_000, 64),
+                                          ("c3_rubble4k_28m", 3_000_000, 16)])
+def test_cull_masks_identical_to_reference_packed_projection(G, config, n, bsz):
+    """calculate_filters (strategies/base_engine.py:18-76): the reference's packed projection vs the one-pass cull.
+    Bit-exact: camera ids, ascending Gaussian ids, per-camera counts -- against a --use_fast_math build."""
+    spec, g, V, K, P = _scene(config, n, bsz)
+    W, H = spec.width, spec.height
+    xyz, ls, rq = _t(g["xyz"]), _t(g["log_scale"]), _t(g["raw_quat"])
+    scales, quats = torch.exp(ls), torch.nn.functional.normalize(rq, dim=-1)   # base_gaussian_model.py:42-50
+    Vt, Kt = _t(V), _t(K)
+    r = G.fully_fused_projection_packed_fwd(xyz, None, quats, scales, Vt, Kt, W, H, 0.3, 0.01, 1e10, 0.0, False)
+    cam_r, gid_r = r[1], r[2]
+    ours = ops.cull(xyz, scales, quats, Vt, Kt, W, H, activated=True, packed_outputs=True)
+    assert ours["gaussian_ids"].shape[0] == gid_r.shape[0], (ours["gaussian_ids"].shape, gid_r.shape)
+    assert torch.equal(ours["camera_ids"], cam_r)
+    assert torch.equal(ours["gaussian_ids"], gid_r)
+    counts_r = torch.bincount(cam_r, minlength=bsz).tolist()
+    assert ours["counts"] == counts_r
+    assert sum(counts_r) > 0
+    # the engine's call (raw tensors, activations fused): same compacted ids
+    raw = ops.cull(xyz, ls, rq, Vt, Kt, W, H, activated=False)
+    if not torch.equal(raw["gaussian_ids"], gid_r):
+        # exp() here is a deterministic polynomial, torch.exp another implementation: ids may differ only where a
+        # scale differs in the last bit AND the Gaussian sits on a decision boundary
+        a = torch.zeros(bsz * n, dtype=torch.bool, device=DEV)
+        b = torch.zeros_like(a)
+        cam_o = torch.repeat_interleave(torch.arange(bsz, device=DEV), torch.tensor(raw["counts"], device=DEV))
+        a[cam_o * n + raw["gaussian_ids"]] = True
+        b[cam_r * n + gid_r] = True
+        assert int((a != b).sum()) <= max(2, int(2e-7 * bsz * n)), int((a != b).sum())
+
+
+# ------------------------------------------------------------------------------------------------- per-camera stages
+@pytest.fixture(scope="module", params=[("c2_bicycle_6m", 6_000_000), ("c4_bigcity_102m", 8_000_000)],
+                ids=["c2_object", "c4_aerial_1080p"])
+def one_camera(request, G):
+    """Everything one camera's forward produces, from OUR kernels, as identical inputs for both sides."""
+    config, n = request.param
+    spec, g, V, K, P = _scene(config, n, 4)
+    W, H = spec.width, spec.height
+    xyz, ls, rq, ol = _t(g["xyz"]), _t(g["log_scale"]), _t(g["raw_quat"]), _t(g["opacity_logit"])
+    Vt, Kt = _t(V), _t(K)
+    cull = ops.cull(xyz, ls, rq, Vt, Kt, W, H, activated=False)
+    cam = int(np.argmax(cull["counts"]))
+    start = sum(cull["counts"][:cam])
+    ids = cull["gaussian_ids"][start: start + cull["counts"][cam]]
+    assert ids.shape[0] > 1000
+    m, s_, q_, o_ = ops.gather_activate(xyz, ls, rq, ol, ids)
+    v1, k1 = Vt[cam:cam + 1].contiguous(), Kt[cam:cam + 1].contiguous()
+    rad, m2, dep, con, _ = ops.projection_fwd(m, q_, s_, v1, k1, W, H)
+    tw, th = math.ceil(W / 16.0), math.ceil(H / 16.0)
+    sh = _t(g["sh"][ids.cpu().numpy()])
+    campos = _t(P[cam])
+    return dict(spec=spec, W=W, H=H, tw=tw, th=th, n=ids.shape[0], ids=ids, means=m, scales=s_, quats=q_, opac=o_,
+                v1=v1, k1=k1, radii=rad, means2d=m2, depths=dep, conics=con, sh=sh, campos=campos)
+
+
+def test_dense_projection_vs_reference_fast_math(G, one_camera):
+    """fully_fused_projection_fwd.cu:19-129.  The reference build contracts FMAs and uses approximate division;
+    ours is IEEE (bit-exact against the oracle).  So: radii equal except where ceil() sees a value one ulp apart,
+    means2d / conics / depths within float rounding."""
+    c = one_camera
+    rr, rm2, rd, rc, _ = G.fully_fused_projection_fwd(c["means"], None, c["quats"], c["scales"], c["v1"], c["k1"],
+                                                      c["W"], c["H"], 0.3, 0.01, 1e10, 0.0, False)
+    both = (rr > 0) & (c["radii"] > 0)
+    assert float((rr != c["radii"]).float().mean()) < 1e-4
+    assert int(((rr > 0) != (c["radii"] > 0)).sum()) <= max(2, int(1e-5 * c["n"]))
+    assert int((rr - c["radii"]).abs().max()) <= 1
+    assert float((rm2 - c["means2d"])[both].abs().max()) < 2e-3          # pixels
+    assert float(((rd - c["depths"])[both].abs() / rd[both]).max()) < 1e-5
+    assert float(((rc - c["conics"])[both].abs() / (rc[both].abs().amax(-1, keepdim=True) + 1e-12)).max()) < 1e-3
+
+
+def test_tile_stage_identical_given_identical_inputs(G, one_camera):
+    """isect_tiles.cu:100-301: tiles_per_gauss, the sorted 64-bit keys, flatten_ids and the tile offsets -- equal."""
+    c = one_camera
+    rt, rids, rflat = G.isect_tiles(c["means2d"], c["radii"], c["depths"], None, None, 1, 16, c["tw"], c["th"], True, True)
+    ot, oids, oflat = ops.isect_tiles(c["means2d"], c["radii"], c["depths"], 16, c["tw"], c["th"])
+    assert torch.equal(rt, ot)
+    assert torch.equal(rids, oids)
+    assert torch.equal(rflat, oflat)
+    roff = G.isect_offset_encode(rids, 1, c["tw"], c["th"])
+    assert torch.equal(roff, ops.isect_offset_encode(oids, 1, c["tw"], c["th"]))
+    # the engine's fused stage (no 64-bit keys materialised)
+    flat2, off2, n_is = ops.isect_sorted_offsets(c["means2d"], c["radii"], c["depths"], 16, c["tw"], c["th"])
+    assert n_is == rids.shape[0]
+    assert torch.equal(flat2, rflat) and torch.equal(off2, roff)
+    c["flatten_ids"], c["offsets"] = rflat, roff
+
+
+def test_sh_colour_and_inplace_backward(G, CK, one_camera):
+    """compute_sh_fwd.cu:31-58 + engine.py:67-78 and clm_kernels compute_sh_bwd.cu:309-344 (`+=` into v_coeffs)."""
+    c = one_camera
+    n = c["n"]
+    dirs = (c["means"] - c["campos"][None]).contiguous()
+    c3 = c["sh"].view(n, 16, 3)
+    raw = G.compute_sh_fwd(3, dirs, c3, None)
+    col_r = torch.clamp_min(raw + 0.5, 0.0)
+    col_o = ops.sh_colors_fwd(3, c["means"], c["campos"], c["sh"])
+    assert float((col_r - col_o).abs().max()) < 1e-5
+    c["colors"] = col_o
+    torch.manual_seed(0)
+    vcol = torch.randn(n, 3, device=DEV)
+    base = torch.randn(n, 48, device=DEV)         # gradients retained from earlier cameras
+    g_ref = base.clone().view(n, 16, 3)
+    mask = (raw + 0.5 >= 0).float()               # autograd applies the clamp's mask in the reference (engine.py:714)
+    vd_ref = CK.compute_sh_bwd_inplace(16, 3, dirs, c3, g_ref, None, (vcol * mask).contiguous(), True)
+    torch.cuda.synchronize()
+    g_our = base.clone()
+    vm = torch.zeros(n, 3, device=DEV)
+    ops.sh_colors_bwd(3, c["means"], c["campos"], c["sh"], vcol, g_our, vm)
+    safe = ((raw + 0.5).abs() > 1e-4).all(1)      # away from the clamp edge
+    assert _rel(g_our[safe], g_ref.view(n, 48)[safe]) < 1e-5
+    assert _rel(vm[safe], vd_ref.view(n, 3)[safe]) < 1e-3
+
+
+def test_rasterize_fwd_bwd(G, one_camera):
+    """rasterize_to_pixels_fwd.cu:88-159 / rasterize_to_pixels_bwd.cu:105-248."""
+    c = one_camera
+    W, H = c["W"], c["H"]
+    if "flatten_ids" not in c:
+        c["flatten_ids"], c["offsets"], _ = ops.isect_sorted_offsets(c["means2d"], c["radii"], c["depths"], 16, c["tw"], c["th"])
+    if "colors" not in c:
+        c["colors"] = ops.sh_colors_fwd(3, c["means"], c["campos"], c["sh"])
+    colors, opac = c["colors"][None].contiguous(), c["opac"][None].contiguous()
+    flat, off = c["flatten_ids"], c["offsets"]
+    r_rc, r_ra, r_last = G.rasterize_to_pixels_fwd(c["means2d"], c["conics"], colors, opac, None, W, H, 16, off, flat)
+    o_rc, o_ra, o_last = ops.rasterize_fwd(c["means2d"], c["conics"], colors, opac, W, H, 16, off, flat)
+    assert float((r_rc - o_rc).abs().max()) <= 1e-4
+    assert float((r_ra - o_ra).abs().max()) <= 1e-4
+    assert float((r_last != o_last).float().mean()) < 1e-5
+    # with a background colour
+    bg = torch.tensor([[0.2, 0.5, 0.9]], device=DEV)
+    r_b = G.rasterize_to_pixels_fwd(c["means2d"], c["conics"], colors, opac, bg, W, H, 16, off, flat)[0]
+    o_b = ops.rasterize_fwd(c["means2d"], c["conics"], colors, opac, W, H, 16, off, flat, bg)[0]
+    assert float((r_b - o_b).abs().max()) <= 1e-4
+    torch.manual_seed(1)
+    v_rc = torch.randn_like(r_rc)
+    v_ra = torch.randn_like(r_ra) * 0.1
+    for absgrad in (False, True):
+        rv_abs, rv_m, rv_c, rv_col, rv_o = G.rasterize_to_pixels_bwd(c["means2d"], c["conics"], colors, opac, None, W, H, 16,
+                                                                    off, flat, r_ra, r_last, v_rc, v_ra, absgrad)
+        ov_m, ov_c, ov_col, ov_o, ov_abs = ops.rasterize_bwd(c["means2d"], c["conics"], colors, opac, W, H, 16, off, flat,
+                                                            r_ra, r_last, v_rc, v_ra, None, absgrad=absgrad)
+        assert _rel(ov_m, rv_m) < 1e-3
+        assert _rel(ov_c, rv_c) < 1e-3
+        assert _rel(ov_col, rv_col) < 1e-3
+        assert _rel(ov_o, rv_o) < 1e-3
+        if absgrad:
+            assert _rel(ov_abs, rv_abs) < 1e-3
+    c["v_means2d"], c["v_conics"] = rv_m, rv_c
+
+
+def test_projection_bwd(G, one_camera):
+    """fully_fused_projection_bwd.cu:19-185."""
+    c = one_camera
+    torch.manual_seed(2)
+    vm2 = c.get("v_means2d")
+    if vm2 is None:
+        vm2 = torch.randn_like(c["means2d"]) * (c["radii"] > 0)[..., None]
+        vc = torch.randn_like(c["conics"]) * (c["radii"] > 0)[..., None]
+    else:
+        vc = c["v_conics"]
+    vd = torch.randn_like(c["depths"]) * (c["radii"] > 0)
+    r_vm, _, r_vq, r_vs, _ = G.fully_fused_projection_bwd(c["means"], None, c["quats"], c["scales"], c["v1"], c["k1"],
+                                                         c["W"], c["H"], 0.3, c["radii"], c["conics"], None, vm2, vd, vc,
+                                                         None, False)
+    o_vm, o_vq, o_vs = ops.projection_bwd(c["means"], c["quats"], c["scales"], c["v1"], c["k1"], c["W"], c["H"], 0.3,
+                                          c["radii"], c["conics"], vm2, vd, vc)
+    assert _rel(o_vm, r_vm) < 1e-3
+    assert _rel(o_vq, r_vq) < 1e-3
+    assert _rel(o_vs, r_vs) < 1e-3
+
+
+def test_fused_ssim_and_loss(CK, one_camera):
+    """ssim.cu:187-366 + base_engine.py:79-94."""
+    c = one_camera
+    W, H = c["W"], c["H"]
+    torch.manual_seed(3)
+    img = torch.rand(3, H, W, device=DEV)
+    gt_u8 = _t(S.make_gt_images(c["spec"], 1)[0])
+    gt = torch.clamp(gt_u8 / 255.0, 0.0, 1.0)
+    mp, d1, d2, d3 = CK.fusedssim(1e-4, 9e-4, img[None], gt[None], True)
+    dl = torch.full_like(img[None], 1.0 / img.numel())
+    gr = CK.fusedssim_backward(1e-4, 9e-4, img[None], gt[None], dl, d1, d2, d3)
+    torch.cuda.synchronize()
+    s_our, g_our = ops.fused_ssim_fwd_bwd(img[None].contiguous(), gt[None].contiguous())
+    assert abs(float(mp.mean() - s_our)) < 1e-5
+    assert _rel(g_our, gr) < 1e-3
+    ref_total = 0.8 * (img - gt).abs().mean() + 0.2 * (1 - mp.mean())
+    lv, vg = ops.loss_fwd_bwd(img, gt_u8, 0.2, hwc=False)
+    assert abs(float(ref_total - lv[0])) < 1e-5
+    ref_v = 0.8 * torch.sign(img - gt) / img.numel() - 0.2 * gr[0]
+    assert _rel(vg, ref_v) < 1e-3
+
+
+# ------------------------------------------------------------------------------------------------- clm_kernels
+def test_row_transfers_byte_equal_incl_retention(CK):
+    """clm_kernels.cu:26-268: first-camera gather, retention gather (H rows from pinned host + D rows from the
+    previous camera's buffer), gradient store with and without accumulate, retention gradient hand-off, signal."""
+    rng = np.random.default_rng(5)
+    N = 300_000
+    h = torch.from_numpy(rng.standard_normal((N, 48)).astype(np.float32)).pin_memory()
+    vis = rng.random((2, N)) < 0.3
+    f0, f1 = (np.nonzero(vis[k])[0] for k in range(2))
+    ids0 = _t(f0.astype(np.int64))
+    a = torch.empty(len(f0), 48, device=DEV)
+    b = torch.empty_like(a)
+    CK.send_shs2gpu_stream(a, h, ids0, 32, 256)
+    ops.rows_gather(b, h, ids0)
+    assert torch.equal(a, b)
+    # one retention transition camera 0 -> camera 1 (engine.py:519-641)
+    pos0, pos1 = np.cumsum(vis[0]) - 1, np.cumsum(vis[1]) - 1
+    only1 = np.nonzero(~vis[0] & vis[1])[0]
+    both = np.nonzero(vis[0] & vis[1])[0]
+    host_idx, rt_src = _t(only1.astype(np.int32)), _t(pos0[both].astype(np.int32))
+    dst_h, dst_r = _t(pos1[only1].astype(np.int32)), _t(pos1[both].astype(np.int32))
+    n1 = len(f1)
+    ra, rb = torch.zeros(n1, 48, device=DEV), torch.zeros(n1, 48, device=DEV)
+    CK.send_shs2gpu_stream_retention(ra, h, a, host_idx, rt_src, dst_h, dst_r, 32, 256, 128, 256)
+    ops.rows_gather_retention(rb, h, b, host_idx, rt_src, dst_h, dst_r)
+    assert torch.equal(ra, rb)
+    assert torch.equal(rb, _t(h.numpy()[f1]))
+    # gradient rows back: plain store, then accumulate on top
+    g0 = torch.randn(len(f0), 48, device=DEV)
+    hg_r, hg_o = torch.zeros(N, 48).pin_memory(), torch.zeros(N, 48).pin_memory()
+    for accum in (False, True, True):
+        CK.send_shs2cpu_grad_buffer_stream(g0, hg_r, ids0, accum, 32, 256)
+        ops.rows_scatter_grad(g0, hg_o, ids0, accum)
+    torch.cuda.synchronize()
+    assert hg_r.numpy().tobytes() == hg_o.numpy().tobytes()
+    # retention hand-off of camera 0's gradients: rows only camera 0 needs go to the host (+=), shared rows to
+    # camera 1's gradient buffer (+=)  (engine.py:767-802)
+    only0 = np.nonzero(vis[0] & ~vis[1])[0]
+    host_idx_g, rt_dst = _t(only0.astype(np.int32)), _t(pos1[both].astype(np.int32))
+    src_h, src_r = _t(pos0[only0].astype(np.int32)), _t(pos0[both].astype(np.int32))
+    nxt_r, nxt_o = torch.zeros(n1, 48, device=DEV), torch.zeros(n1, 48, device=DEV)
+    CK.send_shs2cpu_grad_buffer_stream_retention(g0, hg_r, nxt_r, host_idx_g, rt_dst, src_h, src_r, True, 32, 256, 128, 256)
+    ops.rows_scatter_grad_retention(g0, hg_o, nxt_o, host_idx_g, rt_dst, src_h, src_r, True)
+    torch.cuda.synchronize()
+    assert torch.equal(nxt_r, nxt_o)
+    assert hg_r.numpy().tobytes() == hg_o.numpy().tobytes()
+    fr, fo = torch.zeros(8, dtype=torch.int32).pin_memory(), torch.zeros(8, dtype=torch.int32).pin_memory()
+    CK.set_signal(fr, 5, 1)
+    ops.set_signal(fo, 5, 1)
+    torch.cuda.synchronize()
+    assert fr.tolist() == fo.tolist()
+
+
+@pytest.mark.parametrize("bsz", [4, 8, 16, 32, 64])
+def test_bitmap_kernels(CK, bsz):
+    """scatter_to_bit / extract_ffs / compute_cnt_h (clm_kernels.cu:291-627) as order_calculation uses them
+    (engine.py:150-235)."""
+    rng = np.random.default_rng(bsz)
+    N = 500_009
+    vis = rng.random((bsz, N)) < rng.uniform(0.02, 0.5, (bsz, 1))
+    dt = {4: torch.int8, 8: torch.int8, 16: torch.int16, 32: torch.int32, 64: torch.int64}[bsz]
+    bm_r = torch.zeros(N, dtype=dt, device=DEV)
+    bm_o = torch.zeros(N, dtype=ops._WORD_DTYPE[ops.word_bytes_for(bsz)], device=DEV)
+    for i in range(bsz):
+        f = _t(np.nonzero(vis[i])[0].astype(np.int64))
+        CK.scatter_to_bit(bm_r, f, bsz - 1 - i)
+        ops.scatter_to_bit(bm_o, f, bsz - 1 - i)
+    assert bm_r.cpu().numpy().tobytes() == bm_o.cpu().numpy().tobytes()
+    ffs_r = torch.empty(N, dtype=torch.uint8, device=DEV)
+    CK.extract_ffs(bm_r, ffs_r)
+    assert torch.equal(ffs_r, ops.extract_ffs(bm_o))
+    tmp = torch.empty(bsz - 1, 64 * 256, dtype=torch.int32, device=DEV)
+    CK.compute_cnt_h(bm_r, tmp, 64, 256)
+    cnt_d_r = tmp.sum(1).to(torch.int32)
+    assert torch.equal(cnt_d_r, ops.compute_cnt_d(bm_o, bsz))
+    # the last-use groups: torch.sort + unique_consecutive (engine.py:205-213) vs the counting sort
+    _, idx = torch.sort(ffs_r, stable=True)
+    out_ids, counts = ops.group_by_ffs(ffs_r, bsz)
+    assert torch.equal(idx.to(torch.int32), out_ids)
+    assert torch.equal(torch.bincount(ffs_r.long(), minlength=bsz + 1), counts)
+
+
+def test_selective_adam(CK):
+    """adam.cu:12-41 (masked, no bias correction)."""
+    torch.manual_seed(7)
+    N = 200_003
+    for M in (1, 3, 4):
+        p, g = torch.randn(N, M, device=DEV), torch.randn(N, M, device=DEV)
+        m, v = torch.randn(N, M, device=DEV) * 0.1, torch.rand(N, M, device=DEV) * 0.01
+        mask = torch.rand(N, device=DEV) < 0.4
+        pr, mr, vr = p.clone(), m.clone(), v.clone()
+        po, mo, vo = p.clone(), m.clone(), v.clone()
+        CK.selective_adam_update(pr, g * 0.25, mr, vr, mask, 1e-2, 0.9 ** 4, 0.999 ** 4, 5e-16, N, M)
+        ops.selective_adam(po, g, mo, vo, mask, 1e-2, 0.9 ** 4, 0.999 ** 4, 5e-16, grad_scale=0.25)
+        assert torch.equal(po[~mask], p[~mask])
+        torch.testing.assert_close(mo, mr, rtol=1e-6, atol=1e-8)
+        torch.testing.assert_close(vo, vr, rtol=1e-6, atol=1e-10)
+        torch.testing.assert_close(po, pr, rtol=1e-5, atol=1e-7)
