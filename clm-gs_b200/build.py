@@ -24,8 +24,10 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
 PER_FILE = {
     "proj.cu": ["-fmad=false"],
     "densify.cu": ["-fmad=false"],
-    "cpu_adam.cpp": ["-Xcompiler", "-mavx2", "-Xcompiler", "-mfma", "-Xcompiler", "-pthread"],
 }
+# host-only translation units go straight to g++ (no device code; nvcc's front end is not needed for them).
+# -ffp-contract=off: the AVX2 and AVX-512 Adam rows must round identically (see cpu_adam.cpp).
+HOST_CXX = ["-O3", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-mavx2", "-ffp-contract=off", "-pthread", "-g1"]
 
 
 def nvcc():
@@ -51,7 +53,10 @@ def compile_one(src, force, verbose):
     sp = os.path.join(CSRC, src)
     if not force and os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(sp), headers_mtime()):
         return obj, ""
-    cmd = [nvcc()] + ARCH + COMMON + PER_FILE.get(src, []) + ["-x", "cu", "-c", sp, "-o", obj]
+    if src.endswith(".cpp"):
+        cmd = [shutil.which("g++") or "g++"] + HOST_CXX + ["-c", sp, "-o", obj]
+    else:
+        cmd = [nvcc()] + ARCH + COMMON + PER_FILE.get(src, []) + ["-x", "cu", "-c", sp, "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, " ".join(cmd), r.stderr[-6000:]))

@@ -205,7 +205,7 @@ def shade_one_camera(gaussians, camera, fw, shs, background, timer=_NULL_TIMER, 
     with timer("raster_fwd"):
         fw["render"], fw["alphas"], fw["last"] = ops.rasterize_fwd(
             fw["means2d"], fw["conics"], fw["colors"][None], fw["opac"][None], W, H, TILE_SIZE, fw["offsets"],
-            fw["flatten_ids"], fw["bg"])
+            fw["flatten_ids"], fw["bg"], work_counters=getattr(gaussians, "raster_work_counters", None))
     return fw
 
 

@@ -150,13 +150,13 @@ class UnifiedAdam:
 
 
 def _pinned_zeros(shape):
-    t = torch.zeros(shape, dtype=torch.float32)
-    return t.pin_memory() if torch.cuda.is_available() else t
+    # allocated pinned directly (Tensor.pin_memory() would allocate pageable memory first and copy: at C4 that is
+    # 78 GB of extra host traffic and, transiently, twice the memory)
+    return torch.zeros(shape, dtype=torch.float32, pin_memory=torch.cuda.is_available())
 
 
 def _pinned_empty(shape):
-    t = torch.empty(shape, dtype=torch.float32)
-    return t.pin_memory() if torch.cuda.is_available() else t
+    return torch.empty(shape, dtype=torch.float32, pin_memory=torch.cuda.is_available())
 
 
 def get_expon_lr_func(lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, max_steps=1000000):

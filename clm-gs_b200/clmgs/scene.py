@@ -10,6 +10,7 @@ Everything is numpy on the host; callers upload what they need.
 """
 from dataclasses import dataclass
 import math
+import os
 
 import numpy as np
 
@@ -36,7 +37,7 @@ CONFIGS = {
 }
 
 
-def make_gaussians(spec: SceneSpec, n=None, chunk=1_000_000, sh_out=None, sh_rows=None, want_sh=True):
+def make_gaussians(spec: SceneSpec, n=None, chunk=1_000_000, sh_out=None, sh_rows=None, want_sh=True, workers=0):
     """Returns dict of float32 arrays: xyz[N,3], log_scale[N,3], raw_quat[N,4],
     opacity_logit[N,1], sh[rows,48].
 
@@ -63,7 +64,8 @@ def make_gaussians(spec: SceneSpec, n=None, chunk=1_000_000, sh_out=None, sh_row
     if want_sh:
         sh = sh_out if sh_out is not None else np.empty((hi - lo, 48), np.float32)
         assert sh.shape[0] == hi - lo
-    for ci, s0 in enumerate(range(0, N, chunk)):
+    def gen_chunk(ci):
+        s0 = ci * chunk
         e0 = min(N, s0 + chunk)
         m = e0 - s0
         # one stream per attribute, so that a shorter chunk (n < chunk) is a prefix of the full one
@@ -92,6 +94,17 @@ def make_gaussians(spec: SceneSpec, n=None, chunk=1_000_000, sh_out=None, sh_row
             rest = 0.1 * np.random.default_rng([seed, ci, 8]).standard_normal((m, 45), dtype=np.float32)
             sh[a_ - lo:b_ - lo, :3] = dc[a_ - s0:b_ - s0]
             sh[a_ - lo:b_ - lo, 3:] = rest[a_ - s0:b_ - s0]
+
+    n_chunks = (N + chunk - 1) // chunk
+    workers = min(n_chunks, workers or (os.cpu_count() or 1))
+    if workers <= 1:
+        for ci in range(n_chunks):
+            gen_chunk(ci)
+    else:
+        # chunks are independent (own RNG streams, disjoint output rows) and numpy's generators drop the GIL
+        import concurrent.futures as cf
+        with cf.ThreadPoolExecutor(max_workers=workers) as ex:
+            list(ex.map(gen_chunk, range(n_chunks)))
     return dict(xyz=xyz, log_scale=log_scale, raw_quat=raw_quat, opacity_logit=opacity, sh=sh,
                 extent=L, spacing=spacing)
 

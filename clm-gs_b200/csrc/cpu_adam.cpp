@@ -9,9 +9,17 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <pthread.h>
+#include <sched.h>
+#include <stdlib.h>
+
 #include <algorithm>
 #include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <functional>
 #include <memory>
+#include <mutex>
 #include <new>
 #include <thread>
 #include <vector>
@@ -27,9 +35,13 @@ struct AdamConst {
     float b1, b2, eps, scale, inv_bc1, bc2_rsqrt;
 };
 
-// one row of `cols` floats; cols % 8 == 0 fast path (48 = 6 x __m256)
-template <bool ZERO_GRAD>  // ZERO_GRAD: the gradient row is known to be zero -- neither read nor re-zeroed
-inline void adam_row(float *p, float *g, float *m, float *v, const float *col_lr, int cols, const AdamConst &c) {
+// One row of `cols` floats.  Two instruction sets, one arithmetic: every operation below is a correctly rounded
+// IEEE mul / add / sqrt / div on independent lanes, and the translation unit is built with -ffp-contract=off, so the
+// 8-lane and the 16-lane variant give identical bits.  ZERO_GRAD: the gradient row is known to be zero -- it is
+// neither read nor re-zeroed.
+template <bool ZERO_GRAD>
+__attribute__((target("avx2"), always_inline)) inline void adam_row_avx2(float *p, float *g, float *m, float *v, const float *col_lr,
+                                                         int cols, const AdamConst &c) {
     int k = 0;
     const __m256 b1 = _mm256_set1_ps(c.b1), omb1 = _mm256_set1_ps(1.0f - c.b1);
     const __m256 b2 = _mm256_set1_ps(c.b2), omb2 = _mm256_set1_ps(1.0f - c.b2);
@@ -57,26 +69,177 @@ inline void adam_row(float *p, float *g, float *m, float *v, const float *col_lr
     }
 }
 
-inline void wait_flag(const volatile int32_t *flag) {
+template <bool ZERO_GRAD>
+__attribute__((target("avx2,avx512f"), always_inline)) inline void adam_row_avx512(float *p, float *g, float *m, float *v,
+                                                              const float *col_lr, int cols, const AdamConst &c) {
+    int k = 0;
+    const __m512 b1 = _mm512_set1_ps(c.b1), omb1 = _mm512_set1_ps(1.0f - c.b1);
+    const __m512 b2 = _mm512_set1_ps(c.b2), omb2 = _mm512_set1_ps(1.0f - c.b2);
+    const __m512 eps = _mm512_set1_ps(c.eps), sc = _mm512_set1_ps(c.scale);
+    const __m512 ibc1 = _mm512_set1_ps(-c.inv_bc1), bc2r = _mm512_set1_ps(c.bc2_rsqrt);
+    for (; k + 16 <= cols; k += 16) {  // a 48-float SH row = 3 x 64-byte lines = 3 iterations
+        __m512 gg = ZERO_GRAD ? _mm512_setzero_ps() : _mm512_mul_ps(_mm512_loadu_ps(g + k), sc);
+        __m512 mm = _mm512_add_ps(_mm512_mul_ps(b1, _mm512_loadu_ps(m + k)), _mm512_mul_ps(omb1, gg));
+        __m512 vv = _mm512_add_ps(_mm512_mul_ps(b2, _mm512_loadu_ps(v + k)), _mm512_mul_ps(omb2, _mm512_mul_ps(gg, gg)));
+        __m512 denom = _mm512_add_ps(_mm512_mul_ps(_mm512_sqrt_ps(vv), bc2r), eps);
+        __m512 step = _mm512_mul_ps(_mm512_mul_ps(_mm512_loadu_ps(col_lr + k), ibc1), _mm512_div_ps(mm, denom));
+        _mm512_storeu_ps(p + k, _mm512_add_ps(_mm512_loadu_ps(p + k), step));
+        _mm512_storeu_ps(m + k, mm);
+        _mm512_storeu_ps(v + k, vv);
+        if (!ZERO_GRAD) _mm512_storeu_ps(g + k, _mm512_setzero_ps());
+    }
+    for (; k < cols; ++k) {
+        float gg = ZERO_GRAD ? 0.f : g[k] * c.scale;
+        float mm = c.b1 * m[k] + (1.0f - c.b1) * gg;
+        float vv = c.b2 * v[k] + (1.0f - c.b2) * gg * gg;
+        float denom = sqrtf(vv) * c.bc2_rsqrt + c.eps;
+        p[k] += -(col_lr[k] * c.inv_bc1) * (mm / denom);
+        m[k] = mm; v[k] = vv;
+        if (!ZERO_GRAD) g[k] = 0.f;
+    }
+}
+
+inline bool use_avx512() {
+    static const bool v = [] {
+        const char *e = getenv("CLMGS_CPU_ADAM_ISA");  // "avx2" forces the 8-lane path
+        if (e && !strcmp(e, "avx2")) return false;
+        return (bool)__builtin_cpu_supports("avx512f");
+    }();
+    return v;
+}
+
+// Rows [a,b) of a row list (or of the identity when rows == nullptr).  One function per instruction set, so that
+// the 8-lane build never contains a 512-bit instruction.
+#define CLMGS_ADAM_ROWS(NAME, TARGET, ROWFN)                                                                          \
+    template <bool ZERO_GRAD>                                                                                        \
+    __attribute__((target(TARGET))) void NAME(float *param, float *grad, float *exp_avg, float *exp_avg_sq,          \
+                                              const float *col_lr, int cols, const int32_t *rows, int64_t a,         \
+                                              int64_t b, const AdamConst &c) {                                       \
+        for (int64_t r = a; r < b; ++r) {                                                                            \
+            const int64_t base = (int64_t)(rows ? rows[r] : r) * cols;                                               \
+            if (rows && r + 4 < b) {                                                                                 \
+                const int64_t nb = (int64_t)rows[r + 4] * cols;                                                      \
+                _mm_prefetch((const char *)(param + nb), _MM_HINT_T0);                                               \
+                if (!ZERO_GRAD) _mm_prefetch((const char *)(grad + nb), _MM_HINT_T0);                                \
+                _mm_prefetch((const char *)(exp_avg + nb), _MM_HINT_T0);                                             \
+                _mm_prefetch((const char *)(exp_avg_sq + nb), _MM_HINT_T0);                                          \
+            }                                                                                                        \
+            ROWFN<ZERO_GRAD>(param + base, grad + base, exp_avg + base, exp_avg_sq + base, col_lr, cols, c);         \
+        }                                                                                                            \
+    }
+CLMGS_ADAM_ROWS(adam_rows_avx2, "avx2", adam_row_avx2)
+CLMGS_ADAM_ROWS(adam_rows_avx512, "avx2,avx512f", adam_row_avx512)
+#undef CLMGS_ADAM_ROWS
+
+template <bool ZERO_GRAD>
+inline void adam_rows(float *param, float *grad, float *exp_avg, float *exp_avg_sq, const float *col_lr, int cols,
+                      const int32_t *rows, int64_t a, int64_t b, const AdamConst &c) {
+    if (use_avx512()) adam_rows_avx512<ZERO_GRAD>(param, grad, exp_avg, exp_avg_sq, col_lr, cols, rows, a, b, c);
+    else adam_rows_avx2<ZERO_GRAD>(param, grad, exp_avg, exp_avg_sq, col_lr, cols, rows, a, b, c);
+}
+
+template <bool ZERO_GRAD>
+inline void adam_row(float *p, float *g, float *m, float *v, const float *col_lr, int cols, const AdamConst &c) {
+    adam_rows<ZERO_GRAD>(p, g, m, v, col_lr, cols, nullptr, 0, 1, c);
+}
+
+inline int64_t now_ns() {
+    return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// returns the nanoseconds spent waiting
+inline int64_t wait_flag(const volatile int32_t *flag) {
+    if (*flag != 0) { __atomic_thread_fence(__ATOMIC_ACQUIRE); return 0; }
+    const int64_t t0 = now_ns();
     int spins = 0;
     while (*flag == 0) {
         _mm_pause();
         if (++spins > 2000) { std::this_thread::yield(); spins = 0; }
     }
     __atomic_thread_fence(__ATOMIC_ACQUIRE);
+    return now_ns() - t0;
 }
+
+// Persistent host workers.  The host Adam runs once per training step and, in the densify / lazy paths, a few more
+// times; creating and joining one std::thread per worker per call (what round 1 did) costs a clone() + an exit per
+// thread per step and lands the new threads on whatever cores the scheduler picks.  The pool keeps its threads
+// parked on a condition variable between calls; CLMGS_CPU_ADAM_PIN=<first cpu> pins worker t to cpu (first + t)
+// modulo the cpu count (multi-process launches give each rank its own range).  One job at a time (run_mu).
+class WorkerPool {
+  public:
+    static WorkerPool &get() {
+        static WorkerPool *p = new WorkerPool();  // leaked on purpose: workers are detached and parked at exit
+        return *p;
+    }
+    template <class F>
+    void run(int n, F &&f) {
+        if (n <= 1) { f(0); return; }
+        std::lock_guard<std::mutex> serial(run_mu_);
+        std::function<void(int)> job = std::forward<F>(f);
+        {
+            std::unique_lock<std::mutex> lk(mu_);
+            while ((int)n_threads_ < n - 1) spawn(lk);
+            job_ = &job;
+            n_active_ = n - 1;   // workers 0..n-2 run tids 1..n-1; the caller runs tid 0
+            remaining_ = n - 1;
+            ++epoch_;
+        }
+        cv_start_.notify_all();
+        f(0);
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_done_.wait(lk, [&] { return remaining_ == 0; });
+        job_ = nullptr;
+    }
+
+  private:
+    void spawn(std::unique_lock<std::mutex> &) {
+        const int id = (int)n_threads_++;
+        const uint64_t born = epoch_;
+        std::thread([this, id, born] { loop(id, born); }).detach();
+    }
+    void loop(int id, uint64_t seen) {
+        const char *pin = getenv("CLMGS_CPU_ADAM_PIN");
+        if (pin && *pin) {
+            const int ncpu = (int)std::max(1u, std::thread::hardware_concurrency());
+            cpu_set_t set;
+            CPU_ZERO(&set);
+            CPU_SET((atoi(pin) + id + 1) % ncpu, &set);
+            pthread_setaffinity_np(pthread_self(), sizeof(set), &set);
+        }
+        for (;;) {
+            std::function<void(int)> *job;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_start_.wait(lk, [&] { return epoch_ != seen; });
+                seen = epoch_;
+                if (id >= n_active_) continue;
+                job = job_;
+            }
+            (*job)(id + 1);
+            {
+                std::lock_guard<std::mutex> lk(mu_);
+                if (--remaining_ == 0) cv_done_.notify_all();
+            }
+        }
+    }
+    std::mutex mu_, run_mu_;
+    std::condition_variable cv_start_, cv_done_;
+    std::function<void(int)> *job_ = nullptr;
+    size_t n_threads_ = 0;
+    int n_active_ = 0, remaining_ = 0;
+    uint64_t epoch_ = 0;
+};
 
 template <class F>
 void parallel_ranges(int64_t n, int n_threads, F f) {
     if (n <= 0) return;
     int T = (int)std::min<int64_t>(n_threads, std::max<int64_t>(1, n / 1024));
     if (T <= 1) { f((int64_t)0, n); return; }
-    std::vector<std::thread> th;
-    th.reserve(T);
-    for (int t = 0; t < T; ++t) th.emplace_back([=] { f(n * t / T, n * (t + 1) / T); });
-    for (auto &t : th) t.join();
+    WorkerPool::get().run(T, [&](int t) { f(n * t / T, n * (t + 1) / T); });
 }
 
+// statistics of the last clmgs_cpu_adam_batched_sparse_step call of this process (clmgs_cpu_adam_last_stats)
+std::atomic<int64_t> g_stat_total_ns(0), g_stat_wait_ns(0), g_stat_rows(0), g_stat_zero_rows(0);
 
 }  // namespace
 
@@ -101,24 +264,17 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
     std::vector<std::atomic<int>> seg_done(n_segments > 0 ? n_segments : 1);
     for (auto &d : seg_done) d.store(0);
     if (host_progress) *host_progress = 0;
+    const int64_t t_start = now_ns();
+    std::atomic<int64_t> max_wait(0);
     auto worker = [&](int tid) {
+        int64_t waited = 0;
         for (int m = 0; m < n_segments; ++m) {
-            if (seg_signal[m] >= 0 && h_signal) wait_flag(h_signal + seg_signal[m]);  // these gradients have landed
+            if (seg_signal[m] >= 0 && h_signal) waited += wait_flag(h_signal + seg_signal[m]);  // these gradients have landed
             const int64_t lo = seg_begin[m], hi = seg_end[m], n = hi - lo;
             const bool zg = seg_zero_grad && seg_zero_grad[m];
             const int64_t a = lo + n * tid / n_threads, b = lo + n * (tid + 1) / n_threads;
-            for (int64_t r = a; r < b; ++r) {
-                const int64_t base = (int64_t)host_rows[r] * cols;
-                if (r + 4 < b) {
-                    const int64_t nb = (int64_t)host_rows[r + 4] * cols;
-                    _mm_prefetch((const char *)(host_param + nb), _MM_HINT_T0);
-                    if (!zg) _mm_prefetch((const char *)(host_grad + nb), _MM_HINT_T0);
-                    _mm_prefetch((const char *)(host_exp_avg + nb), _MM_HINT_T0);
-                    _mm_prefetch((const char *)(host_exp_avg_sq + nb), _MM_HINT_T0);
-                }
-                if (zg) adam_row<true>(host_param + base, host_grad + base, host_exp_avg + base, host_exp_avg_sq + base, col_lr, cols, c);
-                else adam_row<false>(host_param + base, host_grad + base, host_exp_avg + base, host_exp_avg_sq + base, col_lr, cols, c);
-            }
+            if (zg) adam_rows<true>(host_param, host_grad, host_exp_avg, host_exp_avg_sq, col_lr, cols, host_rows, a, b, c);
+            else adam_rows<false>(host_param, host_grad, host_exp_avg, host_exp_avg_sq, col_lr, cols, host_rows, a, b, c);
             // the last thread to finish segment m publishes "segments 0..m are done" (threads run the
             // segments in order, so completion is monotonic)
             if (seg_done[m].fetch_add(1, std::memory_order_acq_rel) + 1 == n_threads && host_progress) {
@@ -126,12 +282,30 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
                 *host_progress = m + 1;
             }
         }
+        int64_t cur = max_wait.load();
+        while (waited > cur && !max_wait.compare_exchange_weak(cur, waited)) {}
     };
-    if (n_threads == 1) { worker(0); return CLMGS_OK; }
-    std::vector<std::thread> th;
-    th.reserve(n_threads);
-    for (int t = 0; t < n_threads; ++t) th.emplace_back(worker, t);
-    for (auto &t : th) t.join();
+    WorkerPool::get().run(n_threads, worker);
+    int64_t rows = 0, zrows = 0;
+    for (int m = 0; m < n_segments; ++m) {
+        rows += seg_end[m] - seg_begin[m];
+        if (seg_zero_grad && seg_zero_grad[m]) zrows += seg_end[m] - seg_begin[m];
+    }
+    g_stat_total_ns = now_ns() - t_start;
+    g_stat_wait_ns = max_wait.load();
+    g_stat_rows = rows;
+    g_stat_zero_rows = zrows;
+    return CLMGS_OK;
+}
+
+// out[4] = {wall milliseconds of the last batched_sparse_step call, milliseconds of it spent waiting for gradient
+// flags (the slowest thread's), rows updated, of which rows with the zero-gradient shortcut}.
+CLMGS_EXPORT int clmgs_cpu_adam_last_stats(double *host_out4) {
+    if (!host_out4) { clmgs_set_error("cpu_adam_last_stats: null pointer"); return CLMGS_ERR_INVALID; }
+    host_out4[0] = g_stat_total_ns.load() * 1e-6;
+    host_out4[1] = g_stat_wait_ns.load() * 1e-6;
+    host_out4[2] = (double)g_stat_rows.load();
+    host_out4[3] = (double)g_stat_zero_rows.load();
     return CLMGS_OK;
 }
 

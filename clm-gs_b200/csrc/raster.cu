@@ -95,13 +95,19 @@ __device__ __forceinline__ int stage_compact(bool keep, int tr, int *s_wcnt, int
     return total;
 }
 
-template <bool HAS_BG>
+// COUNT: also accumulate the work counters the bench's FLOP roofline needs into counters[0..2]:
+//   [0] P_f = sum over pixels of the list entries the REFERENCE kernel examines (tile start through the entry
+//             that terminates the pixel, or the whole list) -- the algorithmic figure, independent of the pruning
+//   [1] entries this kernel actually evaluated per pixel (after tile-touch pruning and row skipping)
+//   [2] P_b = sum over pixels of (last blended entry - tile start + 1): what the reference backward walks
+template <bool HAS_BG, bool COUNT>
 __global__ void __launch_bounds__(kBlock)
 raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float *__restrict__ conics,
                   const float *__restrict__ colors, const float *__restrict__ opacities,
                   const float *__restrict__ backgrounds, const int32_t *__restrict__ tile_offsets,
                   const int32_t *__restrict__ flatten_ids, float *__restrict__ render_colors,
-                  float *__restrict__ render_alphas, int32_t *__restrict__ last_ids) {
+                  float *__restrict__ render_alphas, int32_t *__restrict__ last_ids,
+                  unsigned long long *__restrict__ counters) {
     __shared__ float4 s_a[kBlock];  // x, y, conic.x, conic.y
     __shared__ float4 s_b[kBlock];  // conic.z, opacity, r, g
     __shared__ float4 s_c[kBlock];  // b, first row, last row (pixel-centre y), position in the batch
@@ -124,6 +130,8 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
 
     float T = 1.0f, r = 0.f, g = 0.f, b = 0.f;
     int cur_idx = 0;
+    int n_examined = inside ? end - start : 0, n_eval = 0;  // COUNT only
+    bool blended = false;
     for (int bt = 0; bt < num_batches; ++bt) {
         if (__syncthreads_count(done) >= kBlock) break;
         const int batch_start = start + kBlock * bt;
@@ -153,12 +161,18 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
             const float dx = A.x - px, dy = A.y - py;
             const float sigma = 0.5f * (A.z * dx * dx + Bv.x * dy * dy) + A.w * dx * dy;
             const float alpha = fminf(0.999f, Bv.y * __expf(-sigma));
+            if (COUNT) ++n_eval;
             if (sigma < 0.f || alpha < 1.f / 255.f) continue;
             const float next_T = T * (1.0f - alpha);
-            if (next_T <= 1e-4f) { done = true; break; }
+            if (next_T <= 1e-4f) {
+                done = true;
+                if (COUNT) n_examined = batch_start + __float_as_int(Cc.w) - start + 1;
+                break;
+            }
             const float vis = alpha * T;
             r += Bv.z * vis; g += Bv.w * vis; b += Cc.x * vis;
             cur_idx = batch_start + __float_as_int(Cc.w);
+            if (COUNT) blended = true;
             T = next_T;
         }
     }
@@ -172,13 +186,27 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
         render_colors[3 * pix] = r; render_colors[3 * pix + 1] = g; render_colors[3 * pix + 2] = b;
         last_ids[pix] = cur_idx;
     }
+    if (COUNT) {
+        int n_back = blended ? cur_idx - start + 1 : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            n_examined += __shfl_xor_sync(0xffffffffu, n_examined, o);
+            n_eval += __shfl_xor_sync(0xffffffffu, n_eval, o);
+            n_back += __shfl_xor_sync(0xffffffffu, n_back, o);
+        }
+        if ((tr & 31) == 0) {
+            atomicAdd(counters + 0, (unsigned long long)n_examined);
+            atomicAdd(counters + 1, (unsigned long long)n_eval);
+            atomicAdd(counters + 2, (unsigned long long)n_back);
+        }
+    }
 }
 
-CLMGS_EXPORT int clmgs_rasterize_fwd(int C, int64_t N, int64_t n_isects, const float *means2d, const float *conics,
-                                     const float *colors, const float *opacities, const float *backgrounds,
-                                     int width, int height, int tile_size, int tile_width, int tile_height,
-                                     const int32_t *tile_offsets, const int32_t *flatten_ids, float *render_colors,
-                                     float *render_alphas, int32_t *last_ids, void *stream) {
+static int rasterize_fwd_impl(int C, int64_t N, int64_t n_isects, const float *means2d, const float *conics,
+                              const float *colors, const float *opacities, const float *backgrounds,
+                              int width, int height, int tile_size, int tile_width, int tile_height,
+                              const int32_t *tile_offsets, const int32_t *flatten_ids, float *render_colors,
+                              float *render_alphas, int32_t *last_ids, unsigned long long *counters, void *stream) {
     CLMGS_REQUIRE(tile_size == kTile, "rasterize: tile_size must be 16 (got %d)", tile_size);
     CLMGS_REQUIRE(tile_width * kTile >= width && tile_height * kTile >= height,
                   "rasterize: tile grid %dx%d does not cover %dx%d", tile_width, tile_height, width, height);
@@ -187,16 +215,39 @@ CLMGS_EXPORT int clmgs_rasterize_fwd(int C, int64_t N, int64_t n_isects, const f
     RasterArgs a{C, N, n_isects, width, height, tile_width, tile_height};
     dim3 grid(tile_width, tile_height, C), block(kTile, kTile, 1);
     cudaStream_t st = as_stream(stream);
-    if (backgrounds)
-        raster_fwd_kernel<true><<<grid, block, 0, st>>>(a, (const float2 *)means2d, conics, colors, opacities,
-                                                        backgrounds, tile_offsets, flatten_ids, render_colors,
-                                                        render_alphas, last_ids);
-    else
-        raster_fwd_kernel<false><<<grid, block, 0, st>>>(a, (const float2 *)means2d, conics, colors, opacities,
-                                                         backgrounds, tile_offsets, flatten_ids, render_colors,
-                                                         render_alphas, last_ids);
+#define LAUNCH_FWD(BG, CNT)                                                                                      \
+    raster_fwd_kernel<BG, CNT><<<grid, block, 0, st>>>(a, (const float2 *)means2d, conics, colors, opacities,      \
+                                                       backgrounds, tile_offsets, flatten_ids, render_colors,      \
+                                                       render_alphas, last_ids, counters)
+    if (counters) { if (backgrounds) LAUNCH_FWD(true, true); else LAUNCH_FWD(false, true); }
+    else { if (backgrounds) LAUNCH_FWD(true, false); else LAUNCH_FWD(false, false); }
+#undef LAUNCH_FWD
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_rasterize_fwd(int C, int64_t N, int64_t n_isects, const float *means2d, const float *conics,
+                                     const float *colors, const float *opacities, const float *backgrounds,
+                                     int width, int height, int tile_size, int tile_width, int tile_height,
+                                     const int32_t *tile_offsets, const int32_t *flatten_ids, float *render_colors,
+                                     float *render_alphas, int32_t *last_ids, void *stream) {
+    return rasterize_fwd_impl(C, N, n_isects, means2d, conics, colors, opacities, backgrounds, width, height, tile_size,
+                              tile_width, tile_height, tile_offsets, flatten_ids, render_colors, render_alphas, last_ids,
+                              nullptr, stream);
+}
+
+// Same outputs, plus work_counters[3] (device, uint64, ACCUMULATED into: the caller zeroes them) -- see the COUNT
+// note on the kernel.  Measurement only.
+CLMGS_EXPORT int clmgs_rasterize_fwd_counted(int C, int64_t N, int64_t n_isects, const float *means2d,
+                                             const float *conics, const float *colors, const float *opacities,
+                                             const float *backgrounds, int width, int height, int tile_size,
+                                             int tile_width, int tile_height, const int32_t *tile_offsets,
+                                             const int32_t *flatten_ids, float *render_colors, float *render_alphas,
+                                             int32_t *last_ids, int64_t *work_counters, void *stream) {
+    CLMGS_REQUIRE(work_counters != nullptr, "rasterize_fwd_counted: work_counters is null");
+    return rasterize_fwd_impl(C, N, n_isects, means2d, conics, colors, opacities, backgrounds, width, height, tile_size,
+                              tile_width, tile_height, tile_offsets, flatten_ids, render_colors, render_alphas, last_ids,
+                              (unsigned long long *)work_counters, stream);
 }
 
 // ---------------------------------------------------------------------------

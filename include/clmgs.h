@@ -214,6 +214,18 @@ int clmgs_rasterize_fwd(int C, int64_t N, int64_t n_isects, const float *means2d
                         int tile_width, int tile_height, const int32_t *tile_offsets,
                         const int32_t *flatten_ids, float *render_colors, float *render_alphas,
                         int32_t *last_ids, void *stream);
+/* Measurement variant of clmgs_rasterize_fwd (no counterpart in the reference): same outputs, and
+ * work_counters[3] (device int64, accumulated into -- zero them first) receive
+ *   [0] P_f: list entries the reference forward examines per pixel, summed (27 P_f FLOP),
+ *   [1] entries this kernel evaluated per pixel after its tile-touch pruning, summed,
+ *   [2] P_b: last blended entry - tile start + 1 per pixel, summed (75 P_b FLOP for the backward). */
+int clmgs_rasterize_fwd_counted(int C, int64_t N, int64_t n_isects, const float *means2d,
+                                const float *conics, const float *colors, const float *opacities,
+                                const float *backgrounds, int width, int height, int tile_size,
+                                int tile_width, int tile_height, const int32_t *tile_offsets,
+                                const int32_t *flatten_ids, float *render_colors, float *render_alphas,
+                                int32_t *last_ids, int64_t *work_counters, void *stream);
+
 int clmgs_rasterize_bwd(int C, int64_t N, int64_t n_isects, const float *means2d,
                         const float *conics, const float *colors, const float *opacities,
                         const float *backgrounds, int width, int height, int tile_size,
@@ -403,6 +415,11 @@ int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, floa
                                        const volatile int32_t *h_signal, float b1,
                                        float b2, float eps, int64_t step, float scale,
                                        int n_threads, volatile int64_t *host_progress);
+/* Statistics of this process's last clmgs_cpu_adam_batched_sparse_step call (measurement; no counterpart
+ * in the reference apart from --log_cpu_adam_trailing_overhead, engine.py:888-917): host_out4 =
+ * {wall ms of the call, ms of it spent waiting for gradient flags (slowest thread), rows updated,
+ * of which rows that took the zero-gradient shortcut}. */
+int clmgs_cpu_adam_last_stats(double *host_out4);
 
 /* What the rasteriser consumes, in one call: clmgs_isect_emit_sort (sorted) + clmgs_isect_offset_encode
  * without materialising the 64-bit isect_ids -- the last radix pass writes flatten_ids [n_isects] at the

@@ -146,9 +146,22 @@ def test_rasterize_fwd_vs_oracle(W, H, n, bg):
     tw, th = (W + 15) // 16, (H + 15) // 16
     _, ids, flat = oracle.isect_tiles(means2d, radii, depths, 16, tw, th)
     off = oracle.isect_offset_encode(ids, 2, tw, th)
-    rc_r, ra_r, last_r, _ = oracle.rasterize_fwd(means2d, conics, colors, opacs, W, H, 16, off, flat, bgs)
+    rc_r, ra_r, last_r, examined_r = oracle.rasterize_fwd(means2d, conics, colors, opacs, W, H, 16, off, flat, bgs)
     rc, ra, last = ops.rasterize_fwd(_t(means2d), _t(conics), _t(colors), _t(opacs), W, H, 16, _t(off), _t(flat),
                                      None if bgs is None else _t(bgs))
+    # measurement variant: identical outputs + the work counters of the FLOP roofline
+    wc = torch.zeros(3, dtype=torch.int64, device=rc.device)
+    rc2, ra2, last2 = ops.rasterize_fwd(_t(means2d), _t(conics), _t(colors), _t(opacs), W, H, 16, _t(off), _t(flat),
+                                        None if bgs is None else _t(bgs), work_counters=wc)
+    assert torch.equal(rc, rc2) and torch.equal(ra, ra2) and torch.equal(last, last2)
+    p_f, n_eval, p_b = wc.tolist()
+    assert abs(p_f - examined_r) <= 1e-4 * examined_r, (p_f, examined_r)   # threshold flips only
+    assert 0 < n_eval <= p_f
+    tile = (np.arange(H)[:, None] // 16) * tw + (np.arange(W)[None, :] // 16)
+    start = off.reshape(2, -1)[:, tile.reshape(-1)].reshape(2, H, W)
+    blended = (ra_r[..., 0] > 0)
+    p_b_ref = int(((last_r - start + 1) * blended).sum())
+    assert abs(p_b - p_b_ref) <= 1e-4 * p_b_ref, (p_b, p_b_ref)
     rc, ra, last = rc.cpu().numpy(), ra.cpu().numpy(), last.cpu().numpy()
     err = np.abs(rc - rc_r).max(-1)
     # north_star: rendered images within 1e-4 absolute.  A pixel whose alpha sits within an

@@ -204,3 +204,37 @@ def test_lazy_catch_up_rejects_bad_arguments():
     ls[1] = -5
     with pytest.raises(_lib.ClmgsError, match="negative"):
         L.call("clmgs_cpu_adam_lazy_catch_up", t[0], t[1], t[2], 48, lr, None, 4, ls, 3, 3, 0.9, 0.999, 1e-8, 1)
+
+
+def test_cpu_adam_avx2_and_avx512_rows_are_bit_identical_and_stats_are_reported():
+    """The host Adam picks AVX-512 rows where the CPU has them and AVX2 rows elsewhere; the two must give the same
+    bits (they are built without FMA contraction).  Each ISA runs in its own process (the choice is made once)."""
+    import subprocess
+    import sys
+    code = r'''
+import sys, hashlib, numpy as np
+sys.path[:0] = [%r, %r]
+from clmgs import ops, _lib
+rng = np.random.default_rng(11)
+N = 30011
+p = rng.standard_normal((N, 48)).astype(np.float32); g = rng.standard_normal((N, 48)).astype(np.float32)
+m = (rng.standard_normal((N, 48)) * 0.1).astype(np.float32); v = (rng.random((N, 48)) * 0.01).astype(np.float32)
+col_lr = np.array([2.5e-3] * 3 + [2.5e-3 / 20] * 45, np.float32)
+rows = rng.permutation(N).astype(np.int32)
+sig = np.ones(2, np.int32)
+for step in (1, 2, 3):   # persistent pool: several calls, different thread counts
+    ops.cpu_adam_batched_sparse_step(p, g, m, v, col_lr, rows, [0, N // 3], [N // 3, N], [0, 1], sig, 0.9, 0.999, 1e-15,
+                                     step, 0.25, n_threads=1 + step, seg_zero_grad=[1, 0])
+    g[:] = rng.standard_normal((N, 48)).astype(np.float32)
+st = np.zeros(4)
+_lib.call("clmgs_cpu_adam_last_stats", st)
+assert st[2] == N and st[3] == N // 3 and st[0] > 0 and st[1] >= 0, st
+print(hashlib.sha256(p.tobytes() + m.tobytes() + v.tobytes()).hexdigest())
+''' % (ROOT, os.path.join(ROOT, "clm-gs_b200"))
+    digests = {}
+    for isa in ("avx2", "auto"):
+        env = dict(os.environ, CLMGS_CPU_ADAM_ISA=isa)
+        r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+        digests[isa] = r.stdout.strip().splitlines()[-1]
+    assert digests["avx2"] == digests["auto"], digests
