@@ -479,7 +479,7 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
     if pipe:
         # return with the host Adam (and the tail of the GPU work) still running; the next call or
         # wait_host_adam() picks it up.  Everything that crosses streams carries record_stream marks.
-        gaussians.last_batch_stats = dict(n_union=n_union, n_visible=[f.shape[0] for f in filters],
+        gaussians.last_batch_stats = dict(n_union=n_union, n_first=int(fe[1]), n_visible=[f.shape[0] for f in filters],
                                           n_isects=n_isects_log)
         return losses, ordered_cams, sparsity
     import time as _t
@@ -494,7 +494,7 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
     torch.cuda.synchronize()
     if timer.enabled:
         timer.collect()
-    gaussians.last_batch_stats = dict(cpu_adam_trailing_ms=join_ms, n_union=n_union,
+    gaussians.last_batch_stats = dict(cpu_adam_trailing_ms=join_ms, n_union=n_union, n_first=int(fe[1]),
                                       n_visible=[f.shape[0] for f in filters],
                                       n_isects=n_isects_log)
     return losses, ordered_cams, sparsity

@@ -35,6 +35,11 @@ class DistContext:
         self.lo, self.hi = self.shard.range_of(self.rank)
 
 
+def training_setup_dist(gaussians, args, ctx):
+    """Optimiser set-up of a rank (TrainArgs.bsz = GLOBAL batch)."""
+    return gaussians.training_setup(args)
+
+
 def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters_grad_buffer, background, pipe_args,
                                      comm_stream, perm_generator, ctx: DistContext, timer=None):
     """gaussians._parameters / parameters_grad_buffer / host-Adam state hold this rank's SHARD
