@@ -108,7 +108,7 @@ LAUNCHES = dict(clmgs_cull_count=2, clmgs_cull_emit=1, clmgs_gather_activate=1, 
                 clmgs_selective_adam=1, clmgs_adam_dense=1, clmgs_extract_first_use=1, clmgs_slot_map=1,
                 clmgs_rows_gather_i32=1, clmgs_rows_flush_slots=1, clmgs_sh_colors_fwd_slots=1,
                 clmgs_sh_colors_bwd_slots=1, clmgs_densification_stats=1, clmgs_rows_accumulate=1,
-                clmgs_rows_scatter_grad_i64=1)
+                clmgs_rows_scatter_grad_i64=1, clmgs_rows_gather_to_slots=1)
 
 
 def count_launches(lib):
@@ -206,7 +206,12 @@ def run_ours(a):
     # the Adam moments of the GPU-resident attributes sharded by Gaussian id (clmgs/engine_dist.py).
     ctx = engine_dist.DistContext(N) if world > 1 else None
     lo, hi = (ctx.lo, ctx.hi) if ctx else (0, N)
-    sh_host = torch.empty(hi - lo, 48, dtype=torch.float32, pin_memory=True)
+    if ctx is not None:
+        # the SH parameter table is ONE node-shared host mapping that every rank's GPU reads (clmgs/shm.py); each
+        # rank generates and later updates only its own rows
+        sh_host = ctx.create_shared_table().tensor[lo:hi]
+    else:
+        sh_host = torch.empty(hi - lo, 48, dtype=torch.float32, pin_memory=True)
     g = S.make_gaussians(spec, sh_out=sh_host.numpy(), sh_rows=(lo, hi),
                          workers=max(1, (os.cpu_count() or 1) // world))  # each rank generates only its SH shard
     args = model.TrainArgs(bsz=global_batch, sparse_adam=sparse_adam, cpu_adam_threads=host_threads)

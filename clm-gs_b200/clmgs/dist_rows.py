@@ -17,9 +17,14 @@ import torch.distributed as dist
 
 
 class ShardMap:
+    """Equal shards of `shard` = ceil(N / world) ids (the last one may be shorter): the same partition serves the
+    host tables and the NCCL reduce-scatter / all-gather of the GPU-resident attributes, which need equal counts
+    (tensors are padded to world x shard rows)."""
+
     def __init__(self, n_total: int, world: int):
         self.n_total, self.world = int(n_total), int(world)
-        self.bounds = [self.n_total * g // self.world for g in range(self.world + 1)]
+        self.shard = -(-self.n_total // self.world)
+        self.bounds = [min(self.n_total, g * self.shard) for g in range(self.world + 1)]
 
     def range_of(self, rank):
         return self.bounds[rank], self.bounds[rank + 1]
@@ -74,3 +79,22 @@ class RowExchange:
         dist.all_to_all_single(recv, grad_rows.contiguous(), output_split_sizes=plan.recv_counts,
                                input_split_sizes=plan.send_counts, group=self.group)
         accumulate_local(plan.recv_local, recv)
+
+
+def merge_requests(recv_local: torch.Tensor, n_local: int, want_untouched: bool = False):
+    """Owner side of the sparse reduce-scatter: several ranks return gradients for the same row.  From the
+    requester-major list of requested LOCAL rows (ascending per requester, repeats across requesters) build, without
+    sorting (a flag table over the shard + its compaction -- the lists are already ordered):
+      uniq       ascending distinct local rows (= the rows this rank's host Adam updates)
+      dst_index  position of every received row in `uniq` (where its gradient is accumulated)
+      untouched  ascending local rows nobody asked for (dense Adam still decays their moments), or None.
+    One host sync (the size of uniq).  Device-agnostic: torch indexing only."""
+    dev = recv_local.device
+    mask = torch.zeros(n_local, dtype=torch.bool, device=dev)
+    mask[recv_local] = True
+    uniq = torch.nonzero(mask).flatten()
+    pos = torch.empty(n_local, dtype=torch.int64, device=dev)
+    pos[uniq] = torch.arange(uniq.shape[0], dtype=torch.int64, device=dev)
+    dst_index = pos[recv_local]
+    untouched = torch.nonzero(~mask).flatten() if want_untouched else None
+    return uniq, dst_index, untouched, mask

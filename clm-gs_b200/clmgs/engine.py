@@ -121,15 +121,20 @@ def wait_host_adam(gaussians):
             raise pend["err"][0]
 
 
-def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, timer=_NULL_TIMER, parity=0):
+def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, timer=_NULL_TIMER, parity=0,
+                      host_rows=True):
     """engine.py:135-298: camera order (TSP over sampled visibility distance), ordered bitmap,
-    per-Gaussian last-use groups for the host Adam."""
+    per-Gaussian last-use groups for the host Adam.  host_rows=False (multi-GPU engine: the host Adam's row lists
+    come from the gradient exchange) skips the last-use grouping and its N x 4-byte device->host copy.
+    perm_generator: a CPU or a CUDA torch.Generator (the reference passes a CUDA one, train.py:191), or None."""
     bitmap = cull["bitmap"]
     dev = bitmap.device
     with timer("order"):
         n_sampled = max(1, n_gaussians // (bsz * bsz) if bsz >= 32 else n_gaussians // 32)
         stride = max(1, n_gaussians // n_sampled)
-        off = int(torch.randint(0, stride, (1,), generator=perm_generator).item()) if perm_generator is not None else 0
+        off = 0
+        if perm_generator is not None:  # drawn on the generator's own device
+            off = int(torch.randint(0, stride, (1,), generator=perm_generator, device=perm_generator.device).item())
         sample_ids = torch.arange(n_sampled, device=dev, dtype=torch.int64) * stride + off
         sample_ids.clamp_(max=n_gaussians - 1)
         dist = ops.bitmap_distance(bitmap, bsz, sample_ids).cpu().numpy()  # D2H sync (reference: .tolist())
@@ -145,24 +150,28 @@ def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, tim
         sparsity = [f.shape[0] / float(n_gaussians) for f in filters]
         ordered_bitmap = ops.bitmap_permute(bitmap, bsz, ordered_cams)
         ffs = ops.extract_ffs(ordered_bitmap)
-        rows_dev, counts = ops.group_by_ffs(ffs, bsz)
-        rows_host = _pinned_rows_buffer(n_gaussians, parity)
-        rows_host.copy_(rows_dev, non_blocking=True)
+        rows_dev = counts = rows_host = None
+        if host_rows:
+            rows_dev, counts = ops.group_by_ffs(ffs, bsz)
+            rows_host = _pinned_rows_buffer(n_gaussians, parity)
+            rows_host.copy_(rows_dev, non_blocking=True)
         # batch-resident rows: Gaussians grouped by the first camera that needs them; a Gaussian's slot in the
         # device row table is its position in that grouping (so each first-use group is a contiguous slot range)
         first = ops.extract_first_use(ordered_bitmap, bsz)
         first_rows_dev, first_counts = ops.group_by_ffs(first, bsz)
-        counts_h = counts.cpu().numpy()  # sync: also completes the rows copy above (same stream)
+        counts_h = counts.cpu().numpy() if host_rows else None  # sync: also completes the rows copy above (same stream)
         first_counts_h = first_counts.cpu().numpy()
         n_untouched = int(first_counts_h[0])
         union_ids = first_rows_dev[n_untouched:]
         slot_of = torch.empty(n_gaussians, dtype=torch.int32, device=dev)
         ops.slot_map(union_ids, slot_of)
-    offs = np.concatenate([[0], np.cumsum(counts_h)]).astype(np.int64)
-    # group m of the host Adam = rows whose last user is camera m-1 <-> ffs key bsz+1-m (engine.py:213)
-    keys = [0] + [bsz + 1 - m for m in range(1, bsz + 1)]
-    row_begin = np.ascontiguousarray(offs[keys], dtype=np.int64)
-    row_end = np.ascontiguousarray(offs[[k + 1 for k in keys]], dtype=np.int64)
+    row_begin = row_end = None
+    if host_rows:
+        offs = np.concatenate([[0], np.cumsum(counts_h)]).astype(np.int64)
+        # group m of the host Adam = rows whose last user is camera m-1 <-> ffs key bsz+1-m (engine.py:213)
+        keys = [0] + [bsz + 1 - m for m in range(1, bsz + 1)]
+        row_begin = np.ascontiguousarray(offs[keys], dtype=np.int64)
+        row_end = np.ascontiguousarray(offs[[k + 1 for k in keys]], dtype=np.int64)
     first_edges = np.concatenate([[0], np.cumsum(first_counts_h[1:])]).astype(np.int64)  # slots of first-use group k
     return dict(ordered_cams=ordered_cams, filters=filters, sparsity=sparsity, ordered_bitmap=ordered_bitmap,
                 visibility=ffs, rows_host=rows_host, rows_dev=rows_dev, row_begin=row_begin, row_end=row_end,

@@ -1,17 +1,30 @@
-"""Multi-GPU training iteration: cameras data-parallel, offloaded SH state sharded by Gaussian id.
+"""Multi-GPU training iteration on one node: cameras data-parallel, Gaussian state sharded by id.
 
-New design -- the reference is single-GPU.  One process per GPU:
+New design -- the reference is single-GPU.  One process per GPU, global batch = all ranks' cameras,
+ONE optimiser step per call.  Rank g owns the Gaussian range [g S, (g+1) S), S = ceil(N / G):
 
-  replicated : the 11 GPU-resident floats per Gaussian + their Adam moments (every rank culls all N)
-  sharded    : rank g owns SH rows [N g/G, N (g+1)/G): pinned table, gradient table, host-Adam moments
-  per batch  : 1. each rank culls / orders ITS cameras (global batch = all ranks' cameras)
-               2. SH rows of the union of its cameras come from their owners: ids all-to-all, owners gather
-                  from pinned host with the zero-copy kernel, rows all-to-all-v over NCCL/NVLink into a
-                  per-batch device cache (HBM is plentiful on B200: no per-camera retention needed)
-               3. cameras render from the cache; SH gradients accumulate into a cache-shaped buffer
-               4. dense gradients of the replicated attributes: NCCL all-reduce, identical Adam on all ranks
-               5. SH gradients go back to owners (all-to-all-v), are summed there (vector atomics), stored to
-                  the pinned gradient shard and consumed by the owner's host Adam
+  replicated : the 11 GPU-resident floats per Gaussian (every rank culls all N for its cameras)
+  sharded    : Adam moments of those 11 floats (ShardedGpuAdam), pinned gradient table, host-Adam moments and the
+               responsibility for updating the SH rows of the range
+  shared     : the SH parameter table itself -- one node-shared host mapping registered with every rank's GPU
+               (clmgs/shm.py), so a rank reads the rows its cameras need from host DRAM over its OWN PCIe link with
+               the single-GPU zero-copy kernels and the single-GPU first-use grouping; there is no owner->renderer
+               hop and the eight host links add up
+
+  per step   : 1. cull + TSP order of the LOCAL cameras; need_ids = ascending union of their Gaussians
+               2. plan: ids all-to-all -> every owner knows which of its rows will receive gradients and from
+                  whom; it merges the (already sorted) lists with a flag table (no sort), starts its host Adam
+                  thread, which waits on per-chunk flags
+               3. copy stream loads first-use group k of the local cameras into the batch-resident rows (slots in
+                  ascending-id = owner-major order); compute stream renders camera k, accumulates SH gradients
+                  into a slot-shaped buffer and the dense gradients of the replicated attributes
+               4. sparse reduce-scatter of the SH gradients: NCCL all-to-all-v straight out of the slot buffer
+                  (owner-major already) -> owner sums duplicates with 16-byte vector atomics -> stores its rows to
+                  its pinned gradient table chunk by chunk, one flag per chunk -> host Adam consumes chunk j while
+                  chunk j+1 crosses the link
+               5. NCCL reduce-scatter of the dense gradients -> owner Adam on its slice (moments sharded) ->
+                  all-gather of the updated slices
+               6. join host Adam; barrier (the next step reads rows other ranks just updated)
   math       : identical to one GPU running the global batch, up to fp32 summation order.
 """
 import threading
@@ -21,9 +34,11 @@ import torch
 import torch.distributed as dist
 
 from . import ops
-from .dist_rows import RowExchange, ShardMap
+from .dist_rows import RowExchange, ShardMap, merge_requests
 from .engine import (StageTimer, _NULL_TIMER, backward_one_camera, calculate_filters, geometry_one_camera,
-                     shade_one_camera)
+                     order_calculation, shade_one_camera)
+
+_GPU_NAMES = ("xyz", "opacity", "scaling", "rotation")
 
 
 class DistContext:
@@ -33,123 +48,244 @@ class DistContext:
         self.shard = ShardMap(n_total, self.world)
         self.exchange = RowExchange(self.shard, self.rank, group)
         self.lo, self.hi = self.shard.range_of(self.rank)
+        self.n_total = int(n_total)
+        self.table = None            # SharedHostTable of the SH parameters (create_shared_table)
+
+    def create_shared_table(self, cols=48):
+        """The node-shared SH parameter table [N, cols]; each rank fills rows [lo, hi) and then calls
+        training_setup_dist (which registers the mapping with CUDA and synchronises the ranks)."""
+        from .shm import SharedHostTable
+        self.table = SharedHostTable(self.n_total, cols, self.group)
+        return self.table
 
 
 def training_setup_dist(gaussians, args, ctx):
-    """Optimiser set-up of a rank (TrainArgs.bsz = GLOBAL batch)."""
-    return gaussians.training_setup(args)
+    """Optimiser set-up of a rank.  args.bsz = GLOBAL batch.  gaussians was built by create_from_arrays with
+    sh = ctx.table.tensor[lo:hi] (this rank's rows of the shared table).  Pads the replicated tensors to world x S
+    rows (equal counts for reduce-scatter / all-gather) and shards the Adam moments."""
+    assert ctx.table is not None, "call ctx.create_shared_table() and fill this rank's rows first"
+    dev = gaussians._xyz.device
+    N, S, G = ctx.n_total, ctx.shard.shard, ctx.world
+    for name in ("_xyz", "_opacity", "_scaling", "_rotation"):
+        t = getattr(gaussians, name)
+        buf = torch.zeros((G * S,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+        buf[:N].copy_(t)
+        setattr(gaussians, name + "_padded", buf)
+        setattr(gaussians, name, buf[:N])
+    gaussians.training_setup(args, gpu_shard=(ctx.lo, ctx.hi))
+    gaussians.dist_ctx = ctx
+    ctx.table.register_cuda()
+    gaussians.shared_parameters = ctx.table.tensor
+    torch.cuda.synchronize()
+    dist.barrier(group=ctx.group)   # every rank's rows are in the table
+    return gaussians
 
 
 def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters_grad_buffer, background, pipe_args,
                                      comm_stream, perm_generator, ctx: DistContext, timer=None):
-    """gaussians._parameters / parameters_grad_buffer / host-Adam state hold this rank's SHARD
-    ([hi-lo, 48]); the GPU-resident tensors hold all N.  gaussians.args.bsz must be the GLOBAL batch
-    size (it scales lr / betas / eps and the gradient average, GM:180-211, engine.py:870-872).
-    Returns (losses of the local cameras, local order, local sparsity)."""
+    """See the module docstring.  gaussians._parameters / parameters_grad_buffer / host-Adam state hold this rank's
+    SHARD ([hi-lo, 48]); gaussians.shared_parameters is the whole table; the GPU-resident tensors hold all N.
+    Returns (losses of the local cameras in processed order, local order, local sparsity)."""
     timer = timer or _NULL_TIMER
     args = gaussians.args
     bsz_local = len(local_cameras)
     bsz_global = bsz_local * ctx.world
     assert args.bsz == bsz_global, "TrainArgs.bsz must be the global batch size (%d)" % bsz_global
-    N = gaussians.n_gaussians
-    dev = gaussians._xyz.device
-    h_params, h_grad = gaussians._parameters, parameters_grad_buffer[: ctx.hi - ctx.lo]
-    assert h_params.shape[0] == ctx.hi - ctx.lo, "SH table must be this rank's shard"
-
-    compute = torch.cuda.current_stream()
-    with torch.no_grad():
-        filters, cull = calculate_filters(local_cameras, gaussians, timer)
-        # local order: keep input order (TSP only matters for per-camera retention, which the cache replaces)
-        ordered = list(range(bsz_local))
-        sparsity = [f.shape[0] / float(N) for f in filters]
-        with timer("need_ids"):
-            need_ids = torch.nonzero(cull["bitmap"]).flatten()  # union of this rank's cameras, ascending
-        # geometry of the local cameras needs no SH rows: queue it on the compute stream, then run the row
-        # exchange on the copy stream so that NVLink / PCIe traffic overlaps projection + tile sort
-        geoms = [geometry_one_camera(gaussians, local_cameras[k], filters[k], timer) for k in ordered]
-        ready = torch.cuda.Event()
-        ready.record(compute)
-        with torch.cuda.stream(comm_stream):
-            comm_stream.wait_event(ready)
-            with timer("rows_exchange_in", comm_stream):
-                plan = ctx.exchange.plan(need_ids)
-
-                def gather_local(local_idx):
-                    # several ranks usually ask for the same row: read each requested row from pinned host ONCE
-                    # (PCIe), then serve every requester from device memory
-                    uniq, inv = torch.unique(local_idx, return_inverse=True)
-                    rows_u = ops._empty((uniq.shape[0], 48), torch.float32, dev)
-                    ops.rows_gather(rows_u, h_params, uniq)           # zero-copy read of my pinned shard
-                    out = ops._empty((local_idx.shape[0], 48), torch.float32, dev)
-                    ops.rows_gather(out, rows_u, inv)                 # device -> device fan-out
-                    return out
-
-                cache = ctx.exchange.fetch(plan, gather_local)
-            cache.record_stream(compute)
-            cache_ready = torch.cuda.Event()
-            cache_ready.record(comm_stream)
-        need_ids.record_stream(comm_stream)
-        # the cache is a slot table: row of Gaussian id = its rank in need_ids (same kernels as the single-GPU engine)
-        slot_of = torch.empty(N, dtype=torch.int32, device=dev)
-        ops.slot_map(need_ids.to(torch.int32), slot_of)
-        cache_grad = ops._zeros((need_ids.shape[0], 48), torch.float32, dev)
-        grads = dict(xyz=torch.zeros_like(gaussians._xyz), opacity=torch.zeros_like(gaussians._opacity),
-                     scaling=torch.zeros_like(gaussians._scaling), rotation=torch.zeros_like(gaussians._rotation))
-        losses, n_isects = [], []
-        compute.wait_event(cache_ready)
-        for k in ordered:
-            cam, ids = local_cameras[k], filters[k]
-            fw = shade_one_camera(gaussians, cam, geoms[k], cache, background, timer, ids=ids, slot_of=slot_of)
-            geoms[k] = None
-            with timer("loss"):
-                loss_vec, v_render = ops.loss_fwd_bwd(fw["render"][0], cam.original_image, args.lambda_dssim, hwc=True)
-            losses.append(loss_vec[0])
-            backward_one_camera(gaussians, cam, ids, cache, cache_grad, fw, v_render[None], grads, timer, slot_of=slot_of)
-            n_isects.append(fw["n_isects"])
-            del fw, v_render
-
-        # replicated attributes: sum gradients over ranks, same Adam everywhere
-        with timer("allreduce_dense"):
-            for g in grads.values():
-                dist.all_reduce(g, group=ctx.group)
-        visibility = None
-        if args.sparse_adam:
-            visibility = (cull["bitmap"] != 0).to(torch.uint8)
-            dist.all_reduce(visibility, op=dist.ReduceOp.MAX, group=ctx.group)
-        with timer("gpu_adam"):
-            gaussians.optimizer.gpu_adam.step(grads, visibility=visibility, grad_scale=1.0 / bsz_global)
-
-        # SH gradients back to their owners, summed there, then the owner's host Adam
-        touched = {}
-
-        def accumulate_local(local_idx, rows):
-            uniq, inv = torch.unique(local_idx, return_inverse=True)
-            acc = ops._zeros((uniq.shape[0], 48), torch.float32, dev)
-            ops.rows_accumulate(acc, rows, inv)
-            ops.rows_scatter_grad(acc, h_grad, uniq, accum=False)   # table rows are zero: plain store
-            touched["rows"] = uniq
-
-        with timer("rows_exchange_out"):
-            ctx.exchange.return_grads(plan, cache_grad, accumulate_local)
-        torch.cuda.synchronize()
+    N, S, G = gaussians.n_gaussians, ctx.shard.shard, ctx.world
     n_local = ctx.hi - ctx.lo
-    t_rows = touched["rows"]
-    if args.sparse_adam:
-        rows = t_rows.to(torch.int32).cpu().numpy()
-        seg_b, seg_e, seg_zg = [0], [len(rows)], [0]
-    else:
-        # dense Adam also decays the moments of the rows nobody touched; their gradient rows are zero, so that
-        # segment skips the gradient table
-        mask = torch.ones(n_local, dtype=torch.bool, device=dev)
-        mask[t_rows] = False
-        unt = torch.nonzero(mask).flatten()
-        rows = torch.cat([unt, t_rows]).to(torch.int32).cpu().numpy()
-        seg_b, seg_e, seg_zg = [0, int(unt.shape[0])], [int(unt.shape[0]), len(rows)], [1, 0]
-    sig = np.zeros(1, np.int32)
-    gaussians.optimizer.cpu_adam.batched_sparse_step(h_grad, rows, seg_b, seg_e, [-1] * len(seg_b), sig, 1.0 / bsz_global,
-                                                     None, seg_zg)
+    dev = gaussians._xyz.device
+    h_table = gaussians.shared_parameters
+    h_grad = parameters_grad_buffer[:n_local]
+    assert gaussians._parameters.shape[0] == n_local, "SH table view must be this rank's shard"
+    compute = torch.cuda.current_stream()
+    if getattr(gaussians, "_flush_stream", None) is None or gaussians._flush_stream.device != dev:
+        gaussians._flush_stream = torch.cuda.Stream(device=dev, priority=-1)
+    flush_stream = gaussians._flush_stream
+    cpu_adam = gaussians.optimizer.cpu_adam
+    if getattr(cpu_adam, "lazy_pending", False):
+        cpu_adam.catch_up(None)
+
+    with torch.no_grad():
+        # ---- 1. visibility + local order ---------------------------------------------------------------
+        filters, cull = calculate_filters(local_cameras, gaussians, timer)
+        oc = order_calculation(filters, cull, N, bsz_local, perm_generator, args, timer, host_rows=False)
+        ordered, filters, sparsity = oc["ordered_cams"], oc["filters"], oc["sparsity"]
+        cams = [local_cameras[i] for i in ordered]
+        union_ids, fe = oc["union_ids"], oc["first_edges"]     # grouped by first use (int32), slot edges per camera
+        n_need = int(fe[-1])
+        with timer("need_ids"):
+            # ascending union = owner-major order; slot of a Gaussian = its rank in it
+            need_ids = torch.nonzero(oc["ordered_bitmap"]).flatten()
+            assert need_ids.shape[0] == n_need
+            need32 = need_ids.to(torch.int32)
+            slot_of = torch.empty(N, dtype=torch.int32, device=dev)
+            ops.slot_map(need32, slot_of)
+
+        # ---- 2. plan + owner-side merge + host Adam thread ---------------------------------------------
+        with timer("plan"):
+            plan = ctx.exchange.plan(need_ids)
+            uniq, dst_index, untouched, touched_mask = merge_requests(plan.recv_local, n_local,
+                                                                      want_untouched=not args.sparse_adam)
+            n_uniq = int(uniq.shape[0])
+            n_unt = 0 if untouched is None else int(untouched.shape[0])
+            rows_host = _pinned_i32(gaussians, n_local)
+            if n_unt:
+                rows_host[:n_unt].copy_(untouched.to(torch.int32), non_blocking=True)
+            rows_host[n_unt:n_unt + n_uniq].copy_(uniq.to(torch.int32), non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        J = max(1, min(int(getattr(args, "final_flush_chunks", 8)), max(1, n_uniq // 65536)))
+        edges = [n_uniq * j // J for j in range(J + 1)]
+        seg_b, seg_e, seg_sig, seg_zg = [], [], [], []
+        if n_unt:  # dense Adam: untouched rows decay their moments; gradient rows are zero -> shortcut, no wait
+            seg_b.append(0); seg_e.append(n_unt); seg_sig.append(-1); seg_zg.append(1)
+        for j in range(J):
+            seg_b.append(n_unt + edges[j]); seg_e.append(n_unt + edges[j + 1]); seg_sig.append(j); seg_zg.append(0)
+        signal = _signal_flags(gaussians, J)
+        worker_err, worker_times = [], {}
+
+        def cpuadam_thread():
+            import time as _t
+            t0 = _t.perf_counter()
+            try:
+                cpu_adam.batched_sparse_step(h_grad, rows_host, seg_b, seg_e, seg_sig, signal, 1.0 / bsz_global, None,
+                                             seg_zg)
+            except Exception as e:  # surfaced after join
+                worker_err.append(e)
+            worker_times["cpu_adam_thread_ms"] = (_t.perf_counter() - t0) * 1e3
+
+        worker = threading.Thread(target=cpuadam_thread, daemon=True)
+        worker.start()
+        try:
+            out = _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, plan, uniq, dst_index,
+                                       touched_mask, edges, signal, h_table, h_grad, background, comm_stream,
+                                       flush_stream, timer)
+        except BaseException:
+            torch.cuda.synchronize()
+            signal.fill_(1)       # never leave the host-Adam thread spinning on flags that will not come
+            worker.join()
+            raise
+    import time as _t
+    comm_stream.synchronize()
+    flush_stream.synchronize()
+    compute.synchronize()
+    t_join = _t.perf_counter()
+    worker.join()
+    join_ms = (_t.perf_counter() - t_join) * 1e3
+    if worker_err:
+        raise worker_err[0]
+    # the next step's row loads read rows that OTHER ranks' host Adams just updated
+    dist.barrier(group=ctx.group)
     if timer.enabled:
         timer.collect()
-    gaussians.last_batch_stats = dict(n_visible=[f.shape[0] for f in filters], n_isects=n_isects,
-                                      n_need=int(need_ids.shape[0]), rows_from_peers=int(need_ids.shape[0] - plan.send_counts[ctx.rank]))
-    return losses, ordered, sparsity
+    gaussians.last_batch_stats = dict(n_visible=[f.shape[0] for f in filters], n_isects=out["n_isects"], n_union=n_need,
+                                      n_first=int(fe[1]), n_owner_rows=n_uniq, n_adam_rows=n_uniq,
+                                      rows_from_peers=int(n_need - plan.send_counts[ctx.rank]),
+                                      cpu_adam_trailing_ms=join_ms, **worker_times)
+    return out["losses"], ordered, sparsity
+
+
+def _pinned_i32(gaussians, n):
+    buf = getattr(gaussians, "_dist_rows_host", None)
+    if buf is None or buf.shape[0] < n:
+        buf = gaussians._dist_rows_host = torch.empty(max(n, 1), dtype=torch.int32, pin_memory=True)
+    return buf
+
+
+def _signal_flags(gaussians, n):
+    buf = getattr(gaussians, "_dist_signal", None)
+    if buf is None or buf.shape[0] != n:
+        buf = gaussians._dist_signal = torch.zeros(n, dtype=torch.int32, pin_memory=True)
+    else:
+        buf.zero_()
+    gaussians.signal_tensor_pinned = buf
+    return buf
+
+
+def _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, plan, uniq, dst_index, touched_mask,
+                         edges, signal, h_table, h_grad, background, comm_stream, flush_stream, timer):
+    args = gaussians.args
+    dev = gaussians._xyz.device
+    bsz_local, G, S = len(cams), ctx.world, ctx.shard.shard
+    bsz_global = bsz_local * G
+    n_local = ctx.hi - ctx.lo
+    compute = torch.cuda.current_stream()
+    union_ids, fe = oc["union_ids"], oc["first_edges"]
+    n_need = int(fe[-1])
+    lookahead = max(0, int(getattr(args, "geometry_lookahead", 3)))
+
+    # ---- 3. rows in (copy stream, first-use groups) + cameras (compute stream) --------------------------
+    start_evt = torch.cuda.Event()
+    start_evt.record(compute)
+    comm_stream.wait_event(start_evt)
+    with torch.cuda.stream(comm_stream):
+        d_rows = ops._empty((n_need, 48), torch.float32, dev)
+        d_rows.record_stream(compute)
+        union_ids.record_stream(comm_stream)
+        slot_of.record_stream(comm_stream)
+        rows_evt = []
+        for k in range(bsz_local):
+            a0, a1 = int(fe[k]), int(fe[k + 1])
+            with timer("rows_load_first" if k == 0 else "rows_prefetch", comm_stream):
+                ops.rows_gather_to_slots(d_rows, h_table, union_ids[a0:a1], slot_of)
+            e = torch.cuda.Event()
+            e.record(comm_stream)
+            rows_evt.append(e)
+    d_grad = ops._zeros((n_need, 48), torch.float32, dev)
+    # dense gradients of the replicated attributes, padded to G x S rows for the reduce-scatter
+    grads = {n: torch.zeros_like(getattr(gaussians, "_" + n + "_padded")) for n in _GPU_NAMES}
+    gview = {n: grads[n][: gaussians.n_gaussians] for n in _GPU_NAMES}
+    losses, n_isects, geoms = [], [], [None] * bsz_local
+    for k in range(bsz_local):
+        cam, ids = cams[k], filters[k]
+        for kk in range(k, min(bsz_local, k + 1 + lookahead)):
+            if geoms[kk] is None:
+                geoms[kk] = geometry_one_camera(gaussians, cams[kk], filters[kk], timer)
+        fw, geoms[k] = geoms[k], None
+        fw = shade_one_camera(gaussians, cam, fw, d_rows, background, timer, rows_ready=rows_evt[k], ids=ids,
+                              slot_of=slot_of)
+        with timer("loss"):
+            loss_vec, v_render = ops.loss_fwd_bwd(fw["render"][0], cam.original_image, args.lambda_dssim, hwc=True)
+        losses.append(loss_vec[0])
+        v_means2d = backward_one_camera(gaussians, cam, ids, d_rows, d_grad, fw, v_render[None], gview, timer,
+                                        slot_of=slot_of)
+        if args.densification_stats:
+            with timer("densification_stats"):
+                ops.densification_stats(ids, v_means2d[0], fw["radii"][0], cam.image_width, cam.image_height,
+                                        gaussians.max_radii2D, gaussians.xyz_gradient_accum, gaussians.denom)
+        n_isects.append(fw["n_isects"])
+        del fw, v_render, loss_vec
+
+    # ---- 4. SH gradients: sparse reduce-scatter to the owners, owner stores + flags ---------------------
+    with timer("grad_exchange"):
+        recv = torch.empty(plan.recv_local.shape[0], 48, dtype=torch.float32, device=dev)
+        dist.all_to_all_single(recv, d_grad, output_split_sizes=plan.recv_counts, input_split_sizes=plan.send_counts,
+                               group=ctx.group)
+        acc = ops._zeros((uniq.shape[0], 48), torch.float32, dev)
+        ops.rows_accumulate(acc, recv, dst_index)
+    acc_ready = torch.cuda.Event()
+    acc_ready.record(compute)
+    acc.record_stream(flush_stream)
+    uniq.record_stream(flush_stream)
+    with torch.cuda.stream(flush_stream):
+        flush_stream.wait_event(acc_ready)
+        with timer("grad_handoff", flush_stream):
+            for j in range(len(edges) - 1):
+                c0, c1 = edges[j], edges[j + 1]
+                ops.rows_scatter_grad(acc[c0:c1], h_grad, uniq[c0:c1], accum=False)   # table rows are zero: plain store
+                ops.set_signal(signal, j, 1)
+
+    # ---- 5. GPU-resident attributes: reduce-scatter -> owner Adam on its slice -> all-gather ---------------
+    shards = {}
+    with timer("reduce_scatter_dense"):
+        for n in _GPU_NAMES:
+            full = grads[n]
+            shards[n] = torch.empty((S,) + tuple(full.shape[1:]), dtype=full.dtype, device=dev)
+            dist.reduce_scatter_tensor(shards[n], full, group=ctx.group)
+    with timer("gpu_adam"):
+        vis = touched_mask.view(torch.uint8) if args.sparse_adam else None
+        gaussians.optimizer.gpu_adam.step(shards, visibility=vis, grad_scale=1.0 / bsz_global)
+    with timer("all_gather_params"):
+        for n in _GPU_NAMES:
+            full = getattr(gaussians, "_" + n + "_padded")
+            dist.all_gather_into_tensor(full, full[ctx.rank * S:(ctx.rank + 1) * S].clone(), group=ctx.group)
+    return dict(losses=losses, n_isects=n_isects)

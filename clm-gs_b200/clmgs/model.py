@@ -93,6 +93,38 @@ class GpuAdam:
                                self.step_count, grad_scale)
 
 
+class ShardedGpuAdam:
+    """Multi-GPU: the Adam moments of the GPU-resident attributes exist only for this rank's Gaussian range
+    [lo, hi) (44 x 2 / world bytes per Gaussian instead of 88): gradients arrive by reduce-scatter, the owner
+    updates its slice of the replicated parameters, an all-gather publishes it.  Same update rules
+    as GpuAdam."""
+
+    def __init__(self, groups, sparse, lo, hi):
+        self.param_groups, self.sparse, self.lo, self.hi = groups, sparse, lo, hi
+        self.state, self.step_count = {}, 0
+        for g in groups:
+            p = g["params"][0]
+            shape = (hi - lo,) + tuple(p.shape[1:])
+            self.state[g["name"]] = dict(exp_avg=torch.zeros(shape, dtype=p.dtype, device=p.device),
+                                         exp_avg_sq=torch.zeros(shape, dtype=p.dtype, device=p.device))
+
+    @torch.no_grad()
+    def step(self, grad_shards, visibility=None, grad_scale=1.0):
+        """grad_shards: name -> summed gradient of rows [lo, hi); visibility: uint8/bool [hi - lo] (selective)."""
+        self.step_count += 1
+        n = self.hi - self.lo
+        for g in self.param_groups:
+            p = g["params"][0][self.lo:self.hi]
+            st, gr = self.state[g["name"]], grad_shards[g["name"]][:n]
+            b1, b2 = g["betas"]
+            if self.sparse:
+                ops.selective_adam(p, gr, st["exp_avg"], st["exp_avg_sq"], visibility, g["lr"], b1, b2, g["eps"],
+                                   grad_scale)
+            else:
+                ops.adam_dense(p, gr, st["exp_avg"], st["exp_avg_sq"], g["lr"], b1, b2, g["eps"], self.step_count,
+                               grad_scale)
+
+
 class CpuAdam:
     """Host Adam over the pinned [N,48] SH table (the reference's cpu_adam.FusedCPUAdam,
     optimizer.py:130-142): per-column learning rates, bias correction on."""
@@ -211,7 +243,9 @@ class GaussianModelCLMOffload:
         return [self._xyz, self._opacity, self._scaling, self._rotation, self._parameters]
 
     # -- optimiser (GM:122-234) --------------------------------------------------------
-    def training_setup(self, args: TrainArgs):
+    def training_setup(self, args: TrainArgs, gpu_shard=None):
+        """gpu_shard = (lo, hi): multi-GPU, keep the moments of the GPU-resident attributes for that id range only
+        (the pinned SH table / host Adam state passed to create_from_arrays is then that range's shard, too)."""
         self.args = args
         # densification statistics (GM:122-127, base_gaussian_model max_radii2D)
         self.max_radii2D = torch.zeros(self.n_gaussians, device=self.device)
@@ -235,7 +269,9 @@ class GaussianModelCLMOffload:
         cpu = CpuAdam(self._parameters, [3, 45], columns_lr * lr_scale, [b ** bsz for b in betas], eps / lr_scale,
                       args.cpu_adam_threads, capacity=self.parameters_buffer.shape[0])
         self.percent_dense = args.percent_dense
-        self.optimizer = UnifiedAdam(GpuAdam(groups, args.sparse_adam), cpu)
+        gpu = (GpuAdam(groups, args.sparse_adam) if gpu_shard is None
+               else ShardedGpuAdam(groups, args.sparse_adam, int(gpu_shard[0]), int(gpu_shard[1])))
+        self.optimizer = UnifiedAdam(gpu, cpu)
         self.xyz_scheduler_args = get_expon_lr_func(
             lr_init=args.position_lr_init * args.spatial_lr_scale * lr_scale,
             lr_final=args.position_lr_final * args.spatial_lr_scale * lr_scale,
@@ -265,6 +301,11 @@ class GaussianModelCLMOffload:
         """classify bytes -> new state.  One plan, one gather kernel for the GPU tensors and their moments, one in-place
         compaction of the pinned tables (strategies/clm_offload/gaussian_model.py:522-739 re-concatenates every
         tensor three times and compacts the pinned table with a temporary of the whole kept set)."""
+        if getattr(self, "dist_ctx", None) is not None:
+            # ADVICE r1: the sharded multi-GPU state cannot be restructured in place -- rows would have to migrate
+            # between the ranks' host shards and every rank would need the same noise; refuse instead of corrupting
+            raise RuntimeError("densify / prune is not supported on the Gaussian-sharded multi-GPU state "
+                               "(clmgs.engine_dist); restructure on one GPU and re-shard")
         self.materialize_host_rows()  # joins a pipelined host update and replays postponed (lazy) updates
         dev = self._xyz.device
         n_old = self.n_gaussians

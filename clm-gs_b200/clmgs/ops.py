@@ -458,6 +458,10 @@ def rows_gather_i32(d_rows, h_rows, ids32):
     call("clmgs_rows_gather_i32", d_rows, h_rows, ids32, ids32.shape[0], _st())
 
 
+def rows_gather_to_slots(d_rows, h_rows, ids32, slot_of):
+    call("clmgs_rows_gather_to_slots", d_rows, h_rows, ids32, ids32.shape[0], slot_of, _st())
+
+
 def rows_flush_slots(d_grad_rows, slot_of, ids32, h_grad):
     call("clmgs_rows_flush_slots", d_grad_rows, slot_of, ids32, ids32.shape[0], h_grad, _st())
 

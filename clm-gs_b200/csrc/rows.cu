@@ -459,6 +459,18 @@ CLMGS_EXPORT int clmgs_rows_gather_i32(float *d_rows, const float *h_rows, const
     return CLMGS_OK;
 }
 
+CLMGS_EXPORT int clmgs_rows_gather_to_slots(float *d_rows, const float *h_rows, const int32_t *ids, int64_t n,
+                                            const int32_t *slot_of, void *stream) {
+    set_carveouts();
+    if (n == 0) return CLMGS_OK;
+    if (int rc = check_align(d_rows, "d_rows")) return rc;
+    if (int rc = check_align(h_rows, "h_rows")) return rc;
+    copy_rows_kernel<<<grid_for(n), kThreads, 0, as_stream(stream)>>>(F4(d_rows), CF4(h_rows), n, Map32{ids},
+                                                                     Map32Via{ids, slot_of});
+    CLMGS_LAUNCH_OK();
+    return CLMGS_OK;
+}
+
 CLMGS_EXPORT int clmgs_rows_flush_slots(const float *d_grad_rows, const int32_t *slot_of, const int32_t *ids,
                                         int64_t n, float *h_grad, void *stream) {
     set_carveouts();

@@ -288,6 +288,8 @@ int clmgs_set_signal(int32_t *h_flags, int index, int value, void *stream);
  *                             ORDERED bitmap (counterpart of clmgs_extract_ffs, which gives the last use)
  *   clmgs_slot_map          : slot_of[ids[p]] = p for the touched Gaussians grouped by first use
  *   clmgs_rows_gather_i32   : clmgs_rows_gather_i64 with int32 ids (a first-use group -> its contiguous slots)
+ *   clmgs_rows_gather_to_slots : d_rows[slot_of[ids[r]]] = h_rows[ids[r]] (slots in an order other than the
+ *                             first-use grouping: the multi-GPU engine keeps them in ascending-id = owner-major order)
  *   clmgs_rows_flush_slots  : h_grad[ids[r]] = d_grad_rows[slot_of[ids[r]]] (a last-use group, stored once)
  *   clmgs_sh_colors_*_slots : the engine-fused SH colour stage reading / accumulating rows through
  *                             slot_of[ids[g]] (K = 16, degree <= 3). */
@@ -296,6 +298,8 @@ int clmgs_extract_first_use(const void *bitmap, int word_bytes, int bsz, uint8_t
 int clmgs_slot_map(const int32_t *ids, int64_t n, int32_t *slot_of, void *stream);
 int clmgs_rows_gather_i32(float *d_rows, const float *h_rows, const int32_t *ids, int64_t n,
                           void *stream);
+int clmgs_rows_gather_to_slots(float *d_rows, const float *h_rows, const int32_t *ids, int64_t n,
+                               const int32_t *slot_of, void *stream);
 int clmgs_rows_flush_slots(const float *d_grad_rows, const int32_t *slot_of, const int32_t *ids,
                            int64_t n, float *h_grad, void *stream);
 int clmgs_sh_colors_fwd_slots(int64_t N, int degree, const float *means, const float *campos,
