@@ -57,3 +57,64 @@ def test_row_exchange_empty_request(tmp_path):
     got = np.concatenate([np.load(tmp_path / ("grad_%d.npy" % r)) for r in range(world)])
     ref = np.zeros((N, 48), np.float32); ref[needs[0]] = 1
     np.testing.assert_array_equal(got, ref)
+
+
+def test_shard_map_equal_shards():
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path[:0] = [root, os.path.join(root, "clm-gs_b200")]
+    from clmgs.dist_rows import ShardMap
+    for N, G in ((1001, 2), (102_000_000, 8), (7, 8), (64, 1)):
+        sm = ShardMap(N, G)
+        assert sm.bounds[0] == 0 and sm.bounds[-1] == N and sm.shard * G >= N
+        assert all(0 <= sm.bounds[g + 1] - sm.bounds[g] <= sm.shard for g in range(G))
+        assert all(sm.bounds[g] == min(N, g * sm.shard) for g in range(G + 1))   # rank g's slice of a padded tensor
+
+
+def _merge_worker(rank, world, port, N, needs, out_dir):
+    """plan -> owner-side merge (no sort) -> gradient return accumulated through dst_index, as engine_dist does it;
+    plus the node-shared host table: every rank writes its rows, every rank reads all rows."""
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path[:0] = [root, os.path.join(root, "clm-gs_b200")]
+    from clmgs.dist_rows import RowExchange, ShardMap, merge_requests
+    from clmgs.shm import SharedHostTable
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    shard = ShardMap(N, world)
+    lo, hi = shard.range_of(rank)
+    table = SharedHostTable(N, 48)
+    table.array[lo:hi] = (np.arange(lo, hi, dtype=np.float32)[:, None] * 100 + np.arange(48, dtype=np.float32)[None])
+    dist.barrier()
+    full = np.arange(N, dtype=np.float32)[:, None] * 100 + np.arange(48, dtype=np.float32)[None]
+    assert np.array_equal(table.array, full), "a rank does not see the other ranks' rows of the shared table"
+    ex = RowExchange(shard, rank)
+    need = torch.from_numpy(needs[rank])
+    plan = ex.plan(need)
+    uniq, dst_index, untouched, mask = merge_requests(plan.recv_local, hi - lo, want_untouched=True)
+    assert torch.equal(uniq, torch.unique(plan.recv_local)) and bool((uniq[1:] > uniq[:-1]).all())
+    assert torch.equal(uniq[dst_index], plan.recv_local)
+    assert torch.equal(torch.sort(torch.cat([uniq, untouched]))[0], torch.arange(hi - lo))
+    grads = torch.full((need.shape[0], 48), float(rank + 1))
+    recv = torch.empty(plan.recv_local.shape[0], 48)
+    dist.all_to_all_single(recv, grads, output_split_sizes=plan.recv_counts, input_split_sizes=plan.send_counts)
+    acc = torch.zeros(uniq.shape[0], 48).index_add_(0, dst_index, recv)
+    my_grad = torch.zeros(hi - lo, 48)
+    my_grad[uniq] = acc
+    np.save(os.path.join(out_dir, "grad_%d.npy" % rank), my_grad.numpy())
+    dist.barrier()
+    table.close()
+    dist.destroy_process_group()
+
+
+def test_owner_merge_and_shared_table_two_ranks(tmp_path):
+    N, world = 1003, 2
+    rng = np.random.default_rng(1)
+    needs = [np.sort(rng.choice(N, 500, replace=False)).astype(np.int64),
+             np.sort(rng.choice(N, 300, replace=False)).astype(np.int64)]
+    mp.spawn(_merge_worker, args=(world, _free_port(), N, needs, str(tmp_path)), nprocs=world, join=True)
+    ref = np.zeros((N, 48), np.float32)
+    for r in range(world):
+        ref[needs[r]] += r + 1
+    got = np.concatenate([np.load(tmp_path / ("grad_%d.npy" % r)) for r in range(world)])
+    np.testing.assert_array_equal(got, ref)
