@@ -42,7 +42,7 @@ def small_scene(n=3000, W=96, H=64, ncam=3):
     return spec, g, V, K, P, scales, quats.astype(np.float32)
 
 
-def main():
+def main(out_dir=HERE):
     torch.manual_seed(0)
     spec, g, V, K, P, scales, quats = small_scene()
     W, H = spec.width, spec.height
@@ -61,7 +61,7 @@ def main():
     loss = (means2d * v_means2d).sum() + (depths * v_depths).sum() + (conics * v_conics).sum()
     v_means, v_quats, v_scales = torch.autograd.grad(loss, [means, q, s])
     np.savez_compressed(
-        os.path.join(HERE, "proj.npz"), means=g["xyz"], quats=quats, scales=scales, viewmats=V, Ks=K,
+        os.path.join(out_dir, "proj.npz"), means=g["xyz"], quats=quats, scales=scales, viewmats=V, Ks=K,
         width=W, height=H, radii=radii.numpy(), means2d=means2d.detach().numpy(),
         depths=depths.detach().numpy(), conics=conics.detach().numpy(), v_means2d=v_means2d.numpy(),
         v_depths=v_depths.numpy(), v_conics=v_conics.numpy(), v_means=v_means.numpy(),
@@ -73,7 +73,7 @@ def main():
     tpg, isect_ids, flatten_ids = T._isect_tiles(m2d, radii, dep, 16, tw, th, sort=True)
     offsets = T._isect_offset_encode(isect_ids, len(V), tw, th)
     np.savez_compressed(
-        os.path.join(HERE, "isect.npz"), means2d=m2d.numpy(), radii=radii.numpy(), depths=dep.numpy(),
+        os.path.join(out_dir, "isect.npz"), means2d=m2d.numpy(), radii=radii.numpy(), depths=dep.numpy(),
         tile_size=16, tile_width=tw, tile_height=th, tiles_per_gauss=tpg.numpy(),
         isect_ids=isect_ids.numpy(), flatten_ids=flatten_ids.numpy(), isect_offsets=offsets.numpy())
 
@@ -93,7 +93,7 @@ def main():
         out[f"v_colors{deg}"] = v_col.numpy()
         out[f"v_coeffs{deg}"] = gc.numpy()
         out[f"v_dirs{deg}"] = (gd if gd is not None else torch.zeros_like(d)).numpy()
-    np.savez_compressed(os.path.join(HERE, "sh.npz"), dirs=dirs.numpy(), **out)
+    np.savez_compressed(os.path.join(out_dir, "sh.npz"), dirs=dirs.numpy(), **out)
 
     # ---- loss: 0.8*L1 + 0.2*(1-ssim) and its gradient -----------------------
     Hh, Ww = 45, 70  # not multiples of 32/16 on purpose
@@ -104,11 +104,11 @@ def main():
     ss = ssim(img.unsqueeze(0), gt.unsqueeze(0))
     L = 0.8 * Ll1 + 0.2 * (1.0 - ss)
     (gi,) = torch.autograd.grad(L, [img])
-    np.savez_compressed(os.path.join(HERE, "loss.npz"), image=img.detach().numpy(), gt_u8=gt_u8.numpy(),
+    np.savez_compressed(os.path.join(out_dir, "loss.npz"), image=img.detach().numpy(), gt_u8=gt_u8.numpy(),
                         loss=L.item(), ssim=ss.item(), l1=Ll1.item(), v_image=gi.numpy())
     for f in ("proj", "isect", "sh", "loss"):
-        print(f, os.path.getsize(os.path.join(HERE, f + ".npz")) // 1024, "KiB")
+        print(f, os.path.getsize(os.path.join(out_dir, f + ".npz")) // 1024, "KiB")
 
 
 if __name__ == "__main__":
-    main()
+    main(sys.argv[1] if len(sys.argv) > 1 else HERE)

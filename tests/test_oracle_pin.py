@@ -5,6 +5,8 @@ gsplat's own torch twin (submodules/gsplat/gsplat/cuda/_torch_impl.py) and the
 reference's utils/loss_utils.py.  Tolerances follow gsplat's tests/test_basic.py
 (:161-254 projection 1e-4, :407-437 isect exact, :545-573 SH 1e-4).
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -192,3 +194,20 @@ def test_expf_within_2ulp_of_libm():
     ref = np.exp(x.astype(np.float64))
     ulp = np.abs(got.astype(np.float64) - ref) / np.spacing(ref.astype(np.float32)).astype(np.float64)
     assert ulp.max() <= 2.0, ulp.max()
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/submodules/gsplat"), reason="needs the reference mount (build container only)")
+def test_committed_fixtures_are_what_make_golden_generates(tmp_path):
+    """The four reference-generated fixtures must be reproducible from the committed script (two of them
+    had drifted from it after the scene generator changed)."""
+    import subprocess
+    import sys
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    r = subprocess.run([sys.executable, os.path.join(here, "make_golden.py"), str(tmp_path)], capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    for f in ("proj", "isect", "sh", "loss"):
+        a, b = dict(np.load(os.path.join(here, f + ".npz"))), dict(np.load(tmp_path / (f + ".npz")))
+        assert sorted(a) == sorted(b), f
+        for k in a:
+            np.testing.assert_array_equal(a[k], b[k], err_msg="%s.npz:%s" % (f, k))
