@@ -369,6 +369,6 @@ def test_selective_adam(CK):
         CK.selective_adam_update(pr, g * 0.25, mr, vr, mask, 1e-2, 0.9 ** 4, 0.999 ** 4, 5e-16, N, M)
         ops.selective_adam(po, g, mo, vo, mask, 1e-2, 0.9 ** 4, 0.999 ** 4, 5e-16, grad_scale=0.25)
         assert torch.equal(po[~mask], p[~mask])
-        torch.testing.assert_close(mo, mr, rtol=1e-6, atol=1e-8)
+        torch.testing.assert_close(mo, mr, rtol=1e-5, atol=1e-7)   # FMA contraction differs between the two builds
         torch.testing.assert_close(vo, vr, rtol=1e-6, atol=1e-10)
         torch.testing.assert_close(po, pr, rtol=1e-5, atol=1e-7)
