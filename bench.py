@@ -173,7 +173,7 @@ def run_ours(a):
     import torch
     import torch.distributed as dist
 
-    from clmgs import _lib, engine, engine_dist, model, peaks as PK, scene as S
+    from clmgs import _lib, engine, engine_dist, hostmem, model, peaks as PK, scene as S
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -211,7 +211,7 @@ def run_ours(a):
         # rank generates and later updates only its own rows
         sh_host = ctx.create_shared_table().tensor[lo:hi]
     else:
-        sh_host = torch.empty(hi - lo, 48, dtype=torch.float32, pin_memory=True)
+        sh_host = hostmem.pinned_tensor((hi - lo, 48), torch.float32)
     g = S.make_gaussians(spec, sh_out=sh_host.numpy(), sh_rows=(lo, hi),
                          workers=max(1, (os.cpu_count() or 1) // world))  # each rank generates only its SH shard
     args = model.TrainArgs(bsz=global_batch, sparse_adam=sparse_adam, cpu_adam_threads=host_threads)
@@ -460,6 +460,7 @@ def run_ours(a):
                    gpu_launches=launches, clocks=clk, roofline=roof, raster=raster, stages=stages,
                    peaks={k: v for k, v in pk.items()})
         out["config"]["hbm_allocated_gb"] = round(torch.cuda.max_memory_allocated() / 1e9, 2)
+        out["config"]["host_huge_pages"] = hostmem.huge_page_stats()
         if pipelined:
             out["pipelined"] = pipelined
         if lazy:

@@ -27,7 +27,7 @@ import threading
 import numpy as np
 import torch
 
-from . import ops
+from . import hostmem, ops
 
 TILE_SIZE = 16  # strategies/base_engine.py:15
 
@@ -109,6 +109,20 @@ def _pinned_rows_buffer(n, parity=0):
     return buf
 
 
+def _packed_staging(gaussians, n_rows, which=0):
+    """Pinned [rows, 48] staging buffer the gradient flush DMAs into and the host Adam reads from; grown in 1/8-octave
+    steps and kept across batches (two of them only in pipelined mode, where the previous batch's host Adam may
+    still be reading its own)."""
+    bufs = getattr(gaussians, "_packed_grad_staging", None)
+    if bufs is None:
+        bufs = gaussians._packed_grad_staging = {}
+    buf = bufs.get(which)
+    if buf is None or buf.shape[0] < n_rows:
+        bufs[which] = None
+        buf = bufs[which] = hostmem.pinned_tensor((ops._bucket(max(n_rows, 1)), 48), torch.float32)
+    return buf
+
+
 def wait_host_adam(gaussians):
     """Join a host Adam left running by a pipeline_host_adam call (no-op otherwise).  Call it before
     reading the SH table or the host optimiser state."""
@@ -163,8 +177,13 @@ def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, tim
         first_counts_h = first_counts.cpu().numpy()
         n_untouched = int(first_counts_h[0])
         union_ids = first_rows_dev[n_untouched:]
+        # A Gaussian's slot in the batch-resident device tables = its position in the LAST-use grouping: the rows
+        # whose last user is camera k are one contiguous slot range, so their gradients leave with one plain DMA copy
+        # (copy engine, no SMs) into a packed pinned staging buffer laid out like the host Adam's row list.  Loads
+        # scatter into the slots (they are zero-copy gather kernels either way).  Without the last-use grouping
+        # (multi-GPU engine, which makes its own slots) fall back to the first-use order.
         slot_of = torch.empty(n_gaussians, dtype=torch.int32, device=dev)
-        ops.slot_map(union_ids, slot_of)
+        ops.slot_map(rows_dev[int(counts_h[0]):] if host_rows else union_ids, slot_of)
     row_begin = row_end = None
     if host_rows:
         offs = np.concatenate([[0], np.cumsum(counts_h)]).astype(np.int64)
@@ -324,6 +343,9 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
 
     progress = np.zeros(1, np.int64)
     prev_worker = prev["worker"] if prev is not None else None
+    # packed pinned staging for this batch's SH gradients: row s = slot s = list entry n_unt + s (see order_calculation)
+    n_unt = int(re_[0])
+    h_packed = _packed_staging(gaussians, N - n_unt, parity if pipe else 0)
 
     def cpuadam_thread():
         import time as _t
@@ -333,7 +355,8 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
         try:
             cpu_adam.batched_sparse_step(h_grad, oc["rows_host"], seg_begin, seg_end, seg_signal, signal, 1.0 / bsz,
                                          progress, [1 if (s_ == -1 and not args.sparse_adam and i_ == 0) else 0
-                                                    for i_, s_ in enumerate(seg_signal)])
+                                                    for i_, s_ in enumerate(seg_signal)],
+                                         grad_packed=h_packed, packed_base=n_unt)
         except Exception as e:  # surfaced after join
             worker_err.append(e)
         worker_times["cpu_adam_thread_ms"] = (_t.perf_counter() - t0) * 1e3
@@ -341,7 +364,7 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     worker = threading.Thread(target=cpuadam_thread, daemon=True)
     worker.start()
     try:
-        out = _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_grad, background, comm_stream,
+        out = _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_packed, background, comm_stream,
                              signal, timer, worker, worker_err, chunk_edges, prev, pipe)
         if pipe:
             # ids at the ends of the final-flush pieces: the next call loads rows up to hi[c] once piece c is updated
@@ -355,6 +378,7 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     except BaseException:
         # never leave the host-Adam thread spinning on flags that will not come
         torch.cuda.synchronize()
+        h_packed.zero_()          # whatever has not been flushed counts as a zero gradient
         gaussians.signal_tensor_pinned.fill_(1)
         worker.join()
         raise
@@ -368,7 +392,7 @@ def _wait_progress(pend, need):
         _t.sleep(5e-5)
 
 
-def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_grad, background, comm_stream, signal,
+def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_packed, background, comm_stream, signal,
                    timer, worker, worker_err, chunk_edges, prev=None, pipe=False):
     args = gaussians.args
     bsz = len(batched_cameras)
@@ -407,6 +431,7 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
             d_rows = ops._empty((n_union, 48), torch.float32, dev)
             d_rows.record_stream(compute)
             union_ids.record_stream(comm_stream)
+            slot_of.record_stream(comm_stream)
             rows_evt = []
             for k in range(bsz):
                 a0, a1 = int(fe[k]), int(fe[k + 1])
@@ -422,20 +447,19 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
                         for c in range(len(cuts)):
                             _wait_progress(prev, prev["n_seg"] if c == len(cuts) - 1 else base + c + 1)
                             if edges[c + 1] > edges[c]:
-                                ops.rows_gather_i32(d_rows[a0 + edges[c]:a0 + edges[c + 1]], h_params,
-                                                    union_ids[a0 + edges[c]:a0 + edges[c + 1]])
+                                ops.rows_gather_to_slots(d_rows, h_params, union_ids[a0 + edges[c]:a0 + edges[c + 1]],
+                                                         slot_of)
                     prev["keep"] = None  # the previous batch is completely done: release its buffers
                 else:
                     with timer("rows_load_first" if k == 0 else "rows_prefetch", comm_stream):
-                        ops.rows_gather_i32(d_rows[a0:a1], h_params, union_ids[a0:a1])
+                        ops.rows_gather_to_slots(d_rows, h_params, union_ids[a0:a1], slot_of)
                 e = torch.cuda.Event()
                 e.record(comm_stream)
                 rows_evt.append(e)
         d_grad = ops._zeros((n_union, 48), torch.float32, dev)   # compute stream; the flush stream waits on bwd events
         d_grad.record_stream(flush_stream)
-        last_rows, rb, re_ = oc["rows_dev"], oc["row_begin"], oc["row_end"]
-        last_rows.record_stream(flush_stream)
-        slot_of.record_stream(flush_stream)
+        rb, re_ = oc["row_begin"], oc["row_end"]
+        n_unt = int(re_[0])
 
         for k in range(bsz):
             ids = filters[k]
@@ -462,20 +486,24 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_gr
             bwd_done.record(compute)
 
             # gradients of the rows whose last user is this camera -> pinned table, then the flag (flush stream)
+            # slots are positions in the last-use grouping, so this group is the contiguous range [g0, g1) - n_unt of
+            # d_grad and of the packed staging buffer: one DMA copy, no kernel
             m = k + 1
-            g0, g1 = int(rb[m]), int(re_[m])
+            g0, g1 = int(rb[m]) - n_unt, int(re_[m]) - n_unt
             with torch.cuda.stream(flush_stream):
                 flush_stream.wait_event(bwd_done)
                 with timer("grad_handoff", flush_stream):
                     if k < bsz - 1:
-                        ops.rows_flush_slots(d_grad, slot_of, last_rows[g0:g1], h_grad)
+                        if g1 > g0:
+                            h_packed[g0:g1].copy_(d_grad[g0:g1], non_blocking=True)
                         ops.set_signal(signal, k, 1)
                     else:
                         # last camera: in pieces, each announced on its own flag, so the host Adam starts on piece j
                         # while piece j+1 is still crossing the link
                         for j in range(len(chunk_edges) - 1):
                             c0, c1 = g0 + chunk_edges[j], g0 + chunk_edges[j + 1]
-                            ops.rows_flush_slots(d_grad, slot_of, last_rows[c0:c1], h_grad)
+                            if c1 > c0:
+                                h_packed[c0:c1].copy_(d_grad[c0:c1], non_blocking=True)
                             ops.set_signal(signal, bsz - 1 + j, 1)
             n_isects_log.append(fw["n_isects"])
             del fw, v_render, loss_vec

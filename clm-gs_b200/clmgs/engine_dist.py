@@ -20,7 +20,7 @@ ONE optimiser step per call.  Rank g owns the Gaussian range [g S, (g+1) S), S =
                   into a slot-shaped buffer and the dense gradients of the replicated attributes
                4. sparse reduce-scatter of the SH gradients: NCCL all-to-all-v straight out of the slot buffer
                   (owner-major already) -> owner sums duplicates with 16-byte vector atomics -> stores its rows to
-                  its pinned gradient table chunk by chunk, one flag per chunk -> host Adam consumes chunk j while
+                  a packed pinned staging buffer chunk by chunk (DMA), one flag per chunk -> host Adam consumes chunk j while
                   chunk j+1 crosses the link
                5. NCCL reduce-scatter of the dense gradients -> owner Adam on its slice (moments sharded) ->
                   all-gather of the updated slices
@@ -142,13 +142,15 @@ def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters
             seg_b.append(n_unt + edges[j]); seg_e.append(n_unt + edges[j + 1]); seg_sig.append(j); seg_zg.append(0)
         signal = _signal_flags(gaussians, J)
         worker_err, worker_times = [], {}
+        from .engine import _packed_staging
+        h_packed = _packed_staging(gaussians, n_uniq)   # row i = summed gradient of uniq[i] = list entry n_unt + i
 
         def cpuadam_thread():
             import time as _t
             t0 = _t.perf_counter()
             try:
                 cpu_adam.batched_sparse_step(h_grad, rows_host, seg_b, seg_e, seg_sig, signal, 1.0 / bsz_global, None,
-                                             seg_zg)
+                                             seg_zg, grad_packed=h_packed, packed_base=n_unt)
             except Exception as e:  # surfaced after join
                 worker_err.append(e)
             worker_times["cpu_adam_thread_ms"] = (_t.perf_counter() - t0) * 1e3
@@ -157,10 +159,11 @@ def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters
         worker.start()
         try:
             out = _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, plan, uniq, dst_index,
-                                       touched_mask, edges, signal, h_table, h_grad, background, comm_stream,
+                                       touched_mask, edges, signal, h_table, h_packed, background, comm_stream,
                                        flush_stream, timer)
         except BaseException:
             torch.cuda.synchronize()
+            h_packed.zero_()
             signal.fill_(1)       # never leave the host-Adam thread spinning on flags that will not come
             worker.join()
             raise
@@ -202,7 +205,7 @@ def _signal_flags(gaussians, n):
 
 
 def _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, plan, uniq, dst_index, touched_mask,
-                         edges, signal, h_table, h_grad, background, comm_stream, flush_stream, timer):
+                         edges, signal, h_table, h_packed, background, comm_stream, flush_stream, timer):
     args = gaussians.args
     dev = gaussians._xyz.device
     bsz_local, G, S = len(cams), ctx.world, ctx.shard.shard
@@ -265,13 +268,13 @@ def _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, pla
     acc_ready = torch.cuda.Event()
     acc_ready.record(compute)
     acc.record_stream(flush_stream)
-    uniq.record_stream(flush_stream)
     with torch.cuda.stream(flush_stream):
         flush_stream.wait_event(acc_ready)
         with timer("grad_handoff", flush_stream):
-            for j in range(len(edges) - 1):
+            for j in range(len(edges) - 1):   # contiguous on both sides: plain DMA copies (copy engine, no SMs)
                 c0, c1 = edges[j], edges[j + 1]
-                ops.rows_scatter_grad(acc[c0:c1], h_grad, uniq[c0:c1], accum=False)   # table rows are zero: plain store
+                if c1 > c0:
+                    h_packed[c0:c1].copy_(acc[c0:c1], non_blocking=True)
                 ops.set_signal(signal, j, 1)
 
     # ---- 5. GPU-resident attributes: reduce-scatter -> owner Adam on its slice -> all-gather ---------------

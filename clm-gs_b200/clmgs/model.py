@@ -21,7 +21,7 @@ import os
 import numpy as np
 import torch
 
-from . import ops
+from . import hostmem, ops
 
 
 @dataclass
@@ -149,13 +149,13 @@ class CpuAdam:
         self.n_threads = n_threads if n_threads > 0 else max(1, (os.cpu_count() or 2) - 1)
 
     def batched_sparse_step(self, grad, rows, seg_begin, seg_end, seg_signal, signal_tensor_pinned, scale,
-                            progress=None, seg_zero_grad=None):
+                            progress=None, seg_zero_grad=None, grad_packed=None, packed_base=0):
         """engine.py:320-327.  Blocking; run it on a worker thread (ctypes drops the GIL)."""
         self.step_count += 1
         ops.cpu_adam_batched_sparse_step(self.param, grad, self.exp_avg, self.exp_avg_sq, self.columns_lr, rows,
                                          seg_begin, seg_end, seg_signal, signal_tensor_pinned, self.betas[0],
                                          self.betas[1], self.eps, self.step_count, scale, self.n_threads, progress,
-                                         seg_zero_grad)
+                                         seg_zero_grad, grad_packed, packed_base)
 
     def catch_up(self, rows=None, include_this_step=False):
         """Lazy dense Adam: replay the postponed zero-gradient steps of `rows` (int32 ids; None = every row) through
@@ -183,12 +183,12 @@ class UnifiedAdam:
 
 def _pinned_zeros(shape):
     # allocated pinned directly (Tensor.pin_memory() would allocate pageable memory first and copy: at C4 that is
-    # 78 GB of extra host traffic and, transiently, twice the memory)
-    return torch.zeros(shape, dtype=torch.float32, pin_memory=torch.cuda.is_available())
+    # 78 GB of extra host traffic and, transiently, twice the memory), on 2 MiB pages where available (hostmem.py)
+    return hostmem.pinned_tensor(shape, torch.float32, zero=True)
 
 
 def _pinned_empty(shape):
-    return torch.empty(shape, dtype=torch.float32, pin_memory=torch.cuda.is_available())
+    return hostmem.pinned_tensor(shape, torch.float32)
 
 
 def get_expon_lr_func(lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, max_steps=1000000):

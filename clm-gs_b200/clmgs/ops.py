@@ -406,14 +406,22 @@ def adam_dense(param, grad, exp_avg, exp_avg_sq, lr, b1, b2, eps, step, grad_sca
 
 
 def cpu_adam_batched_sparse_step(param, grad, exp_avg, exp_avg_sq, col_lr, rows, seg_begin, seg_end, seg_signal,
-                                 signal, b1, b2, eps, step, scale, n_threads=0, progress=None, seg_zero_grad=None):
+                                 signal, b1, b2, eps, step, scale, n_threads=0, progress=None, seg_zero_grad=None,
+                                 grad_packed=None, packed_base=0):
     """All arguments are HOST tensors/arrays (pinned where the GPU also touches them).  Blocking.
-    Segment s = rows[seg_begin[s]:seg_end[s]], processed after signal[seg_signal[s]] != 0 (no wait if < 0)."""
+    Segment s = rows[seg_begin[s]:seg_end[s]], processed after signal[seg_signal[s]] != 0 (no wait if < 0).
+    grad_packed: gradients come from this packed staging buffer (row r - packed_base for list entry r) instead of
+    the table `grad` (which is then not touched)."""
     import numpy as np
     seg_begin = np.ascontiguousarray(seg_begin, np.int64)
     seg_end = np.ascontiguousarray(seg_end, np.int64)
     seg_signal = np.ascontiguousarray(seg_signal, np.int32)
     zg = None if seg_zero_grad is None else np.ascontiguousarray(seg_zero_grad, np.int32)
+    if grad_packed is not None:
+        call("clmgs_cpu_adam_batched_sparse_step_packed", param, grad_packed, int(packed_base), exp_avg, exp_avg_sq,
+             int(param.shape[1]), col_lr, rows, seg_begin, seg_end, seg_signal, zg, len(seg_begin), signal, float(b1),
+             float(b2), float(eps), int(step), float(scale), int(n_threads), progress)
+        return
     call("clmgs_cpu_adam_batched_sparse_step", param, grad, exp_avg, exp_avg_sq, int(param.shape[1]), col_lr, rows,
          seg_begin, seg_end, seg_signal, zg, len(seg_begin), signal, float(b1), float(b2), float(eps), int(step),
          float(scale), int(n_threads), progress)

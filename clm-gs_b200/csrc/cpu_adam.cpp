@@ -37,9 +37,13 @@ struct AdamConst {
 
 // One row of `cols` floats.  Two instruction sets, one arithmetic: every operation below is a correctly rounded
 // IEEE mul / add / sqrt / div on independent lanes, and the translation unit is built with -ffp-contract=off, so the
-// 8-lane and the 16-lane variant give identical bits.  ZERO_GRAD: the gradient row is known to be zero -- it is
-// neither read nor re-zeroed.
-template <bool ZERO_GRAD>
+// 8-lane and the 16-lane variant give identical bits.
+// GMODE: where the gradient row comes from
+//   G_TABLE  row of the pinned gradient table; consumed rows are zeroed in place (the reference's "version 3")
+//   G_ZERO   the gradient row is known to be zero -- it is neither read nor re-zeroed
+//   G_PACKED row of a packed staging buffer (one row per list entry, written by a DMA copy); read once, not zeroed
+enum { G_TABLE = 0, G_ZERO = 1, G_PACKED = 2 };
+template <int GMODE>
 __attribute__((target("avx2"), always_inline)) inline void adam_row_avx2(float *p, float *g, float *m, float *v, const float *col_lr,
                                                          int cols, const AdamConst &c) {
     int k = 0;
@@ -48,7 +52,7 @@ __attribute__((target("avx2"), always_inline)) inline void adam_row_avx2(float *
     const __m256 eps = _mm256_set1_ps(c.eps), sc = _mm256_set1_ps(c.scale);
     const __m256 ibc1 = _mm256_set1_ps(-c.inv_bc1), bc2r = _mm256_set1_ps(c.bc2_rsqrt);
     for (; k + 8 <= cols; k += 8) {
-        __m256 gg = ZERO_GRAD ? _mm256_setzero_ps() : _mm256_mul_ps(_mm256_loadu_ps(g + k), sc);
+        __m256 gg = GMODE == G_ZERO ? _mm256_setzero_ps() : _mm256_mul_ps(_mm256_loadu_ps(g + k), sc);
         __m256 mm = _mm256_add_ps(_mm256_mul_ps(b1, _mm256_loadu_ps(m + k)), _mm256_mul_ps(omb1, gg));
         __m256 vv = _mm256_add_ps(_mm256_mul_ps(b2, _mm256_loadu_ps(v + k)), _mm256_mul_ps(omb2, _mm256_mul_ps(gg, gg)));
         __m256 denom = _mm256_add_ps(_mm256_mul_ps(_mm256_sqrt_ps(vv), bc2r), eps);
@@ -56,20 +60,20 @@ __attribute__((target("avx2"), always_inline)) inline void adam_row_avx2(float *
         _mm256_storeu_ps(p + k, _mm256_add_ps(_mm256_loadu_ps(p + k), step));
         _mm256_storeu_ps(m + k, mm);
         _mm256_storeu_ps(v + k, vv);
-        if (!ZERO_GRAD) _mm256_storeu_ps(g + k, _mm256_setzero_ps());  // version 3: zero the consumed gradient in place
+        if (GMODE == G_TABLE) _mm256_storeu_ps(g + k, _mm256_setzero_ps());  // version 3: zero the consumed gradient in place
     }
     for (; k < cols; ++k) {
-        float gg = ZERO_GRAD ? 0.f : g[k] * c.scale;
+        float gg = GMODE == G_ZERO ? 0.f : g[k] * c.scale;
         float mm = c.b1 * m[k] + (1.0f - c.b1) * gg;
         float vv = c.b2 * v[k] + (1.0f - c.b2) * gg * gg;
         float denom = sqrtf(vv) * c.bc2_rsqrt + c.eps;
         p[k] += -(col_lr[k] * c.inv_bc1) * (mm / denom);
         m[k] = mm; v[k] = vv;
-        if (!ZERO_GRAD) g[k] = 0.f;
+        if (GMODE == G_TABLE) g[k] = 0.f;
     }
 }
 
-template <bool ZERO_GRAD>
+template <int GMODE>
 __attribute__((target("avx2,avx512f"), always_inline)) inline void adam_row_avx512(float *p, float *g, float *m, float *v,
                                                               const float *col_lr, int cols, const AdamConst &c) {
     int k = 0;
@@ -78,7 +82,7 @@ __attribute__((target("avx2,avx512f"), always_inline)) inline void adam_row_avx5
     const __m512 eps = _mm512_set1_ps(c.eps), sc = _mm512_set1_ps(c.scale);
     const __m512 ibc1 = _mm512_set1_ps(-c.inv_bc1), bc2r = _mm512_set1_ps(c.bc2_rsqrt);
     for (; k + 16 <= cols; k += 16) {  // a 48-float SH row = 3 x 64-byte lines = 3 iterations
-        __m512 gg = ZERO_GRAD ? _mm512_setzero_ps() : _mm512_mul_ps(_mm512_loadu_ps(g + k), sc);
+        __m512 gg = GMODE == G_ZERO ? _mm512_setzero_ps() : _mm512_mul_ps(_mm512_loadu_ps(g + k), sc);
         __m512 mm = _mm512_add_ps(_mm512_mul_ps(b1, _mm512_loadu_ps(m + k)), _mm512_mul_ps(omb1, gg));
         __m512 vv = _mm512_add_ps(_mm512_mul_ps(b2, _mm512_loadu_ps(v + k)), _mm512_mul_ps(omb2, _mm512_mul_ps(gg, gg)));
         __m512 denom = _mm512_add_ps(_mm512_mul_ps(_mm512_sqrt_ps(vv), bc2r), eps);
@@ -86,16 +90,16 @@ __attribute__((target("avx2,avx512f"), always_inline)) inline void adam_row_avx5
         _mm512_storeu_ps(p + k, _mm512_add_ps(_mm512_loadu_ps(p + k), step));
         _mm512_storeu_ps(m + k, mm);
         _mm512_storeu_ps(v + k, vv);
-        if (!ZERO_GRAD) _mm512_storeu_ps(g + k, _mm512_setzero_ps());
+        if (GMODE == G_TABLE) _mm512_storeu_ps(g + k, _mm512_setzero_ps());
     }
     for (; k < cols; ++k) {
-        float gg = ZERO_GRAD ? 0.f : g[k] * c.scale;
+        float gg = GMODE == G_ZERO ? 0.f : g[k] * c.scale;
         float mm = c.b1 * m[k] + (1.0f - c.b1) * gg;
         float vv = c.b2 * v[k] + (1.0f - c.b2) * gg * gg;
         float denom = sqrtf(vv) * c.bc2_rsqrt + c.eps;
         p[k] += -(col_lr[k] * c.inv_bc1) * (mm / denom);
         m[k] = mm; v[k] = vv;
-        if (!ZERO_GRAD) g[k] = 0.f;
+        if (GMODE == G_TABLE) g[k] = 0.f;
     }
 }
 
@@ -111,36 +115,37 @@ inline bool use_avx512() {
 // Rows [a,b) of a row list (or of the identity when rows == nullptr).  One function per instruction set, so that
 // the 8-lane build never contains a 512-bit instruction.
 #define CLMGS_ADAM_ROWS(NAME, TARGET, ROWFN)                                                                          \
-    template <bool ZERO_GRAD>                                                                                        \
+    template <int GMODE>                                                                                             \
     __attribute__((target(TARGET))) void NAME(float *param, float *grad, float *exp_avg, float *exp_avg_sq,          \
                                               const float *col_lr, int cols, const int32_t *rows, int64_t a,         \
-                                              int64_t b, const AdamConst &c) {                                       \
+                                              int64_t b, int64_t packed_base, const AdamConst &c) {                  \
         for (int64_t r = a; r < b; ++r) {                                                                            \
             const int64_t base = (int64_t)(rows ? rows[r] : r) * cols;                                               \
             if (rows && r + 4 < b) {                                                                                 \
                 const int64_t nb = (int64_t)rows[r + 4] * cols;                                                      \
                 _mm_prefetch((const char *)(param + nb), _MM_HINT_T0);                                               \
-                if (!ZERO_GRAD) _mm_prefetch((const char *)(grad + nb), _MM_HINT_T0);                                \
+                if (GMODE == G_TABLE) _mm_prefetch((const char *)(grad + nb), _MM_HINT_T0);                          \
                 _mm_prefetch((const char *)(exp_avg + nb), _MM_HINT_T0);                                             \
                 _mm_prefetch((const char *)(exp_avg_sq + nb), _MM_HINT_T0);                                          \
             }                                                                                                        \
-            ROWFN<ZERO_GRAD>(param + base, grad + base, exp_avg + base, exp_avg_sq + base, col_lr, cols, c);         \
+            float *g = GMODE == G_PACKED ? grad + (r - packed_base) * cols : grad + base;                            \
+            ROWFN<GMODE>(param + base, g, exp_avg + base, exp_avg_sq + base, col_lr, cols, c);                       \
         }                                                                                                            \
     }
 CLMGS_ADAM_ROWS(adam_rows_avx2, "avx2", adam_row_avx2)
 CLMGS_ADAM_ROWS(adam_rows_avx512, "avx2,avx512f", adam_row_avx512)
 #undef CLMGS_ADAM_ROWS
 
-template <bool ZERO_GRAD>
+template <int GMODE>
 inline void adam_rows(float *param, float *grad, float *exp_avg, float *exp_avg_sq, const float *col_lr, int cols,
-                      const int32_t *rows, int64_t a, int64_t b, const AdamConst &c) {
-    if (use_avx512()) adam_rows_avx512<ZERO_GRAD>(param, grad, exp_avg, exp_avg_sq, col_lr, cols, rows, a, b, c);
-    else adam_rows_avx2<ZERO_GRAD>(param, grad, exp_avg, exp_avg_sq, col_lr, cols, rows, a, b, c);
+                      const int32_t *rows, int64_t a, int64_t b, int64_t packed_base, const AdamConst &c) {
+    if (use_avx512()) adam_rows_avx512<GMODE>(param, grad, exp_avg, exp_avg_sq, col_lr, cols, rows, a, b, packed_base, c);
+    else adam_rows_avx2<GMODE>(param, grad, exp_avg, exp_avg_sq, col_lr, cols, rows, a, b, packed_base, c);
 }
 
 template <bool ZERO_GRAD>
 inline void adam_row(float *p, float *g, float *m, float *v, const float *col_lr, int cols, const AdamConst &c) {
-    adam_rows<ZERO_GRAD>(p, g, m, v, col_lr, cols, nullptr, 0, 1, c);
+    adam_rows<ZERO_GRAD ? G_ZERO : G_TABLE>(p, g, m, v, col_lr, cols, nullptr, 0, 1, 0, c);
 }
 
 inline int64_t now_ns() {
@@ -243,14 +248,12 @@ std::atomic<int64_t> g_stat_total_ns(0), g_stat_wait_ns(0), g_stat_rows(0), g_st
 
 }  // namespace
 
-CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, float *host_exp_avg,
-                                                    float *host_exp_avg_sq, int cols, const float *col_lr,
-                                                    const int32_t *host_rows, const int64_t *seg_begin,
-                                                    const int64_t *seg_end, const int32_t *seg_signal,
-                                                    const int32_t *seg_zero_grad, int n_segments,
-                                                    const volatile int32_t *h_signal, float b1, float b2, float eps,
-                                                    int64_t step, float scale, int n_threads,
-                                                    volatile int64_t *host_progress) {
+static int batched_sparse_step_impl(float *host_param, float *host_grad, float *host_grad_packed, int64_t packed_base,
+                                    float *host_exp_avg, float *host_exp_avg_sq, int cols, const float *col_lr,
+                                    const int32_t *host_rows, const int64_t *seg_begin, const int64_t *seg_end,
+                                    const int32_t *seg_signal, const int32_t *seg_zero_grad, int n_segments,
+                                    const volatile int32_t *h_signal, float b1, float b2, float eps, int64_t step,
+                                    float scale, int n_threads, volatile int64_t *host_progress) {
     if (cols <= 0 || n_segments < 0 || step < 1) {
         clmgs_set_error("cpu_adam: bad arguments (cols=%d n_segments=%d step=%lld)", cols, n_segments, (long long)step);
         return CLMGS_ERR_INVALID;
@@ -273,8 +276,9 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
             const int64_t lo = seg_begin[m], hi = seg_end[m], n = hi - lo;
             const bool zg = seg_zero_grad && seg_zero_grad[m];
             const int64_t a = lo + n * tid / n_threads, b = lo + n * (tid + 1) / n_threads;
-            if (zg) adam_rows<true>(host_param, host_grad, host_exp_avg, host_exp_avg_sq, col_lr, cols, host_rows, a, b, c);
-            else adam_rows<false>(host_param, host_grad, host_exp_avg, host_exp_avg_sq, col_lr, cols, host_rows, a, b, c);
+            if (zg) adam_rows<G_ZERO>(host_param, host_grad, host_exp_avg, host_exp_avg_sq, col_lr, cols, host_rows, a, b, 0, c);
+            else if (host_grad_packed) adam_rows<G_PACKED>(host_param, host_grad_packed, host_exp_avg, host_exp_avg_sq, col_lr, cols, host_rows, a, b, packed_base, c);
+            else adam_rows<G_TABLE>(host_param, host_grad, host_exp_avg, host_exp_avg_sq, col_lr, cols, host_rows, a, b, 0, c);
             // the last thread to finish segment m publishes "segments 0..m are done" (threads run the
             // segments in order, so completion is monotonic)
             if (seg_done[m].fetch_add(1, std::memory_order_acq_rel) + 1 == n_threads && host_progress) {
@@ -296,6 +300,45 @@ CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *ho
     g_stat_rows = rows;
     g_stat_zero_rows = zrows;
     return CLMGS_OK;
+}
+
+CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, float *host_exp_avg,
+                                                    float *host_exp_avg_sq, int cols, const float *col_lr,
+                                                    const int32_t *host_rows, const int64_t *seg_begin,
+                                                    const int64_t *seg_end, const int32_t *seg_signal,
+                                                    const int32_t *seg_zero_grad, int n_segments,
+                                                    const volatile int32_t *h_signal, float b1, float b2, float eps,
+                                                    int64_t step, float scale, int n_threads,
+                                                    volatile int64_t *host_progress) {
+    return batched_sparse_step_impl(host_param, host_grad, nullptr, 0, host_exp_avg, host_exp_avg_sq, cols, col_lr,
+                                    host_rows, seg_begin, seg_end, seg_signal, seg_zero_grad, n_segments, h_signal, b1,
+                                    b2, eps, step, scale, n_threads, host_progress);
+}
+
+// Gradients in a PACKED staging buffer instead of the [N, cols] table: the gradient of list entry r is row
+// (r - packed_base) of host_grad_packed.  The engine's flush writes that buffer with plain DMA copies (contiguous on
+// both sides), the host reads each row once and does not have to zero it again; the gradient table is not touched.
+CLMGS_EXPORT int clmgs_cpu_adam_batched_sparse_step_packed(float *host_param, float *host_grad_packed,
+                                                           int64_t packed_base, float *host_exp_avg,
+                                                           float *host_exp_avg_sq, int cols, const float *col_lr,
+                                                           const int32_t *host_rows, const int64_t *seg_begin,
+                                                           const int64_t *seg_end, const int32_t *seg_signal,
+                                                           const int32_t *seg_zero_grad, int n_segments,
+                                                           const volatile int32_t *h_signal, float b1, float b2,
+                                                           float eps, int64_t step, float scale, int n_threads,
+                                                           volatile int64_t *host_progress) {
+    if (!host_grad_packed || packed_base < 0) {
+        clmgs_set_error("cpu_adam packed: null staging buffer or negative base");
+        return CLMGS_ERR_INVALID;
+    }
+    for (int m = 0; m < n_segments; ++m)
+        if (!(seg_zero_grad && seg_zero_grad[m]) && seg_begin[m] < packed_base && seg_end[m] > seg_begin[m]) {
+            clmgs_set_error("cpu_adam packed: segment %d starts before packed_base", m);
+            return CLMGS_ERR_INVALID;
+        }
+    return batched_sparse_step_impl(host_param, nullptr, host_grad_packed, packed_base, host_exp_avg, host_exp_avg_sq,
+                                    cols, col_lr, host_rows, seg_begin, seg_end, seg_signal, seg_zero_grad, n_segments,
+                                    h_signal, b1, b2, eps, step, scale, n_threads, host_progress);
 }
 
 // out[4] = {wall milliseconds of the last batched_sparse_step call, milliseconds of it spent waiting for gradient

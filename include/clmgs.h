@@ -419,6 +419,21 @@ int clmgs_cpu_adam_batched_sparse_step(float *host_param, float *host_grad, floa
                                        const volatile int32_t *h_signal, float b1,
                                        float b2, float eps, int64_t step, float scale,
                                        int n_threads, volatile int64_t *host_progress);
+/* Same update with the gradients in a PACKED pinned staging buffer instead of the [N, cols] table (new; the
+ * reference accumulates into the table over PCIe, CK/clm_kernels.cu:128-148, and cpu-adam zeroes it afterwards):
+ * the gradient of list entry r is row (r - packed_base) of h_grad_packed.  The engine's flush fills that buffer
+ * with contiguous DMA copies (copy engine, no SMs, no read-modify-write), the host reads every row once and does
+ * not zero it again; the gradient table stays untouched (all zero).  Segments flagged in seg_zero_grad may lie
+ * before packed_base; all others must not. */
+int clmgs_cpu_adam_batched_sparse_step_packed(float *host_param, float *h_grad_packed, int64_t packed_base,
+                                              float *host_exp_avg, float *host_exp_avg_sq, int cols,
+                                              const float *col_lr, const int32_t *host_rows,
+                                              const int64_t *seg_begin, const int64_t *seg_end,
+                                              const int32_t *seg_signal, const int32_t *seg_zero_grad,
+                                              int n_segments, const volatile int32_t *h_signal, float b1,
+                                              float b2, float eps, int64_t step, float scale, int n_threads,
+                                              volatile int64_t *host_progress);
+
 /* Statistics of this process's last clmgs_cpu_adam_batched_sparse_step call (measurement; no counterpart
  * in the reference apart from --log_cpu_adam_trailing_overhead, engine.py:888-917): host_out4 =
  * {wall ms of the call, ms of it spent waiting for gradient flags (slowest thread), rows updated,

@@ -8,6 +8,7 @@ import threading
 import time
 
 import numpy as np
+import pytest
 
 import oracle
 
@@ -238,3 +239,40 @@ print(hashlib.sha256(p.tobytes() + m.tobytes() + v.tobytes()).hexdigest())
         assert r.returncode == 0, r.stderr[-2000:]
         digests[isa] = r.stdout.strip().splitlines()[-1]
     assert digests["avx2"] == digests["auto"], digests
+
+
+def test_cpu_adam_packed_gradients_equal_table_gradients():
+    """clmgs_cpu_adam_batched_sparse_step_packed: the gradient of list entry r comes from row r - packed_base of a
+    packed staging buffer; same update as reading (and re-zeroing) the [N, 48] table, table untouched."""
+    from clmgs import ops
+    rng = np.random.default_rng(5)
+    N = 6000
+    p = rng.standard_normal((N, 48)).astype(np.float32)
+    m = (rng.standard_normal((N, 48)) * 0.1).astype(np.float32)
+    v = (rng.random((N, 48)) * 0.01).astype(np.float32)
+    col_lr = np.array([2.5e-3] * 3 + [2.5e-3 / 20] * 45, np.float32)
+    rows = rng.permutation(N).astype(np.int32)
+    n_unt = 1500                      # list = [untouched | group A | group B]
+    edges = [n_unt, 3500, N]
+    g_table = np.zeros((N, 48), np.float32)
+    g_packed = rng.standard_normal((N - n_unt, 48)).astype(np.float32)
+    g_table[rows[n_unt:]] = g_packed
+    sig = np.ones(2, np.int32)
+    seg_b, seg_e, seg_s, seg_z = [0, edges[0], edges[1]], [edges[0], edges[1], edges[2]], [-1, 0, 1], [1, 0, 0]
+    a = [x.copy() for x in (p, m, v)]
+    ops.cpu_adam_batched_sparse_step(a[0], g_table, a[1], a[2], col_lr, rows, seg_b, seg_e, seg_s, sig, 0.9, 0.999, 1e-15,
+                                     3, 0.25, n_threads=3, seg_zero_grad=seg_z)
+    assert not g_table.any()
+    b = [x.copy() for x in (p, m, v)]
+    untouched_table = np.full((N, 48), 7.0, np.float32)   # must not be read or written
+    keep = g_packed.copy()
+    ops.cpu_adam_batched_sparse_step(b[0], untouched_table, b[1], b[2], col_lr, rows, seg_b, seg_e, seg_s, sig, 0.9, 0.999,
+                                     1e-15, 3, 0.25, n_threads=3, seg_zero_grad=seg_z, grad_packed=g_packed,
+                                     packed_base=n_unt)
+    for x, y in zip(a, b):
+        np.testing.assert_array_equal(x, y)
+    assert (untouched_table == 7.0).all() and np.array_equal(g_packed, keep)
+    with pytest.raises(Exception):    # a gradient-reading segment before packed_base is refused
+        ops.cpu_adam_batched_sparse_step(b[0], untouched_table, b[1], b[2], col_lr, rows, [0], [10], [-1], sig, 0.9, 0.999,
+                                         1e-15, 4, 0.25, n_threads=1, seg_zero_grad=[0], grad_packed=g_packed,
+                                         packed_base=n_unt)
