@@ -22,6 +22,7 @@ on a python thread that drops the GIL inside the C call -- the reference's three
 (engine.py:423-437, 464-641, 767-826).
 """
 import math
+import os
 import threading
 
 import numpy as np
@@ -32,8 +33,29 @@ from . import hostmem, ops
 TILE_SIZE = 16  # strategies/base_engine.py:15
 
 
+_NVTX = os.environ.get("CLMGS_NVTX", "1") != "0"
+
+
+class nvtx_range:
+    """NVTX range around a host-side phase (the reference marks its phases the same way, engine.py:149-853, so an
+    nsys timeline of this engine reads like one of the reference).  CLMGS_NVTX=0 turns them off."""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if _NVTX:
+            torch.cuda.nvtx.range_push(self.name)
+        return self
+
+    def __exit__(self, *a):
+        if _NVTX:
+            torch.cuda.nvtx.range_pop()
+
+
 class StageTimer:
-    """CUDA-event stage timing on the stream each stage is launched on."""
+    """CUDA-event stage timing on the stream each stage is launched on; every stage is also an
+    NVTX range."""
 
     def __init__(self, enabled=False):
         self.enabled = enabled
@@ -48,6 +70,8 @@ class StageTimer:
             self.o, self.name, self.stream = owner, name, stream
 
         def __enter__(self):
+            if _NVTX:
+                torch.cuda.nvtx.range_push(self.name)
             if self.o.enabled:
                 self.s = torch.cuda.Event(enable_timing=True)
                 self.e = torch.cuda.Event(enable_timing=True)
@@ -55,6 +79,8 @@ class StageTimer:
             return self
 
         def __exit__(self, *a):
+            if _NVTX:
+                torch.cuda.nvtx.range_pop()
             if self.o.enabled:
                 self.e.record(self.stream or torch.cuda.current_stream())
                 self.o.pairs.append((self.name, self.s, self.e))
@@ -290,8 +316,10 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
 
     # ---- stage 1: visibility + order ------------------------------------------------------------
     with torch.no_grad():
-        filters, cull = calculate_filters(batched_cameras, gaussians, timer)
-        oc = order_calculation(filters, cull, N, bsz, perm_generator, args, timer, parity)
+        with nvtx_range("calculate_filters"):        # engine.py:376
+            filters, cull = calculate_filters(batched_cameras, gaussians, timer)
+        with nvtx_range("sort cameras"):             # engine.py:389
+            oc = order_calculation(filters, cull, N, bsz, perm_generator, args, timer, parity)
     ordered_cams, filters, sparsity = oc["ordered_cams"], oc["filters"], oc["sparsity"]
     cams = [batched_cameras[i] for i in ordered_cams]
     bitmap = oc["ordered_bitmap"]
@@ -299,6 +327,9 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     # Lazy dense Adam (opt-in): rows no camera touches skip this step's zero-gradient update; the rows this batch
     # does touch first replay whatever they skipped earlier -- before their coefficients are read by the GPU.
     lazy = bool(getattr(args, "lazy_dense_adam", False)) and not args.sparse_adam
+    if not lazy and gaussians.optimizer.cpu_adam.lazy_pending:
+        # the flag was switched off with postponed updates outstanding: replay them before this step's update
+        gaussians.optimizer.cpu_adam.catch_up(None)
     if lazy:
         assert not pipe, "lazy_dense_adam and pipeline_host_adam are not combined"
         ca = gaussians.optimizer.cpu_adam
@@ -353,10 +384,13 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
             prev_worker.join()  # one host Adam at a time, in batch order
         t0 = _t.perf_counter()
         try:
-            cpu_adam.batched_sparse_step(h_grad, oc["rows_host"], seg_begin, seg_end, seg_signal, signal, 1.0 / bsz,
-                                         progress, [1 if (s_ == -1 and not args.sparse_adam and i_ == 0) else 0
-                                                    for i_, s_ in enumerate(seg_signal)],
-                                         grad_packed=h_packed, packed_base=n_unt)
+            if prev is not None and prev["err"]:
+                raise prev["err"][0]   # the previous batch's host update failed: do not update on top of it
+            with nvtx_range("cpu_adam.sparse_step()"):  # engine.py:319
+                cpu_adam.batched_sparse_step(h_grad, oc["rows_host"], seg_begin, seg_end, seg_signal, signal, 1.0 / bsz,
+                                             progress, [1 if (s_ == -1 and not args.sparse_adam and i_ == 0) else 0
+                                                        for i_, s_ in enumerate(seg_signal)],
+                                             grad_packed=h_packed, packed_base=n_unt)
         except Exception as e:  # surfaced after join
             worker_err.append(e)
         worker_times["cpu_adam_thread_ms"] = (_t.perf_counter() - t0) * 1e3
@@ -390,6 +424,8 @@ def _wait_progress(pend, need):
     prog, w = pend["progress"], pend["worker"]
     while prog[0] < need and w.is_alive():
         _t.sleep(5e-5)
+    if pend["err"]:   # the previous host update died: its rows are only partly updated, do not train on them
+        raise pend["err"][0]
 
 
 def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_packed, background, comm_stream, signal,
@@ -464,6 +500,8 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_pa
         for k in range(bsz):
             ids = filters[k]
             cam = cams[k]
+            if _NVTX:
+                torch.cuda.nvtx.range_push("micro_batch_idx: " + str(k))   # engine.py:485
             # geometry of this and the next few cameras does not need SH rows: issue it before waiting on the
             # copy stream so that it hides the host-link latency of the first load
             for kk in range(k, min(bsz, k + 1 + lookahead)):
@@ -507,6 +545,8 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_pa
                             ops.set_signal(signal, bsz - 1 + j, 1)
             n_isects_log.append(fw["n_isects"])
             del fw, v_render, loss_vec
+            if _NVTX:
+                torch.cuda.nvtx.range_pop()
 
         # ---- stage 5: GPU Adam (grads / bsz fused as grad_scale) ------------------------------------
         with timer("gpu_adam"):
@@ -552,6 +592,9 @@ def naive_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_
     N = gaussians.n_gaussians
     dev = gaussians._xyz.device
     h_params, h_grad = gaussians._parameters, parameters_grad_buffer[:N]
+    wait_host_adam(gaussians)
+    if gaussians.optimizer.cpu_adam.lazy_pending:
+        gaussians.optimizer.cpu_adam.catch_up(None)
     filters, cull = calculate_filters(batched_cameras, gaussians, timer)
     sparsity = [f.shape[0] / float(N) for f in filters]
     with timer("bulk_load"):

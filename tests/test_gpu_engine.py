@@ -280,3 +280,18 @@ def test_c4_shaped_small_iteration_matches_live_oracle():
             _close(stt["exp_avg_sq"].cpu().numpy(), st["v_" + key], 2e-3, (it, "v", key))
         _close(gm.optimizer.cpu_adam.exp_avg.numpy(), st["m_sh"], 1e-3, (it, "m_sh"))
         _close(gm.optimizer.cpu_adam.exp_avg_sq.numpy(), st["v_sh"], 2e-3, (it, "v_sh"))
+
+
+def test_cuda_perm_generator_is_accepted():
+    """The reference builds perm_generator on the GPU (train.py:191, used for a CUDA randperm); the engine draws its
+    sample offset on the generator's own device, so both a CUDA and a CPU generator (and None) work."""
+    W, H, bsz = 112, 80, 4
+    spec, g, V, K, P, gts, args, gm, cams, st = _setup(20_000, W, H, bsz, False)
+    args.densification_stats = False
+    comm = torch.cuda.Stream()
+    for gen in (torch.Generator(device=DEV).manual_seed(1), torch.Generator().manual_seed(1), None):
+        losses, ordered, _ = engine.clm_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None,
+                                                                comm, gen)
+        assert sorted(ordered) == list(range(bsz)) and len(losses) == bsz
+        ref_losses, _, _ = TS.train_one_batch(st, V, K, P, gts, W, H, args, ordered)
+        np.testing.assert_allclose([float(l) for l in losses], ref_losses, rtol=2e-5, atol=2e-6)
