@@ -198,7 +198,8 @@ def run_ours(a):
     _tile_bits = (((W + 15) // 16) * ((H + 15) // 16)).bit_length() + 1  # tile_n_bits + cam_n_bits (C = 1)
     LAUNCHES["clmgs_isect_emit_sort"] = 1 + 3 * 4 + 3 + 3 * ((_tile_bits + 7) // 8)
     LAUNCHES["clmgs_isect_sorted_offsets"] = LAUNCHES["clmgs_isect_emit_sort"] + 2  # + offsets fill and suffix-min
-    host_threads = a.cpu_threads or max(1, (os.cpu_count() or 1) // world)
+    # host Adam threads per rank: this rank's share of the cores minus one for the thread that launches kernels
+    host_threads = a.cpu_threads or max(1, (os.cpu_count() or 1) // world - 1)
     if world > 1:
         os.environ.setdefault("CLMGS_CPU_ADAM_PIN", str(local_rank * host_threads))  # each rank its own cores
     t0 = time.time()
@@ -328,6 +329,9 @@ def run_ours(a):
     gm.raster_work_counters = None
     stage_ms = {k: v / nprof for k, v in timer.totals.items()}
     stage_n = {k: v / nprof for k, v in timer.counts.items()}
+    if "isect_count" in stage_ms:   # S4 = tile counts + emission + sort + offsets (SURVEY.md 8d counts them together)
+        stage_ms["isect_sort"] = stage_ms.get("isect_sort", 0.0) + stage_ms.pop("isect_count")
+        stage_n.pop("isect_count", None)
     hs = np.mean(host_stats, axis=0) if host_stats else np.zeros(4)
     timer = engine.StageTimer(False)
 

@@ -223,10 +223,9 @@ def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, tim
                 union_ids=union_ids, slot_of=slot_of, first_edges=first_edges)
 
 
-def geometry_one_camera(gaussians, camera, ids, timer=_NULL_TIMER):
-    """The part of the forward that does not touch the offloaded SH rows (engine.py:51-63,85-100):
-    gather + activations, projection, tile intersection + sort.  Runs while SH rows are still in
-    flight on the copy stream."""
+def geometry_begin(gaussians, camera, ids, timer=_NULL_TIMER):
+    """First part of a camera's geometry (engine.py:51-63,85-97): gather + activations, projection, tile counts.
+    Nothing here waits for the device; the tile total travels to the host behind an event."""
     W, H = camera.image_width, camera.image_height
     tw, th = math.ceil(W / float(TILE_SIZE)), math.ceil(H / float(TILE_SIZE))
     with timer("gather_activate"):
@@ -235,11 +234,29 @@ def geometry_one_camera(gaussians, camera, ids, timer=_NULL_TIMER):
     with timer("projection_fwd"):
         radii, means2d, depths, conics, _ = ops.projection_fwd(means, quats, scales, camera.viewmat[None],
                                                                camera.K[None], W, H)
-    with timer("isect_sort"):
-        flatten_ids, offsets, _ = ops.isect_sorted_offsets(means2d, radii, depths, TILE_SIZE, tw, th)
-    del depths
+    with timer("isect_count"):
+        cnt = ops.isect_count_async(means2d, radii, TILE_SIZE, tw, th)
     return dict(means=means, scales=scales, quats=quats, opac=opac, radii=radii, means2d=means2d, conics=conics,
-                offsets=offsets, flatten_ids=flatten_ids, n_isects=flatten_ids.shape[0])
+                depths=depths, count_state=cnt, tw=tw, th=th)
+
+
+def geometry_finish(fw, timer=_NULL_TIMER):
+    """Second part (engine.py:89-100): emission + tile sort + offsets, sized by the total that geometry_begin sent to
+    the host (it has normally arrived long before: this is issued at least one camera later)."""
+    if "flatten_ids" in fw:
+        return fw
+    with timer("isect_sort"):
+        flatten_ids, offsets, n_isects = ops.isect_sort_counted(fw.pop("count_state"), fw.pop("depths"), TILE_SIZE,
+                                                                fw["tw"], fw["th"])
+    fw.update(offsets=offsets, flatten_ids=flatten_ids, n_isects=n_isects)
+    return fw
+
+
+def geometry_one_camera(gaussians, camera, ids, timer=_NULL_TIMER):
+    """The part of the forward that does not touch the offloaded SH rows (engine.py:51-63,85-100):
+    gather + activations, projection, tile intersection + sort.  Runs while SH rows are still in
+    flight on the copy stream."""
+    return geometry_finish(geometry_begin(gaussians, camera, ids, timer), timer)
 
 
 def shade_one_camera(gaussians, camera, fw, shs, background, timer=_NULL_TIMER, rows_ready=None, ids=None,
@@ -504,9 +521,14 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_pa
                 torch.cuda.nvtx.range_push("micro_batch_idx: " + str(k))   # engine.py:485
             # geometry of this and the next few cameras does not need SH rows: issue it before waiting on the
             # copy stream so that it hides the host-link latency of the first load
+            # The first part (projection, tile counts) is issued `lookahead` cameras ahead, the tile sort one camera
+            # ahead: its size comes from a count that the first part sent to the host two launches earlier, so
+            # reading it does not stall the host (the reference blocks on .item() for every camera).
             for kk in range(k, min(bsz, k + 1 + lookahead)):
                 if geoms[kk] is None:
-                    geoms[kk] = geometry_one_camera(gaussians, cams[kk], filters[kk], timer)
+                    geoms[kk] = geometry_begin(gaussians, cams[kk], filters[kk], timer)
+            for kk in range(k, min(bsz, k + 2)):
+                geometry_finish(geoms[kk], timer)
             fw, geoms[k] = geoms[k], None
             fw = shade_one_camera(gaussians, cam, fw, d_rows, background, timer, rows_ready=rows_evt[k], ids=ids,
                                   slot_of=slot_of)

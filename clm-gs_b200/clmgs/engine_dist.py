@@ -35,8 +35,8 @@ import torch.distributed as dist
 
 from . import ops
 from .dist_rows import RowExchange, ShardMap, merge_requests
-from .engine import (StageTimer, _NULL_TIMER, backward_one_camera, calculate_filters, geometry_one_camera,
-                     order_calculation, shade_one_camera)
+from .engine import (StageTimer, _NULL_TIMER, backward_one_camera, calculate_filters, geometry_begin,
+                     geometry_finish, order_calculation, shade_one_camera)
 
 _GPU_NAMES = ("xyz", "opacity", "scaling", "rotation")
 
@@ -242,7 +242,9 @@ def _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, pla
         cam, ids = cams[k], filters[k]
         for kk in range(k, min(bsz_local, k + 1 + lookahead)):
             if geoms[kk] is None:
-                geoms[kk] = geometry_one_camera(gaussians, cams[kk], filters[kk], timer)
+                geoms[kk] = geometry_begin(gaussians, cams[kk], filters[kk], timer)
+        for kk in range(k, min(bsz_local, k + 2)):
+            geometry_finish(geoms[kk], timer)
         fw, geoms[k] = geoms[k], None
         fw = shade_one_camera(gaussians, cam, fw, d_rows, background, timer, rows_ready=rows_evt[k], ids=ids,
                               slot_of=slot_of)

@@ -3,9 +3,12 @@
 (engine.py:7-13) plus the ``rasterization()`` composite (gsplat/rendering.py:17-402).
 
 Differentiable through torch.autograd.Function exactly where the reference's are
-(_wrapper.py:691-927,1115-1145).  Restrictions, raised as errors (not silently ignored): 3 colour
-channels, tile_size 16, quats/scales (not precomputed covars), no sparse_grad, "classic"
-rasterize mode, render_mode "RGB".
+(_wrapper.py:691-927,1115-1145), including the packed projection (ids from the cull kernel, backward
+through the dense projection-backward kernel) with optional sparse gradients.  Any number of colour
+channels (the 3-channel kernels run once per group of three: alpha compositing is linear in the
+colours, so results and gradients are those of one wide pass), all five render modes (RGB, D, ED, RGB+D,
+RGB+ED).  Restrictions, raised as errors (not silently ignored): tile_size 16, quats/scales (not
+precomputed covars), "classic" rasterize mode.
 """
 import math
 
@@ -39,22 +42,62 @@ class _Projection(torch.autograd.Function):
         return v_means, v_quats, v_scales, None, None, None, None, None, None, None, None, None
 
 
+class _ProjectionPacked(torch.autograd.Function):
+    """_FullyFusedProjectionPacked (_wrapper.py:930-1112).  Forward = the one-pass cull with packed outputs (the
+    PACKED radius rule, fully_fused_projection_packed_fwd.cu:117-119).  Backward: the packed upstream gradients are
+    scattered into dense [C, N] tensors and go through the dense projection-backward kernel, which recomputes the
+    forward from means / quats / scales and only needs `radii > 0` to know which pairs exist."""
+
+    @staticmethod
+    def forward(ctx, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane, radius_clip,
+                sparse_grad):
+        out = ops.cull(means, scales, quats, viewmats, Ks, width, height, True, eps2d, near_plane, far_plane,
+                       radius_clip, packed_outputs=True)
+        cam, gid = out["camera_ids"], out["gaussian_ids"]
+        ctx.save_for_backward(means, quats, scales, viewmats, Ks, cam, gid, out["radii"], out["conics"])
+        ctx.cfg = (width, height, eps2d, sparse_grad)
+        ctx.mark_non_differentiable(cam, gid, out["radii"])
+        return cam, gid, out["radii"], out["means2d"], out["depths"], out["conics"]
+
+    @staticmethod
+    def backward(ctx, v_cam, v_gid, v_radii, v_means2d, v_depths, v_conics):
+        means, quats, scales, viewmats, Ks, cam, gid, radii, conics = ctx.saved_tensors
+        width, height, eps2d, sparse_grad = ctx.cfg
+        C, N = viewmats.shape[0], means.shape[0]
+        flat = cam * N + gid
+
+        def dense(src, tail, dtype=torch.float32):
+            t = torch.zeros((C * N,) + tail, dtype=dtype, device=means.device)
+            if src is not None:
+                t[flat] = src.to(dtype)
+            return t.view((C, N) + tail)
+
+        v_means, v_quats, v_scales = ops.projection_bwd(means, quats, scales, viewmats, Ks, width, height, eps2d,
+                                                        dense(radii, (), torch.int32), dense(conics, (3,)),
+                                                        dense(v_means2d, (2,)), dense(v_depths, ()), dense(v_conics, (3,)))
+        if sparse_grad:  # _wrapper.py:1078-1101: COO gradients over the Gaussians that are visible somewhere
+            rows = torch.unique(gid)
+            sp = lambda g: torch.sparse_coo_tensor(rows[None], g[rows], size=g.shape, is_coalesced=True)
+            v_means, v_quats, v_scales = sp(v_means), sp(v_quats), sp(v_scales)
+        return v_means, v_quats, v_scales, None, None, None, None, None, None, None, None, None
+
+
 def fully_fused_projection(means, covars, quats, scales, viewmats, Ks, width, height, eps2d=0.3, near_plane=0.01,
                            far_plane=1e10, radius_clip=0.0, packed=False, sparse_grad=False,
                            calc_compensations=False):
     """_wrapper.py:141-219.  dense -> (radii [C,N] i32, means2d, depths, conics, compensations);
-    packed -> (camera_ids i64, gaussian_ids i64, radii, means2d, depths, conics, compensations), no grad."""
+    packed -> (camera_ids i64, gaussian_ids i64, radii, means2d, depths, conics, compensations)."""
     if covars is not None:
         raise NotImplementedError("precomputed covars are not on the CLM path; pass quats and scales")
-    if sparse_grad:
-        raise NotImplementedError("sparse_grad is not on the CLM path")
+    if sparse_grad and not packed:
+        raise ValueError("sparse_grad is only supported with packed=True (as in gsplat, _wrapper.py:190-191)")
     if packed:
-        if means.requires_grad or quats.requires_grad or scales.requires_grad:
-            raise NotImplementedError("packed projection is forward-only here (CLM calls it under no_grad, base_engine.py:22)")
-        out = ops.cull(means, scales, quats, viewmats, Ks, width, height, True, eps2d, near_plane, far_plane,
-                       radius_clip, packed_outputs=True)
-        return (out["camera_ids"], out["gaussian_ids"], out["radii"], out["means2d"], out["depths"], out["conics"],
-                None)
+        if calc_compensations:
+            raise NotImplementedError("compensations (antialiased mode) are not on the CLM path")
+        res = _ProjectionPacked.apply(means.contiguous(), quats.contiguous(), scales.contiguous(), viewmats.contiguous(),
+                                      Ks.contiguous(), int(width), int(height), eps2d, near_plane, far_plane, radius_clip,
+                                      bool(sparse_grad))
+        return tuple(res) + (None,)
     return _Projection.apply(means.contiguous(), quats.contiguous(), scales.contiguous(), viewmats.contiguous(),
                              Ks.contiguous(), int(width), int(height), eps2d, near_plane, far_plane, radius_clip,
                              calc_compensations)
@@ -126,13 +169,32 @@ class _RasterizeToPixels(torch.autograd.Function):
 def rasterize_to_pixels(means2d, conics, colors, opacities, image_width, image_height, tile_size, isect_offsets,
                         flatten_ids, backgrounds=None, packed=False, absgrad=False):
     """_wrapper.py:371-497 -> (render_colors [C,H,W,3], render_alphas [C,H,W,1])."""
-    if colors.shape[-1] != 3:
-        raise NotImplementedError("only 3 colour channels are on the CLM path (engine.py:106-117)")
-    if packed:
-        raise NotImplementedError("packed rasterisation inputs: pass dense [C,N,...] tensors")
-    return _RasterizeToPixels.apply(means2d.contiguous(), conics.contiguous(), colors.contiguous(),
-                                    opacities.contiguous(), backgrounds, int(image_width), int(image_height),
-                                    int(tile_size), isect_offsets, flatten_ids, absgrad)
+    D = colors.shape[-1]
+    if backgrounds is not None:
+        assert backgrounds.shape[-1] == D, (backgrounds.shape, D)
+    means2d, conics, opacities = means2d.contiguous(), conics.contiguous(), opacities.contiguous()
+    if D == 3:
+        return _RasterizeToPixels.apply(means2d, conics, colors.contiguous(), opacities, backgrounds, int(image_width),
+                                        int(image_height), int(tile_size), isect_offsets, flatten_ids, absgrad)
+    # Any other channel count: groups of three through the 3-channel kernels (the reference pads to its next
+    # compiled width and chunks above channel_chunk, rendering.py:329-358).  Compositing is linear in the colours, the
+    # alpha / transmittance recursion does not depend on them, and autograd adds the groups' gradients of means2d /
+    # conics / opacities -- the same sums one wide kernel forms.  The alphas (and their gradient) come from group 0.
+    outs, alphas = [], None
+    for c0 in range(0, D, 3):
+        w = min(3, D - c0)
+        col = colors[..., c0:c0 + w]
+        bg = None if backgrounds is None else backgrounds[..., c0:c0 + w]
+        if w < 3:
+            col = torch.nn.functional.pad(col, (0, 3 - w))
+            bg = None if bg is None else torch.nn.functional.pad(bg, (0, 3 - w))
+        rc, ra = _RasterizeToPixels.apply(means2d, conics, col.contiguous(), opacities,
+                                          None if bg is None else bg.contiguous(), int(image_width), int(image_height),
+                                          int(tile_size), isect_offsets, flatten_ids, absgrad and c0 == 0)
+        outs.append(rc[..., :w])
+        if alphas is None:
+            alphas = ra
+    return torch.cat(outs, dim=-1), alphas
 
 
 def rasterization(means, quats, scales, opacities, colors, viewmats, Ks, width, height, near_plane=0.01,

@@ -227,6 +227,44 @@ def isect_sorted_offsets(means2d, radii, depths, tile_size, tile_width, tile_hei
     return flat, off, n_isects
 
 
+def isect_count_async(means2d, radii, tile_size, tile_width, tile_height):
+    """First half of the engine's tile stage without a host sync: tile counts + their inclusive prefix on the
+    device, and the total copied to a pinned word behind an event.  Pass the result to isect_sort_counted() a few
+    launches later -- by then the event has fired and reading the total costs nothing (the reference blocks on
+    cum[-1].item() right here, isect_tiles.cu:165-166)."""
+    means2d = _f32c(means2d)
+    radii = radii.contiguous()
+    dev = means2d.device
+    C, N = radii.shape
+    total = C * N
+    tpg = _empty((max(total, 1),), torch.int32, dev)
+    cum = _empty((max(total, 1),), torch.int64, dev)
+    count = torch.zeros(1, dtype=torch.int64, pin_memory=True)
+    ev = torch.cuda.Event()
+    if total > 0:
+        sc = _scratch(call("clmgs_isect_count_scratch_bytes", total), dev)
+        call("clmgs_isect_count", total, means2d, radii, int(tile_size), int(tile_width), int(tile_height),
+             tpg, cum, sc, sc.numel(), _st())
+        count.copy_(cum[total - 1:total], non_blocking=True)
+    ev.record(torch.cuda.current_stream())
+    return dict(means2d=means2d, radii=radii, cum=cum, tpg=tpg, count=count, event=ev, C=C, N=N)
+
+
+def isect_sort_counted(state, depths, tile_size, tile_width, tile_height):
+    """Second half: depth-sorted flatten_ids per tile + tile offsets (see isect_sorted_offsets)."""
+    state["event"].synchronize()
+    n_isects = int(state["count"][0])
+    depths = _f32c(depths)
+    dev = depths.device
+    C, N = state["C"], state["N"]
+    flat = _empty((n_isects,), torch.int32, dev)
+    off = torch.empty(C, tile_height, tile_width, dtype=torch.int32, device=dev)
+    sc2 = _scratch(call("clmgs_isect_sort_scratch_bytes", C * N, n_isects), dev)
+    call("clmgs_isect_sorted_offsets", C, N, None, state["means2d"], state["radii"], depths, state["cum"], int(tile_size),
+         int(tile_width), int(tile_height), n_isects, flat, off, sc2, sc2.numel(), _st())
+    return flat, off, n_isects
+
+
 def isect_offset_encode(isect_ids, n_cameras, tile_width, tile_height):
     off = torch.empty(n_cameras, tile_height, tile_width, dtype=torch.int32, device=isect_ids.device)
     call("clmgs_isect_offset_encode", isect_ids.shape[0], isect_ids.contiguous(), int(n_cameras),

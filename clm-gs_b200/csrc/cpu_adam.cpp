@@ -12,6 +12,7 @@
 #include <pthread.h>
 #include <sched.h>
 #include <stdlib.h>
+#include <time.h>
 
 #include <algorithm>
 #include <atomic>
@@ -30,6 +31,8 @@ void clmgs_set_error(const char *fmt, ...);
 #define CLMGS_EXPORT extern "C" __attribute__((visibility("default")))
 
 namespace {
+
+constexpr int kPrefetchRows = 6;  // rows of a sparse list are random 192-byte accesses: no hardware prefetcher helps
 
 struct AdamConst {
     float b1, b2, eps, scale, inv_bc1, bc2_rsqrt;
@@ -121,12 +124,14 @@ inline bool use_avx512() {
                                               int64_t b, int64_t packed_base, const AdamConst &c) {                  \
         for (int64_t r = a; r < b; ++r) {                                                                            \
             const int64_t base = (int64_t)(rows ? rows[r] : r) * cols;                                               \
-            if (rows && r + 4 < b) {                                                                                 \
-                const int64_t nb = (int64_t)rows[r + 4] * cols;                                                      \
-                _mm_prefetch((const char *)(param + nb), _MM_HINT_T0);                                               \
-                if (GMODE == G_TABLE) _mm_prefetch((const char *)(grad + nb), _MM_HINT_T0);                          \
-                _mm_prefetch((const char *)(exp_avg + nb), _MM_HINT_T0);                                             \
-                _mm_prefetch((const char *)(exp_avg_sq + nb), _MM_HINT_T0);                                          \
+            if (rows && r + kPrefetchRows < b) { /* every 64-byte line of the row that comes up kPrefetchRows later */ \
+                const int64_t nb = (int64_t)rows[r + kPrefetchRows] * cols;                                          \
+                for (int l = 0; l < cols; l += 16) {                                                                 \
+                    _mm_prefetch((const char *)(param + nb + l), _MM_HINT_T0);                                       \
+                    if (GMODE == G_TABLE) _mm_prefetch((const char *)(grad + nb + l), _MM_HINT_T0);                  \
+                    _mm_prefetch((const char *)(exp_avg + nb + l), _MM_HINT_T0);                                     \
+                    _mm_prefetch((const char *)(exp_avg_sq + nb + l), _MM_HINT_T0);                                  \
+                }                                                                                                    \
             }                                                                                                        \
             float *g = GMODE == G_PACKED ? grad + (r - packed_base) * cols : grad + base;                            \
             ROWFN<GMODE>(param + base, g, exp_avg + base, exp_avg_sq + base, col_lr, cols, c);                       \
@@ -155,11 +160,15 @@ inline int64_t now_ns() {
 // returns the nanoseconds spent waiting
 inline int64_t wait_flag(const volatile int32_t *flag) {
     if (*flag != 0) { __atomic_thread_fence(__ATOMIC_ACQUIRE); return 0; }
+    // Short spin, then sleep in 20 us naps: a gradient group takes milliseconds to arrive, and every host thread
+    // that spins here is a core the kernel-launching thread and the CUDA driver threads cannot have (measured at
+    // C4: with all cores spinning, the GPU ran dry between launches).
     const int64_t t0 = now_ns();
     int spins = 0;
     while (*flag == 0) {
-        _mm_pause();
-        if (++spins > 2000) { std::this_thread::yield(); spins = 0; }
+        if (++spins < 256) { _mm_pause(); continue; }
+        struct timespec ts = {0, 20000};
+        nanosleep(&ts, nullptr);
     }
     __atomic_thread_fence(__ATOMIC_ACQUIRE);
     return now_ns() - t0;
