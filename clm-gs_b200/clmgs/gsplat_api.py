@@ -201,30 +201,67 @@ def rasterization(means, quats, scales, opacities, colors, viewmats, Ks, width, 
                   far_plane=1e10, radius_clip=0.0, eps2d=0.3, sh_degree=None, packed=True, tile_size=16,
                   backgrounds=None, render_mode="RGB", sparse_grad=False, absgrad=False, rasterize_mode="classic",
                   channel_chunk=32):
-    """gsplat.rasterization() (gsplat/rendering.py:17-402) for the options CLM-style training uses.
-    `packed=True` is accepted and computed through the dense path (same results, different memory)."""
-    if render_mode != "RGB" or rasterize_mode != "classic" or sparse_grad:
-        raise NotImplementedError("render_mode=RGB, rasterize_mode=classic, sparse_grad=False only")
+    """gsplat.rasterization() (gsplat/rendering.py:17-402): same arguments, same returns (render_colors [C,H,W,X],
+    render_alphas [C,H,W,1], meta with the keys of rendering.py:384-401).  packed=True really is the packed data
+    flow (meta["camera_ids"] / meta["gaussian_ids"], [nnz, ...] intermediates); render_mode RGB / D / ED / RGB+D /
+    RGB+ED; colours [N,D] / [C,N,D] or SH coefficients [N,K,3] / [C,N,K,3] with sh_degree."""
+    assert render_mode in ("RGB", "D", "ED", "RGB+D", "RGB+ED"), render_mode
+    if rasterize_mode != "classic":
+        raise NotImplementedError("rasterize_mode='antialiased' (compensations) is not on the CLM path")
     C, N = viewmats.shape[0], means.shape[0]
-    radii, means2d, depths, conics, _ = fully_fused_projection(means, None, quats, scales, viewmats, Ks, width, height,
-                                                               eps2d, near_plane, far_plane, radius_clip, False)
+    assert means.shape == (N, 3) and quats.shape == (N, 4) and scales.shape == (N, 3) and opacities.shape == (N,)
+    assert viewmats.shape == (C, 4, 4) and Ks.shape == (C, 3, 3)
+    if sh_degree is None:
+        assert (colors.dim() == 2 and colors.shape[0] == N) or (colors.dim() == 3 and colors.shape[:2] == (C, N)), colors.shape
+    else:
+        assert (colors.dim() == 3 and colors.shape[0] == N and colors.shape[2] == 3) or (
+            colors.dim() == 4 and colors.shape[:2] == (C, N) and colors.shape[3] == 3), colors.shape
+        assert (sh_degree + 1) ** 2 <= colors.shape[-2], colors.shape
+    proj = fully_fused_projection(means, None, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane,
+                                  radius_clip, packed, sparse_grad, False)
+    if packed:
+        camera_ids, gaussian_ids, radii, means2d, depths, conics, _ = proj
+        opac = opacities[gaussian_ids]                       # [nnz]
+    else:
+        radii, means2d, depths, conics, _ = proj
+        opac = opacities.repeat(C, 1)                        # [C, N]
+        camera_ids = gaussian_ids = None
     tile_width, tile_height = math.ceil(width / float(tile_size)), math.ceil(height / float(tile_size))
-    tiles_per_gauss, isect_ids, flatten_ids = isect_tiles(means2d, radii, depths, tile_size, tile_width, tile_height)
+    tiles_per_gauss, isect_ids, flatten_ids = isect_tiles(means2d, radii, depths, tile_size, tile_width, tile_height,
+                                                          packed=packed, n_cameras=C, camera_ids=camera_ids,
+                                                          gaussian_ids=gaussian_ids)
     isect_offsets = isect_offset_encode(isect_ids, C, tile_width, tile_height)
     if sh_degree is None:
-        cols = colors if colors.dim() == 3 else colors[None].expand(C, -1, -1)
+        if packed:
+            cols = colors[gaussian_ids] if colors.dim() == 2 else colors[camera_ids, gaussian_ids]
+        else:
+            cols = colors.expand(C, -1, -1) if colors.dim() == 2 else colors
     else:
         camtoworlds = torch.inverse(viewmats)
-        dirs = means[None, :, :] - camtoworlds[:, None, :3, 3]
-        shs = colors if colors.dim() == 4 else colors[None].expand(C, -1, -1, -1)
+        if packed:
+            dirs = means[gaussian_ids, :] - camtoworlds[camera_ids, :3, 3]
+            shs = colors[gaussian_ids] if colors.dim() == 3 else colors[camera_ids, gaussian_ids]
+        else:
+            dirs = means[None, :, :] - camtoworlds[:, None, :3, 3]
+            shs = colors.expand(C, -1, -1, -1) if colors.dim() == 3 else colors
         cols = spherical_harmonics(sh_degree, dirs.contiguous(), shs.contiguous(), masks=radii > 0)
-        cols = torch.clamp_min(cols + 0.5, 0.0)
-    opac = opacities[None].expand(C, -1).contiguous()
-    render_colors, render_alphas = rasterize_to_pixels(means2d, conics, cols.contiguous(), opac, width, height,
-                                                       tile_size, isect_offsets, flatten_ids, backgrounds,
+        cols = torch.clamp_min(cols + 0.5, 0.0)              # rendering.py:315
+    if render_mode in ("RGB+D", "RGB+ED"):
+        cols = torch.cat((cols, depths[..., None]), dim=-1)
+        if backgrounds is not None:
+            backgrounds = torch.cat([backgrounds, torch.zeros(C, 1, device=backgrounds.device)], dim=-1)
+    elif render_mode in ("D", "ED"):
+        cols = depths[..., None]
+        if backgrounds is not None:
+            backgrounds = torch.zeros(C, 1, device=backgrounds.device)
+    render_colors, render_alphas = rasterize_to_pixels(means2d, conics, cols, opac, width, height, tile_size,
+                                                       isect_offsets, flatten_ids, backgrounds, packed=packed,
                                                        absgrad=absgrad)
-    meta = dict(camera_ids=None, gaussian_ids=None, radii=radii, means2d=means2d, depths=depths, conics=conics,
-                opacities=opac, tile_width=tile_width, tile_height=tile_height, tiles_per_gauss=tiles_per_gauss,
-                isect_ids=isect_ids, flatten_ids=flatten_ids, isect_offsets=isect_offsets, width=width, height=height,
-                tile_size=tile_size, n_cameras=C)
+    if render_mode in ("ED", "RGB+ED"):   # accumulated depth -> expected depth (rendering.py:373-381)
+        render_colors = torch.cat([render_colors[..., :-1], render_colors[..., -1:] / render_alphas.clamp(min=1e-10)],
+                                  dim=-1)
+    meta = dict(camera_ids=camera_ids, gaussian_ids=gaussian_ids, radii=radii, means2d=means2d, depths=depths,
+                conics=conics, opacities=opac, tile_width=tile_width, tile_height=tile_height,
+                tiles_per_gauss=tiles_per_gauss, isect_ids=isect_ids, flatten_ids=flatten_ids,
+                isect_offsets=isect_offsets, width=width, height=height, tile_size=tile_size)
     return render_colors, render_alphas, meta

@@ -304,7 +304,7 @@ def rasterize_bwd(means2d, conics, colors, opacities, width, height, tile_size, 
     dev = means2d.device
     C, th, tw = isect_offsets.shape
     N = opacities.shape[-1]
-    CN = C * N
+    CN = opacities.numel()   # dense [C, N] or packed [nnz]: the kernels index the flattened arrays either way
     v_means2d = _zeros((CN, 2), torch.float32, dev).view(means2d.shape)
     v_conics = _zeros((CN, 3), torch.float32, dev).view(conics.shape)
     v_colors = _zeros((CN, 3), torch.float32, dev).view(colors.shape)
