@@ -77,7 +77,8 @@ class _ProjectionPacked(torch.autograd.Function):
                                                         dense(v_means2d, (2,)), dense(v_depths, ()), dense(v_conics, (3,)))
         if sparse_grad:  # _wrapper.py:1078-1101: COO gradients over the Gaussians that are visible somewhere
             rows = torch.unique(gid)
-            sp = lambda g: torch.sparse_coo_tensor(rows[None], g[rows], size=g.shape, is_coalesced=True)
+            sp = lambda g: torch.sparse_coo_tensor(rows[None], g[rows], size=g.shape, is_coalesced=True,
+                                                   check_invariants=False)
             v_means, v_quats, v_scales = sp(v_means), sp(v_quats), sp(v_scales)
         return v_means, v_quats, v_scales, None, None, None, None, None, None, None, None, None
 

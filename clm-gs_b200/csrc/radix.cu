@@ -370,9 +370,12 @@ int clmgs_radix_sort_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t 
         fill_i32_kernel<<<(unsigned)ceil_div64(n_slots, 256), 256, 0, st>>>(offsets, n_slots, (int32_t)n);
         CLMGS_LAUNCH_OK();
     }
+    // Balanced digits: 13 key bits go as 7 + 6 rather than 8 + 5.  Fewer bins in the wider pass means longer runs per
+    // bin and tile (4096 / 128 = 32 pairs = 128 B instead of 64 B), i.e. fewer partially written 32-byte sectors.
+    const int base_bits = passes ? end_bit / passes : 0, extra = passes ? end_bit % passes : 0;
+    int shift = 0;
     for (int p = 0; p < passes; ++p) {
-        const int shift = 8 * p;
-        const int bits = end_bit - shift < 8 ? end_bit - shift : 8;
+        const int bits = base_bits + (p < extra ? 1 : 0);
         const uint32_t mask = (1u << bits) - 1u;
         const bool last = p == passes - 1;
         radix_hist_kernel<<<(unsigned)ntiles, kThreads, 0, st>>>(n, keys, shift, mask, hist, ntiles);
@@ -393,6 +396,7 @@ int clmgs_radix_sort_u32(int64_t n, uint32_t *keys, uint32_t *keys_alt, int32_t 
         }
         uint32_t *tk = keys; keys = keys_alt; keys_alt = tk;
         int32_t *tv = vals; vals = vals_alt; vals_alt = tv;
+        shift += bits;
     }
     if (keys_out) *keys_out = keys;
     if (vals_out) *vals_out = vals;

@@ -175,6 +175,7 @@ def test_rasterization_sparse_grad_and_render_modes():
     rc2.sum().backward()
     for a, b in zip(leaves, dense):
         assert a.grad.is_sparse and not b.grad.is_sparse
-        torch.testing.assert_close(a.grad.to_dense(), b.grad, rtol=0, atol=0)
+        # two backward runs: the rasteriser's atomics sum in a different order
+        assert float((a.grad.to_dense() - b.grad).abs().max()) <= 1e-3 * float(b.grad.abs().max())
     with pytest.raises(ValueError):
         G.rasterization(*args, packed=False, sparse_grad=True)
