@@ -22,6 +22,7 @@
 //    sums are added by 8 different lanes in parallel.
 #include "common.cuh"
 #include <math_constants.h>
+#include <stdlib.h>
 
 constexpr int kTile = 16;
 constexpr int kBlock = kTile * kTile;
@@ -288,7 +289,10 @@ __device__ __forceinline__ int inside_any(int warp_bin_final, int start) {
     return warp_bin_final >= start ? warp_bin_final : start - 1;
 }
 
-template <bool HAS_BG, bool ABSGRAD>
+// TILE_ACC: the per-Gaussian sums of a tile's 8 warps meet in shared memory (shared atomics, one slot of 9-11 floats
+// per staged Gaussian) and leave as ONE set of global atomics per (tile, Gaussian) after the batch, instead of one
+// set per (warp, Gaussian) as in the reference (rasterize_to_pixels_bwd.cu:215-246).
+template <bool HAS_BG, bool ABSGRAD, bool TILE_ACC>
 __global__ void __launch_bounds__(kBlock, 4)
 raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float *__restrict__ conics,
                   const float *__restrict__ colors, const float *__restrict__ opacities,
@@ -303,6 +307,9 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
     __shared__ float4 s_b[kBlock];  // conic.z, opacity, r, g
     __shared__ float4 s_c[kBlock];  // b, first row, last row (pixel-centre y), position in the batch
     __shared__ int s_wcnt[kBlock / 32];
+    constexpr int kAcc = ABSGRAD ? 11 : 9;  // rgb, conic xyz, mean xy, opacity (, |mean| xy)
+    __shared__ float s_acc[TILE_ACC ? kBlock * kAcc : 1];
+    __shared__ int s_hit[TILE_ACC ? kBlock : 1];
     const int cam = blockIdx.z;
     const int tile_id = blockIdx.y * a.tile_width + blockIdx.x;
     const int i = blockIdx.y * kTile + threadIdx.y;
@@ -369,6 +376,11 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
         int slot;
         const int batch_size = stage_compact(keep, tr, s_wcnt, slot);
         if (keep) { s_id[slot] = gid_s; s_a[slot] = sA; s_b[slot] = sB; s_c[slot] = sC; }
+        if (TILE_ACC) {
+#pragma unroll
+            for (int q = 0; q < kAcc; ++q) s_acc[q * kBlock + tr] = 0.f;
+            s_hit[tr] = 0;
+        }
         __syncthreads();
         const int t_lo = batch_end - warp_bin_final;  // entries with a smaller position are behind every pixel's last
         for (int tc = 0; tc < batch_size; ++tc) {
@@ -414,6 +426,21 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
             const float red = butterfly8(v, lane);
             v_opa = warp_sum(v_opa);
             if (ABSGRAD) { v_ax = warp_sum(v_ax); v_ay = warp_sum(v_ay); }
+            if (TILE_ACC) {
+                // value q of staged Gaussian tc lives at s_acc[q * kBlock + tc]
+                if ((lane & 3) == 0) {
+                    const int k = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+                    atomicAdd(&s_acc[k * kBlock + tc], red);
+                } else if (lane == 1) {
+                    atomicAdd(&s_acc[8 * kBlock + tc], v_opa);
+                    s_hit[tc] = 1;
+                } else if (ABSGRAD && lane == 2) {
+                    atomicAdd(&s_acc[9 * kBlock + tc], v_ax);
+                } else if (ABSGRAD && lane == 3) {
+                    atomicAdd(&s_acc[10 * kBlock + tc], v_ay);
+                }
+                continue;
+            }
             const int64_t gid = s_id[tc];
             if ((lane & 3) == 0) {
                 const int k = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
@@ -425,6 +452,25 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
                 atomicAdd(v_means2d_abs + 2 * gid, v_ax);
             } else if (ABSGRAD && lane == 3) {
                 atomicAdd(v_means2d_abs + 2 * gid + 1, v_ay);
+            }
+        }
+        if (TILE_ACC) {
+            __syncthreads();  // every warp's contribution to this batch is in s_acc
+            if (tr < batch_size && s_hit[tr]) {
+                const int64_t gid = s_id[tr];
+                atomicAdd(v_colors + 3 * gid, s_acc[0 * kBlock + tr]);
+                atomicAdd(v_colors + 3 * gid + 1, s_acc[1 * kBlock + tr]);
+                atomicAdd(v_colors + 3 * gid + 2, s_acc[2 * kBlock + tr]);
+                atomicAdd(v_conics + 3 * gid, s_acc[3 * kBlock + tr]);
+                atomicAdd(v_conics + 3 * gid + 1, s_acc[4 * kBlock + tr]);
+                atomicAdd(v_conics + 3 * gid + 2, s_acc[5 * kBlock + tr]);
+                atomicAdd(v_means2d + 2 * gid, s_acc[6 * kBlock + tr]);
+                atomicAdd(v_means2d + 2 * gid + 1, s_acc[7 * kBlock + tr]);
+                atomicAdd(v_opacities + gid, s_acc[8 * kBlock + tr]);
+                if (ABSGRAD) {
+                    atomicAdd(v_means2d_abs + 2 * gid, s_acc[9 * kBlock + tr]);
+                    atomicAdd(v_means2d_abs + 2 * gid + 1, s_acc[10 * kBlock + tr]);
+                }
             }
         }
     }
@@ -445,13 +491,17 @@ CLMGS_EXPORT int clmgs_rasterize_bwd(int C, int64_t N, int64_t n_isects, const f
     RasterArgs a{C, N, n_isects, width, height, tile_width, tile_height};
     dim3 grid(tile_width, tile_height, C), block(kTile, kTile, 1);
     cudaStream_t st = as_stream(stream);
-#define LAUNCH(BG, AB)                                                                                          \
-    raster_bwd_kernel<BG, AB><<<grid, block, 0, st>>>(a, (const float2 *)means2d, conics, colors, opacities,     \
-                                                      backgrounds, tile_offsets, flatten_ids, render_alphas,     \
-                                                      last_ids, v_render_colors, v_render_alphas, v_means2d_abs, \
-                                                      v_means2d, v_conics, v_colors, v_opacities)
-    if (backgrounds) { if (v_means2d_abs) LAUNCH(true, true); else LAUNCH(true, false); }
-    else { if (v_means2d_abs) LAUNCH(false, true); else LAUNCH(false, false); }
+    // CLMGS_RASTER_BWD_TILE_ACC=0 selects the per-warp global atomics (kept for A/B measurements)
+    static const bool tile_acc = [] { const char *e = getenv("CLMGS_RASTER_BWD_TILE_ACC"); return !(e && e[0] == '0'); }();
+#define LAUNCH(BG, AB, TA)                                                                                          \
+    raster_bwd_kernel<BG, AB, TA><<<grid, block, 0, st>>>(a, (const float2 *)means2d, conics, colors, opacities,     \
+                                                          backgrounds, tile_offsets, flatten_ids, render_alphas,     \
+                                                          last_ids, v_render_colors, v_render_alphas, v_means2d_abs, \
+                                                          v_means2d, v_conics, v_colors, v_opacities)
+#define LAUNCH2(BG, AB) do { if (tile_acc) LAUNCH(BG, AB, true); else LAUNCH(BG, AB, false); } while (0)
+    if (backgrounds) { if (v_means2d_abs) LAUNCH2(true, true); else LAUNCH2(true, false); }
+    else { if (v_means2d_abs) LAUNCH2(false, true); else LAUNCH2(false, false); }
+#undef LAUNCH2
 #undef LAUNCH
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
