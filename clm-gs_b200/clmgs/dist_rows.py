@@ -12,6 +12,7 @@ gather / accumulate are callbacks (CUDA kernels in the engine, plain indexing in
 from dataclasses import dataclass
 from typing import Callable, List
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -98,3 +99,77 @@ def merge_requests(recv_local: torch.Tensor, n_local: int, want_untouched: bool 
     dst_index = pos[recv_local]
     untouched = torch.nonzero(~mask).flatten() if want_untouched else None
     return uniq, dst_index, untouched, mask
+
+
+@dataclass
+class ChunkPlan:
+    """Gradient return in K chunks (see plan_chunked)."""
+    K: int
+    send_order: torch.Tensor          # this rank's needed ids in slot order: (last chunk, id) -- chunk slices are owner-major
+    send_counts: List[List[int]]      # [K][G]: rows of chunk c owned by rank o
+    recv_counts: List[List[int]]      # [K][G]: rows of chunk c arriving from rank s
+    acc_order: torch.Tensor           # owner: touched local rows in accumulator order: (final chunk, local row)
+    final_counts: List[int]           # [K]: rows whose last contribution arrives with chunk c
+    dst_index: List[torch.Tensor]     # [K]: accumulator slot of every row received in exchange c (source-major)
+    untouched: torch.Tensor           # owner: local rows nobody touches (or None)
+    touched_mask: torch.Tensor        # owner: bool [n_local]
+    rows_from_peers: int
+
+
+def plan_chunked(exchange: "RowExchange", need_ids: torch.Tensor, last_chunk: torch.Tensor, K: int, n_local: int,
+                 want_untouched: bool = False) -> ChunkPlan:
+    """Sparse reduce-scatter of touched-row gradients, pipelined in K chunks of the local camera sequence.
+
+    A rank's gradient for a row is final once the last of ITS cameras that sees the row is done (chunk
+    last_chunk[i] for need_ids[i]); it is sent with that chunk's exchange.  An owner may get contributions for one row
+    from several ranks in different exchanges, so the row's sum is final -- and can go to the owner's host Adam --
+    after the latest of them.  All lists involved are ascending, so the whole plan is flag tables and compactions
+    (no sort).  need_ids: ascending int64 global ids; last_chunk: int64 in [0, K) aligned with need_ids."""
+    G, dev = exchange.world, need_ids.device
+    shard = exchange.shard
+    lo, _ = shard.range_of(exchange.rank)
+    inner = torch.tensor(shard.bounds[1:-1], dtype=torch.int64, device=dev)
+    cuts = torch.searchsorted(need_ids, inner).tolist() if G > 1 else []
+    tot_edges = [0] + cuts + [need_ids.shape[0]]
+    send_tot = [tot_edges[i + 1] - tot_edges[i] for i in range(G)]
+    cnt_out = torch.empty(G, dtype=torch.int64, device=dev)
+    dist.all_to_all_single(cnt_out, torch.tensor(send_tot, dtype=torch.int64, device=dev), group=exchange.group)
+    recv_tot = cnt_out.tolist()
+    # ids and chunk tags travel as one word (owner-major = ascending order)
+    recv_packed = torch.empty(sum(recv_tot), dtype=torch.int64, device=dev)
+    dist.all_to_all_single(recv_packed, (need_ids * K + last_chunk).contiguous(), output_split_sizes=recv_tot,
+                           input_split_sizes=send_tot, group=exchange.group)
+    recv_local = torch.div(recv_packed, K, rounding_mode="floor") - lo
+    recv_tag = recv_packed % K
+    # requester: slots in (chunk, id) order; per chunk the rows are ascending = owner-major
+    order_parts, send_counts = [], []
+    for c in range(K):
+        ids_c = need_ids[last_chunk == c]
+        order_parts.append(ids_c)
+        cc = torch.searchsorted(ids_c, inner).tolist() if G > 1 else []
+        e = [0] + cc + [ids_c.shape[0]]
+        send_counts.append([e[i + 1] - e[i] for i in range(G)])
+    send_order = torch.cat(order_parts) if order_parts else need_ids
+    # owner: final chunk of every touched local row = latest chunk in which anybody sends it
+    fc = torch.full((n_local,), -1, dtype=torch.int64, device=dev)
+    if recv_local.numel():
+        fc.scatter_reduce_(0, recv_local, recv_tag, reduce="amax", include_self=True)
+    acc_parts, final_counts = [], []
+    for c in range(K):
+        rows_c = torch.nonzero(fc == c).flatten()
+        acc_parts.append(rows_c)
+        final_counts.append(int(rows_c.shape[0]))
+    acc_order = torch.cat(acc_parts) if acc_parts else torch.zeros(0, dtype=torch.int64, device=dev)
+    pos = torch.empty(n_local, dtype=torch.int64, device=dev)
+    pos[acc_order] = torch.arange(acc_order.shape[0], dtype=torch.int64, device=dev)
+    seg_edges = torch.tensor(np.cumsum([0] + recv_tot), dtype=torch.int64, device=dev)
+    dst_index, recv_counts = [], []
+    for c in range(K):
+        sel = torch.nonzero(recv_tag == c).flatten()          # keeps source-major, ascending order
+        dst_index.append(pos[recv_local[sel]])
+        e = torch.searchsorted(sel, seg_edges).tolist()
+        recv_counts.append([e[i + 1] - e[i] for i in range(G)])
+    touched = fc >= 0
+    untouched = torch.nonzero(~touched).flatten() if want_untouched else None
+    return ChunkPlan(K, send_order, send_counts, recv_counts, acc_order, final_counts, dst_index, untouched, touched,
+                     int(need_ids.shape[0] - send_tot[exchange.rank]))

@@ -12,16 +12,18 @@ ONE optimiser step per call.  Rank g owns the Gaussian range [g S, (g+1) S), S =
                hop and the eight host links add up
 
   per step   : 1. cull + TSP order of the LOCAL cameras; need_ids = ascending union of their Gaussians
-               2. plan: ids all-to-all -> every owner knows which of its rows will receive gradients and from
-                  whom; it merges the (already sorted) lists with a flag table (no sort), starts its host Adam
-                  thread, which waits on per-chunk flags
+               2. plan: the local camera sequence is cut into K chunks; ids + "chunk of my last use" all-to-all ->
+                  every owner knows which of its rows will receive gradients, from whom and in which chunk's
+                  exchange the last contribution arrives; it merges the (already sorted) lists with flag tables
+                  (no sort) and starts its host Adam thread, which waits on per-chunk flags
                3. copy stream loads first-use group k of the local cameras into the batch-resident rows (slots in
                   ascending-id = owner-major order); compute stream renders camera k, accumulates SH gradients
                   into a slot-shaped buffer and the dense gradients of the replicated attributes
-               4. sparse reduce-scatter of the SH gradients: NCCL all-to-all-v straight out of the slot buffer
-                  (owner-major already) -> owner sums duplicates with 16-byte vector atomics -> stores its rows to
-                  a packed pinned staging buffer chunk by chunk (DMA), one flag per chunk -> host Adam consumes chunk j while
-                  chunk j+1 crosses the link
+               4. after each chunk of cameras, on a side stream: sparse reduce-scatter of the rows whose gradient
+                  is final on this rank -- NCCL all-to-all-v straight out of the slot buffer (slots are in
+                  (last chunk, id) order, so a chunk is one owner-major slice) -> owner sums with 16-byte vector
+                  atomics -> rows whose last contribution this was leave by DMA into a packed pinned staging
+                  buffer + one flag -> the owner's host Adam updates them while later cameras render
                5. NCCL reduce-scatter of the dense gradients -> owner Adam on its slice (moments sharded) ->
                   all-gather of the updated slices
                6. join host Adam; barrier (the next step reads rows other ranks just updated)
@@ -34,7 +36,7 @@ import torch
 import torch.distributed as dist
 
 from . import ops
-from .dist_rows import RowExchange, ShardMap, merge_requests
+from .dist_rows import RowExchange, ShardMap, merge_requests, plan_chunked
 from .engine import (StageTimer, _NULL_TIMER, backward_one_camera, calculate_filters, geometry_begin,
                      geometry_finish, order_calculation, shade_one_camera)
 
@@ -111,39 +113,47 @@ def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters
         oc = order_calculation(filters, cull, N, bsz_local, perm_generator, args, timer, host_rows=False)
         ordered, filters, sparsity = oc["ordered_cams"], oc["filters"], oc["sparsity"]
         cams = [local_cameras[i] for i in ordered]
-        union_ids, fe = oc["union_ids"], oc["first_edges"]     # grouped by first use (int32), slot edges per camera
+        union_ids, fe = oc["union_ids"], oc["first_edges"]     # grouped by first use (int32), id ranges per camera
         n_need = int(fe[-1])
+        K = max(1, min(int(getattr(args, "dist_grad_chunks", 8)), bsz_local // 2 if bsz_local >= 2 else 1))
+        chunk_of = [p * K // bsz_local for p in range(bsz_local)]            # camera position -> chunk
         with timer("need_ids"):
-            # ascending union = owner-major order; slot of a Gaussian = its rank in it
-            need_ids = torch.nonzero(oc["ordered_bitmap"]).flatten()
+            need_ids = torch.nonzero(oc["ordered_bitmap"]).flatten()          # ascending union = owner-major order
             assert need_ids.shape[0] == n_need
-            need32 = need_ids.to(torch.int32)
-            slot_of = torch.empty(N, dtype=torch.int32, device=dev)
-            ops.slot_map(need32, slot_of)
+            # oc["visibility"] = ffs of the ordered bitmap: key k > 0 <-> last used by camera position bsz - k
+            last_pos = bsz_local - oc["visibility"][need_ids].to(torch.int64)
+            last_chunk = torch.div(last_pos * K, bsz_local, rounding_mode="floor")
 
         # ---- 2. plan + owner-side merge + host Adam thread ---------------------------------------------
         with timer("plan"):
-            plan = ctx.exchange.plan(need_ids)
-            uniq, dst_index, untouched, touched_mask = merge_requests(plan.recv_local, n_local,
-                                                                      want_untouched=not args.sparse_adam)
-            n_uniq = int(uniq.shape[0])
-            n_unt = 0 if untouched is None else int(untouched.shape[0])
+            plan = plan_chunked(ctx.exchange, need_ids, last_chunk, K, n_local, want_untouched=not args.sparse_adam)
+            slot_of = torch.empty(N, dtype=torch.int32, device=dev)
+            ops.slot_map(plan.send_order.to(torch.int32), slot_of)            # slots in (last chunk, id) order
+            n_uniq = int(plan.acc_order.shape[0])
+            n_unt = 0 if plan.untouched is None else int(plan.untouched.shape[0])
             rows_host = _pinned_i32(gaussians, n_local)
             if n_unt:
-                rows_host[:n_unt].copy_(untouched.to(torch.int32), non_blocking=True)
-            rows_host[n_unt:n_unt + n_uniq].copy_(uniq.to(torch.int32), non_blocking=True)
+                rows_host[:n_unt].copy_(plan.untouched.to(torch.int32), non_blocking=True)
+            rows_host[n_unt:n_unt + n_uniq].copy_(plan.acc_order.to(torch.int32), non_blocking=True)
             torch.cuda.current_stream().synchronize()
-        J = max(1, min(int(getattr(args, "final_flush_chunks", 8)), max(1, n_uniq // 65536)))
-        edges = [n_uniq * j // J for j in range(J + 1)]
+        # host-Adam segments: [untouched (dense Adam only)] + rows whose sum is final after exchange c, c = 0..K-1;
+        # the last group leaves in J pieces so that the host works on piece j while piece j+1 crosses the link
+        f_edges = np.concatenate([[0], np.cumsum(plan.final_counts)]).astype(np.int64)
+        n_lastg = int(plan.final_counts[K - 1])
+        J = max(1, min(int(getattr(args, "final_flush_chunks", 8)), max(1, n_lastg // 65536)))
+        piece = [n_lastg * j // J for j in range(J + 1)]
         seg_b, seg_e, seg_sig, seg_zg = [], [], [], []
         if n_unt:  # dense Adam: untouched rows decay their moments; gradient rows are zero -> shortcut, no wait
             seg_b.append(0); seg_e.append(n_unt); seg_sig.append(-1); seg_zg.append(1)
+        for c in range(K - 1):
+            seg_b.append(n_unt + int(f_edges[c])); seg_e.append(n_unt + int(f_edges[c + 1])); seg_sig.append(c); seg_zg.append(0)
         for j in range(J):
-            seg_b.append(n_unt + edges[j]); seg_e.append(n_unt + edges[j + 1]); seg_sig.append(j); seg_zg.append(0)
-        signal = _signal_flags(gaussians, J)
+            seg_b.append(n_unt + int(f_edges[K - 1]) + piece[j]); seg_e.append(n_unt + int(f_edges[K - 1]) + piece[j + 1])
+            seg_sig.append(K - 1 + j); seg_zg.append(0)
+        signal = _signal_flags(gaussians, K - 1 + J)
         worker_err, worker_times = [], {}
         from .engine import _packed_staging
-        h_packed = _packed_staging(gaussians, n_uniq)   # row i = summed gradient of uniq[i] = list entry n_unt + i
+        h_packed = _packed_staging(gaussians, n_uniq)   # row i = summed gradient of acc_order[i] = list entry n_unt + i
 
         def cpuadam_thread():
             import time as _t
@@ -158,9 +168,8 @@ def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters
         worker = threading.Thread(target=cpuadam_thread, daemon=True)
         worker.start()
         try:
-            out = _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, plan, uniq, dst_index,
-                                       touched_mask, edges, signal, h_table, h_packed, background, comm_stream,
-                                       flush_stream, timer)
+            out = _render_and_exchange(gaussians, ctx, cams, filters, oc, slot_of, plan, chunk_of, f_edges, piece,
+                                       signal, h_table, h_packed, background, comm_stream, flush_stream, timer)
         except BaseException:
             torch.cuda.synchronize()
             h_packed.zero_()
@@ -182,7 +191,7 @@ def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters
         timer.collect()
     gaussians.last_batch_stats = dict(n_visible=[f.shape[0] for f in filters], n_isects=out["n_isects"], n_union=n_need,
                                       n_first=int(fe[1]), n_owner_rows=n_uniq, n_adam_rows=n_uniq,
-                                      rows_from_peers=int(n_need - plan.send_counts[ctx.rank]),
+                                      rows_from_peers=plan.rows_from_peers, grad_chunks=K,
                                       cpu_adam_trailing_ms=join_ms, **worker_times)
     return out["losses"], ordered, sparsity
 
@@ -204,17 +213,19 @@ def _signal_flags(gaussians, n):
     return buf
 
 
-def _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, plan, uniq, dst_index, touched_mask,
-                         edges, signal, h_table, h_packed, background, comm_stream, flush_stream, timer):
+def _render_and_exchange(gaussians, ctx, cams, filters, oc, slot_of, plan, chunk_of, f_edges, piece, signal, h_table,
+                         h_packed, background, comm_stream, flush_stream, timer):
     args = gaussians.args
     dev = gaussians._xyz.device
-    bsz_local, G, S = len(cams), ctx.world, ctx.shard.shard
+    bsz_local, G, S, K = len(cams), ctx.world, ctx.shard.shard, plan.K
     bsz_global = bsz_local * G
-    n_local = ctx.hi - ctx.lo
     compute = torch.cuda.current_stream()
     union_ids, fe = oc["union_ids"], oc["first_edges"]
     n_need = int(fe[-1])
     lookahead = max(0, int(getattr(args, "geometry_lookahead", 3)))
+    if getattr(gaussians, "_xchg_stream", None) is None or gaussians._xchg_stream.device != dev:
+        gaussians._xchg_stream = torch.cuda.Stream(device=dev, priority=-1)
+    xchg_stream = gaussians._xchg_stream
 
     # ---- 3. rows in (copy stream, first-use groups) + cameras (compute stream) --------------------------
     start_evt = torch.cuda.Event()
@@ -234,6 +245,15 @@ def _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, pla
             e.record(comm_stream)
             rows_evt.append(e)
     d_grad = ops._zeros((n_need, 48), torch.float32, dev)
+    n_uniq = int(plan.acc_order.shape[0])
+    acc = ops._zeros((n_uniq, 48), torch.float32, dev)      # owner-side sums, rows in (final chunk, local row) order
+    zero_evt = torch.cuda.Event()
+    zero_evt.record(compute)
+    xchg_stream.wait_event(zero_evt)
+    d_grad.record_stream(xchg_stream)
+    acc.record_stream(xchg_stream)
+    acc.record_stream(flush_stream)
+    s_edges = np.concatenate([[0], np.cumsum([sum(c) for c in plan.send_counts])]).astype(np.int64)
     # dense gradients of the replicated attributes, padded to G x S rows for the reduce-scatter
     grads = {n: torch.zeros_like(getattr(gaussians, "_" + n + "_padded")) for n in _GPU_NAMES}
     gview = {n: grads[n][: gaussians.n_gaussians] for n in _GPU_NAMES}
@@ -260,24 +280,37 @@ def _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, pla
         n_isects.append(fw["n_isects"])
         del fw, v_render, loss_vec
 
-    # ---- 4. SH gradients: sparse reduce-scatter to the owners, owner stores + flags ---------------------
-    with timer("grad_exchange"):
-        recv = torch.empty(plan.recv_local.shape[0], 48, dtype=torch.float32, device=dev)
-        dist.all_to_all_single(recv, d_grad, output_split_sizes=plan.recv_counts, input_split_sizes=plan.send_counts,
-                               group=ctx.group)
-        acc = ops._zeros((uniq.shape[0], 48), torch.float32, dev)
-        ops.rows_accumulate(acc, recv, dst_index)
-    acc_ready = torch.cuda.Event()
-    acc_ready.record(compute)
-    acc.record_stream(flush_stream)
-    with torch.cuda.stream(flush_stream):
-        flush_stream.wait_event(acc_ready)
-        with timer("grad_handoff", flush_stream):
-            for j in range(len(edges) - 1):   # contiguous on both sides: plain DMA copies (copy engine, no SMs)
-                c0, c1 = edges[j], edges[j + 1]
-                if c1 > c0:
-                    h_packed[c0:c1].copy_(acc[c0:c1], non_blocking=True)
-                ops.set_signal(signal, j, 1)
+        # ---- 4. after the last camera of chunk c: its rows' gradients are final on this rank -> sparse
+        # reduce-scatter to the owners (NCCL all-to-all-v straight out of the slot buffer), owners accumulate, and
+        # the rows whose LAST contribution this was go to the host (DMA into the packed staging buffer + flag)
+        c = chunk_of[k]
+        if k == bsz_local - 1 or chunk_of[k + 1] != c:
+            done = torch.cuda.Event()
+            done.record(compute)
+            with torch.cuda.stream(xchg_stream):
+                xchg_stream.wait_event(done)
+                with timer("grad_exchange", xchg_stream):
+                    recv = ops._empty((sum(plan.recv_counts[c]), 48), torch.float32, dev)
+                    dist.all_to_all_single(recv, d_grad[int(s_edges[c]):int(s_edges[c + 1])],
+                                           output_split_sizes=plan.recv_counts[c],
+                                           input_split_sizes=plan.send_counts[c], group=ctx.group)
+                    ops.rows_accumulate(acc, recv, plan.dst_index[c])
+                summed = torch.cuda.Event()
+                summed.record(xchg_stream)
+            with torch.cuda.stream(flush_stream):
+                flush_stream.wait_event(summed)
+                with timer("grad_handoff", flush_stream):   # contiguous on both sides: DMA copies (copy engine, no SMs)
+                    f0 = int(f_edges[c])
+                    if c < K - 1:
+                        if f_edges[c + 1] > f0:
+                            h_packed[f0:int(f_edges[c + 1])].copy_(acc[f0:int(f_edges[c + 1])], non_blocking=True)
+                        ops.set_signal(signal, c, 1)
+                    else:
+                        for j in range(len(piece) - 1):
+                            c0, c1 = f0 + piece[j], f0 + piece[j + 1]
+                            if c1 > c0:
+                                h_packed[c0:c1].copy_(acc[c0:c1], non_blocking=True)
+                            ops.set_signal(signal, K - 1 + j, 1)
 
     # ---- 5. GPU-resident attributes: reduce-scatter -> owner Adam on its slice -> all-gather ---------------
     shards = {}
@@ -287,10 +320,11 @@ def _render_and_exchange(gaussians, ctx, cams, filters, oc, need32, slot_of, pla
             shards[n] = torch.empty((S,) + tuple(full.shape[1:]), dtype=full.dtype, device=dev)
             dist.reduce_scatter_tensor(shards[n], full, group=ctx.group)
     with timer("gpu_adam"):
-        vis = touched_mask.view(torch.uint8) if args.sparse_adam else None
+        vis = plan.touched_mask.view(torch.uint8) if args.sparse_adam else None
         gaussians.optimizer.gpu_adam.step(shards, visibility=vis, grad_scale=1.0 / bsz_global)
     with timer("all_gather_params"):
         for n in _GPU_NAMES:
             full = getattr(gaussians, "_" + n + "_padded")
             dist.all_gather_into_tensor(full, full[ctx.rank * S:(ctx.rank + 1) * S].clone(), group=ctx.group)
+    xchg_stream.synchronize()
     return dict(losses=losses, n_isects=n_isects)

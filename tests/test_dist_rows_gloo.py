@@ -118,3 +118,65 @@ def test_owner_merge_and_shared_table_two_ranks(tmp_path):
         ref[needs[r]] += r + 1
     got = np.concatenate([np.load(tmp_path / ("grad_%d.npy" % r)) for r in range(world)])
     np.testing.assert_array_equal(got, ref)
+
+
+def _chunk_worker(rank, world, port, N, K, needs, tags, out_dir):
+    """plan_chunked end to end on CPU: K exchanges, owner accumulates through dst_index, a row is 'final' after the
+    exchange given by final_counts; afterwards every touched row holds the sum of all ranks' contributions."""
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path[:0] = [root, os.path.join(root, "clm-gs_b200")]
+    from clmgs.dist_rows import RowExchange, ShardMap, plan_chunked
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    shard = ShardMap(N, world)
+    lo, hi = shard.range_of(rank)
+    ex = RowExchange(shard, rank)
+    need, tag = torch.from_numpy(needs[rank]), torch.from_numpy(tags[rank])
+    plan = plan_chunked(ex, need, tag, K, hi - lo, want_untouched=True)
+    # slot order = (chunk, id); chunk slices owner-major
+    assert torch.equal(torch.sort(plan.send_order)[0], need)
+    off = 0
+    for c in range(K):
+        n_c = sum(plan.send_counts[c])
+        ids_c = plan.send_order[off:off + n_c]
+        assert bool((ids_c[1:] > ids_c[:-1]).all()) and torch.equal(ids_c, need[tag == c])
+        off += n_c
+    acc = torch.zeros(plan.acc_order.shape[0], 48)
+    final_seen = torch.zeros(plan.acc_order.shape[0], dtype=torch.bool)
+    grads = torch.full((need.shape[0], 48), float(rank + 1))      # rows in slot order; value identifies the sender
+    off, f_off = 0, 0
+    for c in range(K):
+        n_c = sum(plan.send_counts[c])
+        recv = torch.empty(sum(plan.recv_counts[c]), 48)
+        dist.all_to_all_single(recv, grads[off:off + n_c].contiguous(), output_split_sizes=plan.recv_counts[c],
+                               input_split_sizes=plan.send_counts[c])
+        acc.index_add_(0, plan.dst_index[c], recv)
+        # nothing arrives for a row after its final chunk
+        assert not bool(final_seen[plan.dst_index[c]].any()), "a contribution arrived after the row was declared final"
+        final_seen[f_off:f_off + plan.final_counts[c]] = True
+        off += n_c
+        f_off += plan.final_counts[c]
+    assert bool(final_seen.all()) and f_off == plan.acc_order.shape[0]
+    my_grad = torch.zeros(hi - lo, 48)
+    my_grad[plan.acc_order] = acc
+    assert torch.equal(torch.sort(torch.cat([plan.acc_order, plan.untouched]))[0], torch.arange(hi - lo))
+    assert torch.equal(plan.touched_mask.nonzero().flatten(), torch.sort(plan.acc_order)[0])
+    np.save(os.path.join(out_dir, "grad_%d.npy" % rank), my_grad.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_chunked_gradient_return_two_ranks(tmp_path):
+    N, world, K = 1003, 2, 4
+    rng = np.random.default_rng(2)
+    needs = [np.sort(rng.choice(N, 600, replace=False)).astype(np.int64),
+             np.sort(rng.choice(N, 350, replace=False)).astype(np.int64)]
+    tags = [rng.integers(0, K, len(n)).astype(np.int64) for n in needs]
+    tags[1][:] = np.where(np.arange(len(tags[1])) % 3 == 0, K - 1, tags[1])   # uneven chunks
+    mp.spawn(_chunk_worker, args=(world, _free_port(), N, K, needs, tags, str(tmp_path)), nprocs=world, join=True)
+    ref = np.zeros((N, 48), np.float32)
+    for r in range(world):
+        ref[needs[r]] += r + 1
+    got = np.concatenate([np.load(tmp_path / ("grad_%d.npy" % r)) for r in range(world)])
+    np.testing.assert_array_equal(got, ref)
