@@ -159,8 +159,8 @@ def algorithmic_work(stats, N, B, W, H, sparse_adam):
         rows_load_first=("host_link_h2d", 192 * n_first),
         rows_prefetch=("host_link_h2d", 192 * max(0, n_union - n_first)),
         grad_handoff=("host_link_d2h", 192 * n_union),
-        bulk_load=("host_link_h2d", 192 * N),
-        bulk_store=("host_link_d2h", 192 * N),
+        bulk_load=("host_link_h2d", 236 * N),    # naive_offload: all 59 floats per Gaussian, both ways
+        bulk_store=("host_link_d2h", 236 * N),
     )
     work = stats.get("raster_work")
     if work:
@@ -228,7 +228,7 @@ def run_ours(a):
     def train_step(cams, timer=None):
         if a.strategy == "naive":
             return engine.naive_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None, comm, gen,
-                                                        timer=timer)
+                                                        timer=timer, offload_all=True)  # all 59 floats, as the reference
         if ctx is None:
             return engine.clm_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None, comm, gen,
                                                       timer=timer)

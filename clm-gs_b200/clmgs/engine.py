@@ -600,13 +600,44 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_pa
 
 
 @torch.no_grad()
+class _NaiveHostState:
+    """naive_offload keeps EVERY parameter and its optimiser state on the host (strategies/naive_offload/
+    gaussian_model.py:88-147: one cpu_adam.CPUAdam over xyz / f_dc / f_rest / opacity / scaling / rotation): pinned
+    copies of the four GPU-resident tensors, their gradient tables and a host Adam each (same batch-scaled
+    hyper-parameters as the GPU Adam they replace)."""
+
+    def __init__(self, gaussians):
+        from .model import CpuAdam
+        self.param, self.grad, self.adam = {}, {}, {}
+        for g in gaussians.optimizer.gpu_adam.param_groups:
+            p = g["params"][0]
+            h = hostmem.pinned_tensor(tuple(p.shape), torch.float32)
+            h.copy_(p)
+            self.param[g["name"]] = h
+            self.grad[g["name"]] = hostmem.pinned_tensor(tuple(p.shape), torch.float32, zero=True)
+            self.adam[g["name"]] = CpuAdam(h, [p.shape[1]], [g["lr"]], g["betas"], g["eps"],
+                                           gaussians.optimizer.cpu_adam.n_threads)
+        self.groups = gaussians.optimizer.gpu_adam.param_groups
+
+
+def naive_sync_to_gpu(gaussians):
+    """After naive_offload_train_one_batch(offload_all=True) the host copies are the up-to-date parameters; bring
+    them to the GPU tensors (the next naive step does this itself)."""
+    st = getattr(gaussians, "_naive_host", None)
+    if st is not None:
+        for g in st.groups:
+            g["params"][0].copy_(st.param[g["name"]], non_blocking=True)
+        torch.cuda.synchronize()
+
+
 def naive_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_grad_buffer, background, pipe_args,
-                                  comm_stream=None, perm_generator=None, timer=None):
+                                  comm_stream=None, perm_generator=None, timer=None, offload_all=False):
     """Minimal ZeRO-offload-style baseline for BASELINE.json's "clm_offload vs naive_offload" comparison
     (strategies/naive_offload/engine.py: load ALL offloaded parameters to the GPU in one transfer, render the
     cameras, send ALL gradients back in one transfer, then update on the CPU -- no selection, no overlap).
-    Built from the same kernels; only the SH table is offloaded here (the reference's naive mode also keeps
-    xyz/opacity/scale/rotation on the host, i.e. it moves 59 instead of 48 floats per Gaussian).
+    Built from the same kernels.  offload_all=False offloads only the 48 SH floats (the other 11 stay on the GPU with
+    the GPU Adam, as in clm_offload); offload_all=True is the reference's naive mode: all 59 floats per Gaussian live
+    on the host, travel both ways every step and are updated by host Adams (what bench.py --strategy naive runs).
     Same math as clm_offload_train_one_batch; cameras are processed in input order."""
     timer = timer or _NULL_TIMER
     args = gaussians.args
@@ -617,6 +648,14 @@ def naive_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_
     wait_host_adam(gaussians)
     if gaussians.optimizer.cpu_adam.lazy_pending:
         gaussians.optimizer.cpu_adam.catch_up(None)
+    host = None
+    if offload_all:
+        host = getattr(gaussians, "_naive_host", None)
+        if host is None or host.param["xyz"].shape[0] != N:
+            host = gaussians._naive_host = _NaiveHostState(gaussians)
+        with timer("bulk_load"):   # the 11 "selection-critical" floats come from the host as well
+            for g in host.groups:
+                g["params"][0].copy_(host.param[g["name"]], non_blocking=True)
     filters, cull = calculate_filters(batched_cameras, gaussians, timer)
     sparsity = [f.shape[0] / float(N) for f in filters]
     with timer("bulk_load"):
@@ -639,17 +678,27 @@ def naive_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_
         backward_one_camera(gaussians, cam, ids, d_rows, d_grad, fw, v_render[None], grads, timer, slot_of=ident)
         n_isects.append(fw["n_isects"])
         del fw, v_render
-    with timer("gpu_adam"):
-        vis = (cull["bitmap"] != 0).to(torch.uint8) if args.sparse_adam else None
-        gaussians.optimizer.gpu_adam.step(grads, visibility=vis, grad_scale=1.0 / bsz)
+    if not offload_all:
+        with timer("gpu_adam"):
+            vis = (cull["bitmap"] != 0).to(torch.uint8) if args.sparse_adam else None
+            gaussians.optimizer.gpu_adam.step(grads, visibility=vis, grad_scale=1.0 / bsz)
     with timer("bulk_store"):
         h_grad.copy_(d_grad, non_blocking=True)
+        if offload_all:
+            for name in host.grad:
+                host.grad[name].copy_(grads[name], non_blocking=True)
     if args.sparse_adam:
         rows = torch.nonzero(cull["bitmap"]).flatten().to(torch.int32).cpu().numpy()
     else:
         rows = np.arange(N, dtype=np.int32)
     torch.cuda.synchronize()
-    gaussians.optimizer.cpu_adam.batched_sparse_step(h_grad, rows, [0], [len(rows)], [-1], np.zeros(1, np.int32), 1.0 / bsz)
+    nosig = np.zeros(1, np.int32)
+    gaussians.optimizer.cpu_adam.batched_sparse_step(h_grad, rows, [0], [len(rows)], [-1], nosig, 1.0 / bsz)
+    if offload_all:
+        for g in host.groups:   # the xyz learning rate follows its schedule (update_learning_rate)
+            ad = host.adam[g["name"]]
+            ad.columns_lr[:] = g["lr"]
+            ad.batched_sparse_step(host.grad[g["name"]], rows, [0], [len(rows)], [-1], nosig, 1.0 / bsz)
     if args.sparse_adam:
         h_grad.zero_()  # rows outside `rows` hold zeros already; keep the table's invariant explicit
     if timer.enabled:

@@ -295,3 +295,26 @@ def test_cuda_perm_generator_is_accepted():
         assert sorted(ordered) == list(range(bsz)) and len(losses) == bsz
         ref_losses, _, _ = TS.train_one_batch(st, V, K, P, gts, W, H, args, ordered)
         np.testing.assert_allclose([float(l) for l in losses], ref_losses, rtol=2e-5, atol=2e-6)
+
+
+def test_naive_offload_all_parameters_on_host_matches_oracle():
+    """offload_all=True = the reference's naive_offload: all 59 floats per Gaussian live on the host, travel both ways
+    every step and are updated by host Adams (strategies/naive_offload/gaussian_model.py:88-147)."""
+    W, H, bsz = 112, 80, 4
+    spec, g, V, K, P, gts, args, gm, cams, st = _setup(20_000, W, H, bsz, False)
+    args.densification_stats = False
+    for it in range(2):
+        losses, order, _ = engine.naive_offload_train_one_batch(gm, None, cams, gm.parameters_grad_buffer, None, None,
+                                                                offload_all=True)
+        ref_losses, _, _ = TS.train_one_batch(st, V, K, P, gts, W, H, args, order)
+        np.testing.assert_allclose([float(l) for l in losses], ref_losses, rtol=5e-5, atol=5e-6)
+    host = gm._naive_host
+    for name, key in (("xyz", "xyz"), ("scaling", "log_scale"), ("rotation", "raw_quat"), ("opacity", "opacity_logit")):
+        _close(host.adam[name].exp_avg.numpy(), st["m_" + key], 1e-3, ("m", key))
+        _close(host.adam[name].exp_avg_sq.numpy(), st["v_" + key], 2e-3, ("v", key))
+    _close(gm.optimizer.cpu_adam.exp_avg.numpy(), st["m_sh"], 1e-3, "m_sh")
+    engine.naive_sync_to_gpu(gm)
+    m_ref = np.abs(st["m_xyz"])
+    well = m_ref > 1e-2 * m_ref.max()
+    d = np.abs(gm._xyz.cpu().numpy() - st["xyz"])[well].max() / np.abs(st["xyz"] - g["xyz"]).max()
+    assert d < 5e-3, d
