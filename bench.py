@@ -217,7 +217,8 @@ def run_ours(a):
                          workers=max(1, (os.cpu_count() or 1) // world))  # each rank generates only its SH shard
     args = model.TrainArgs(bsz=global_batch, sparse_adam=sparse_adam, cpu_adam_threads=host_threads)
     gm = model.GaussianModelCLMOffload(3, dev).create_from_arrays(g["xyz"], g["log_scale"], g["raw_quat"],
-                                                                 g["opacity_logit"], sh_host)
+                                                                 g["opacity_logit"], sh_host,
+                                                                 grad_table=(a.strategy == "naive"))
     extent = g["extent"]
     del g
     if ctx is not None:
