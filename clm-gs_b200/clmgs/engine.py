@@ -599,7 +599,6 @@ def _train_cameras(gaussians, batched_cameras, oc, cull, filters, h_params, h_pa
     return losses, ordered_cams, sparsity
 
 
-@torch.no_grad()
 class _NaiveHostState:
     """naive_offload keeps EVERY parameter and its optimiser state on the host (strategies/naive_offload/
     gaussian_model.py:88-147: one cpu_adam.CPUAdam over xyz / f_dc / f_rest / opacity / scaling / rotation): pinned
@@ -630,6 +629,7 @@ def naive_sync_to_gpu(gaussians):
         torch.cuda.synchronize()
 
 
+@torch.no_grad()
 def naive_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_grad_buffer, background, pipe_args,
                                   comm_stream=None, perm_generator=None, timer=None, offload_all=False):
     """Minimal ZeRO-offload-style baseline for BASELINE.json's "clm_offload vs naive_offload" comparison
