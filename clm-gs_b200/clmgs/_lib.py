@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _PKG = os.path.dirname(_HERE)
 _ROOT = os.path.dirname(_PKG)
 HEADER = os.path.join(_ROOT, "include", "clmgs.h")
-LIB_PATH = os.path.join(_PKG, "libclmgs.so")
+LIB_PATH = os.environ.get("CLMGS_LIB_PATH") or os.path.join(_PKG, "libclmgs.so")   # override: tuning variants only
 
 _SCALARS = {"int": C.c_int, "int64_t": C.c_int64, "float": C.c_float, "size_t": C.c_size_t,
             "int32_t": C.c_int32}

@@ -18,8 +18,21 @@
 
 namespace {
 
-constexpr int kThreads = 256;
-constexpr int kItems = 16;
+// tunables (tools/radix_sweep.sh builds variants with -D...)
+#ifndef CLMGS_RADIX_THREADS
+#define CLMGS_RADIX_THREADS 256
+#endif
+#ifndef CLMGS_RADIX_ITEMS
+#define CLMGS_RADIX_ITEMS 16
+#endif
+#ifndef CLMGS_RADIX_BLOCKS_PER_SM
+#define CLMGS_RADIX_BLOCKS_PER_SM 3
+#endif
+#ifndef CLMGS_RADIX_STAGES
+#define CLMGS_RADIX_STAGES 2
+#endif
+constexpr int kThreads = CLMGS_RADIX_THREADS;
+constexpr int kItems = CLMGS_RADIX_ITEMS;
 constexpr int kTile = kThreads * kItems;  // 4096 pairs per block
 constexpr int kWarps = kThreads / 32;
 constexpr int kBins = 256;
@@ -112,7 +125,7 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N)); }
 
-constexpr int kScatterBlocksPerSM = 3;
+constexpr int kScatterBlocksPerSM = CLMGS_RADIX_BLOCKS_PER_SM;
 constexpr size_t kStageBytes = (size_t)kTile * 8;            // keys + values of one tile
 constexpr size_t kScatterDynSmem = 2 * kStageBytes;          // double buffered: 64 KB
 
