@@ -108,7 +108,7 @@ LAUNCHES = dict(clmgs_cull_count=2, clmgs_cull_emit=1, clmgs_gather_activate=1, 
                 clmgs_selective_adam=1, clmgs_adam_dense=1, clmgs_extract_first_use=1, clmgs_slot_map=1,
                 clmgs_rows_gather_i32=1, clmgs_rows_flush_slots=1, clmgs_sh_colors_fwd_slots=1,
                 clmgs_sh_colors_bwd_slots=1, clmgs_densification_stats=1, clmgs_rows_accumulate=1,
-                clmgs_rows_scatter_grad_i64=1, clmgs_rows_gather_to_slots=1)
+                clmgs_rows_scatter_grad_i64=1, clmgs_rows_gather_to_slots=1, clmgs_store_i64_to_host=1)
 
 
 def count_launches(lib):

@@ -245,7 +245,8 @@ def isect_count_async(means2d, radii, tile_size, tile_width, tile_height):
         sc = _scratch(call("clmgs_isect_count_scratch_bytes", total), dev)
         call("clmgs_isect_count", total, means2d, radii, int(tile_size), int(tile_width), int(tile_height),
              tpg, cum, sc, sc.numel(), _st())
-        count.copy_(cum[total - 1:total], non_blocking=True)
+        # by a kernel, not a memcpy: the D2H copy engine is busy with the gradient flush's bulk DMA
+        call("clmgs_store_i64_to_host", count, cum[total - 1:total], _st())
     ev.record(torch.cuda.current_stream())
     return dict(means2d=means2d, radii=radii, cum=cum, tpg=tpg, count=count, event=ev, C=C, N=N)
 

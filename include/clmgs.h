@@ -279,6 +279,11 @@ int clmgs_rows_scatter_grad_retention(const float *d_grad, float *h_grad, float 
                                       const int32_t *src_rows_to_next, int64_t n_host,
                                       int64_t n_next, int accum, void *stream);
 int clmgs_set_signal(int32_t *h_flags, int index, int value, void *stream);
+/* *h_dst = *d_src by a one-thread kernel (h_dst pinned + mapped).  For data-dependent sizes the host needs (the
+ * tile total the reference reads with .item(), isect_tiles.cu:165-166): unlike a cudaMemcpyAsync it does not queue
+ * behind bulk DMA transfers on the device-to-host copy engine.  Record an event after it and read *h_dst once the
+ * event has fired. */
+int clmgs_store_i64_to_host(int64_t *h_dst, const int64_t *d_src, void *stream);
 /* Batch-resident SH rows ("slots"; new design replacing the per-camera re-packing of retained rows,
  * CK/clm_kernels.cu:71-126,206-268 + engine.py:519-641,767-803).  Every Gaussian the batch touches
  * owns one row of a device table for the whole batch: rows are loaded when their first camera comes
