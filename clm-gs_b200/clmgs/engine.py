@@ -135,17 +135,21 @@ def _pinned_rows_buffer(n, parity=0):
     return buf
 
 
-def _packed_staging(gaussians, n_rows, which=0):
-    """Pinned [rows, 48] staging buffer the gradient flush DMAs into and the host Adam reads from; grown in 1/8-octave
-    steps and kept across batches (two of them only in pipelined mode, where the previous batch's host Adam may
-    still be reading its own)."""
+def _packed_staging(gaussians, n_rows, which=0, cap=None):
+    """Pinned [rows, 48] staging buffer the gradient flush DMAs into and the host Adam reads from; kept across
+    batches and grown with 25 % headroom (pinning gigabytes takes seconds: it must not happen in steady state), never
+    beyond `cap` rows (two of them only in pipelined mode, where the previous batch's host Adam may still be reading
+    its own)."""
     bufs = getattr(gaussians, "_packed_grad_staging", None)
     if bufs is None:
         bufs = gaussians._packed_grad_staging = {}
     buf = bufs.get(which)
     if buf is None or buf.shape[0] < n_rows:
         bufs[which] = None
-        buf = bufs[which] = hostmem.pinned_tensor((ops._bucket(max(n_rows, 1)), 48), torch.float32)
+        want = ops._bucket(max(int(n_rows * 1.25), 1))
+        if cap is not None:
+            want = max(n_rows, min(want, int(cap)))
+        buf = bufs[which] = hostmem.pinned_tensor((want, 48), torch.float32)
     return buf
 
 
@@ -393,7 +397,7 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
     prev_worker = prev["worker"] if prev is not None else None
     # packed pinned staging for this batch's SH gradients: row s = slot s = list entry n_unt + s (see order_calculation)
     n_unt = int(re_[0])
-    h_packed = _packed_staging(gaussians, N - n_unt, parity if pipe else 0)
+    h_packed = _packed_staging(gaussians, N - n_unt, parity if pipe else 0, cap=N)
 
     def cpuadam_thread():
         import time as _t

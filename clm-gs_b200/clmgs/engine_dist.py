@@ -153,7 +153,7 @@ def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters
         signal = _signal_flags(gaussians, K - 1 + J)
         worker_err, worker_times = [], {}
         from .engine import _packed_staging
-        h_packed = _packed_staging(gaussians, n_uniq)   # row i = summed gradient of acc_order[i] = list entry n_unt + i
+        h_packed = _packed_staging(gaussians, n_uniq, cap=n_local)   # row i = summed gradient of acc_order[i] = list entry n_unt + i
 
         def cpuadam_thread():
             import time as _t
