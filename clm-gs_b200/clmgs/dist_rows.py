@@ -114,6 +114,7 @@ class ChunkPlan:
     untouched: torch.Tensor           # owner: local rows nobody touches (or None)
     touched_mask: torch.Tensor        # owner: bool [n_local]
     rows_from_peers: int
+    remote_slot: torch.Tensor = None  # aligned with send_order: the row's slot in ITS OWNER's accumulator (peer push)
 
 
 def plan_chunked(exchange: "RowExchange", need_ids: torch.Tensor, last_chunk: torch.Tensor, K: int, n_local: int,
@@ -171,5 +172,11 @@ def plan_chunked(exchange: "RowExchange", need_ids: torch.Tensor, last_chunk: to
         recv_counts.append([e[i + 1] - e[i] for i in range(G)])
     touched = fc >= 0
     untouched = torch.nonzero(~touched).flatten() if want_untouched else None
+    # every requester also learns where its rows live in their owners' accumulators, so that the gradient return can
+    # be a direct accumulate into peer memory instead of send + receive + accumulate
+    slot_at_owner = torch.empty(need_ids.shape[0], dtype=torch.int64, device=dev)
+    dist.all_to_all_single(slot_at_owner, pos[recv_local].contiguous(), output_split_sizes=send_tot,
+                           input_split_sizes=recv_tot, group=exchange.group)
+    remote_slot = torch.cat([slot_at_owner[last_chunk == c] for c in range(K)]) if K else slot_at_owner
     return ChunkPlan(K, send_order, send_counts, recv_counts, acc_order, final_counts, dst_index, untouched, touched,
-                     int(need_ids.shape[0] - send_tot[exchange.rank]))
+                     int(need_ids.shape[0] - send_tot[exchange.rank]), remote_slot)

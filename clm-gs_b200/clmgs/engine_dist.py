@@ -41,6 +41,7 @@ from .engine import (StageTimer, _NULL_TIMER, backward_one_camera, calculate_fil
                      geometry_finish, order_calculation, shade_one_camera)
 
 _GPU_NAMES = ("xyz", "opacity", "scaling", "rotation")
+_SIGNAL_TIMEOUT_MS = 120_000   # a peer that never signals traps the wait instead of hanging the GPU
 
 
 class DistContext:
@@ -76,6 +77,16 @@ def training_setup_dist(gaussians, args, ctx):
         setattr(gaussians, name, buf[:N])
     gaussians.training_setup(args, gpu_shard=(ctx.lo, ctx.hi))
     gaussians.dist_ctx = ctx
+    ctx.symm = None
+    if G > 1 and getattr(args, "dist_grad_exchange", "peer") == "peer":
+        # Owner-side gradient accumulators in SYMMETRIC memory: every rank maps every rank's buffer, so a renderer
+        # adds its gradient rows straight into the owner's HBM over NVLink (vector atomics) -- the sparse
+        # reduce-scatter is ONE kernel per (chunk, owner) with no send / receive buffers and no collective call.
+        import torch.distributed._symmetric_memory as symm_mem
+        ctx.acc_sym = symm_mem.empty(S * 48, dtype=torch.float32, device=dev)
+        ctx.acc_sym.zero_()
+        ctx.symm = symm_mem.rendezvous(ctx.acc_sym, ctx.group if ctx.group is not None else dist.group.WORLD)
+        ctx.peer_acc = [ctx.symm.get_buffer(r, (S, 48), torch.float32) for r in range(G)]
     ctx.table.register_cuda()
     gaussians.shared_parameters = ctx.table.tensor
     torch.cuda.synchronize()
@@ -246,13 +257,16 @@ def _render_and_exchange(gaussians, ctx, cams, filters, oc, slot_of, plan, chunk
             rows_evt.append(e)
     d_grad = ops._zeros((n_need, 48), torch.float32, dev)
     n_uniq = int(plan.acc_order.shape[0])
-    acc = ops._zeros((n_uniq, 48), torch.float32, dev)      # owner-side sums, rows in (final chunk, local row) order
+    # owner-side sums, rows in (final chunk, local row) order; peer mode: this rank's symmetric buffer (zeroed at the
+    # end of the previous step, before the barrier)
+    acc = ctx.peer_acc[ctx.rank][:n_uniq] if ctx.symm is not None else ops._zeros((n_uniq, 48), torch.float32, dev)
     zero_evt = torch.cuda.Event()
     zero_evt.record(compute)
     xchg_stream.wait_event(zero_evt)
     d_grad.record_stream(xchg_stream)
-    acc.record_stream(xchg_stream)
-    acc.record_stream(flush_stream)
+    if ctx.symm is None:
+        acc.record_stream(xchg_stream)
+        acc.record_stream(flush_stream)
     s_edges = np.concatenate([[0], np.cumsum([sum(c) for c in plan.send_counts])]).astype(np.int64)
     # dense gradients of the replicated attributes, padded to G x S rows for the reduce-scatter
     grads = {n: torch.zeros_like(getattr(gaussians, "_" + n + "_padded")) for n in _GPU_NAMES}
@@ -290,11 +304,27 @@ def _render_and_exchange(gaussians, ctx, cams, filters, oc, slot_of, plan, chunk
             with torch.cuda.stream(xchg_stream):
                 xchg_stream.wait_event(done)
                 with timer("grad_exchange", xchg_stream):
-                    recv = ops._empty((sum(plan.recv_counts[c]), 48), torch.float32, dev)
-                    dist.all_to_all_single(recv, d_grad[int(s_edges[c]):int(s_edges[c + 1])],
-                                           output_split_sizes=plan.recv_counts[c],
-                                           input_split_sizes=plan.send_counts[c], group=ctx.group)
-                    ops.rows_accumulate(acc, recv, plan.dst_index[c])
+                    if ctx.symm is not None:
+                        # peer push: add this chunk's rows into each owner's accumulator (its HBM, over NVLink), then
+                        # tell the owners; the chunk's sums are complete here once every peer has signalled
+                        off = int(s_edges[c])
+                        for o in range(G):
+                            n_o = plan.send_counts[c][o]
+                            if n_o:
+                                ops.rows_accumulate(ctx.peer_acc[o], d_grad[off:off + n_o], plan.remote_slot[off:off + n_o])
+                            off += n_o
+                        for o in range(G):
+                            if o != ctx.rank:
+                                ctx.symm.put_signal(o, c, _SIGNAL_TIMEOUT_MS)
+                        for o in range(G):
+                            if o != ctx.rank:
+                                ctx.symm.wait_signal(o, c, _SIGNAL_TIMEOUT_MS)
+                    else:
+                        recv = ops._empty((sum(plan.recv_counts[c]), 48), torch.float32, dev)
+                        dist.all_to_all_single(recv, d_grad[int(s_edges[c]):int(s_edges[c + 1])],
+                                               output_split_sizes=plan.recv_counts[c],
+                                               input_split_sizes=plan.send_counts[c], group=ctx.group)
+                        ops.rows_accumulate(acc, recv, plan.dst_index[c])
                 summed = torch.cuda.Event()
                 summed.record(xchg_stream)
             with torch.cuda.stream(flush_stream):
@@ -327,4 +357,7 @@ def _render_and_exchange(gaussians, ctx, cams, filters, oc, slot_of, plan, chunk
             full = getattr(gaussians, "_" + n + "_padded")
             dist.all_gather_into_tensor(full, full[ctx.rank * S:(ctx.rank + 1) * S].clone(), group=ctx.group)
     xchg_stream.synchronize()
+    if ctx.symm is not None:
+        flush_stream.synchronize()       # the DMA copies out of the accumulator are done
+        acc.zero_()                      # ready for the next step's pushes (the caller's barrier orders it before them)
     return dict(losses=losses, n_isects=n_isects)

@@ -47,6 +47,7 @@ class TrainArgs:
     cpu_adam_threads: int = 0  # 0 = all hardware threads
     final_flush_chunks: int = 8  # last camera: flush + host Adam pipelined in this many pieces
     dist_grad_chunks: int = 8  # multi-GPU: the local cameras' SH gradients return to their owners in this many exchanges
+    dist_grad_exchange: str = "peer"  # "peer": accumulate straight into the owner's HBM over NVLink; "nccl": all-to-all-v
     pipeline_host_adam: bool = False  # opt-in: return before the host Adam finished; the next call overlaps it
     lazy_dense_adam: bool = False  # opt-in (dense Adam only): postpone the zero-gradient updates of untouched rows
     rows_lookahead: int = 2  # SH-row prefetches issued this many cameras ahead on the copy stream

@@ -19,6 +19,7 @@ import torch.distributed as dist
 from clmgs import engine, engine_dist, model, scene as S
 
 sparse = "--sparse" in sys.argv
+exchange = "nccl" if "--nccl" in sys.argv else "peer"   # gradient return: peer-memory accumulate (default) / all-to-all-v
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
 dev = "cuda:%d" % int(os.environ["LOCAL_RANK"])
@@ -29,7 +30,7 @@ spec = S.SceneSpec("distcheck", n, W, H, B, "aerial", 50.0, 0)
 g = S.make_gaussians(spec)
 V, K, P = S.make_cameras(spec, B, g["extent"])
 gts = S.make_gt_images(spec, B)
-args = model.TrainArgs(bsz=B, cpu_adam_threads=2, sparse_adam=sparse)
+args = model.TrainArgs(bsz=B, cpu_adam_threads=2, sparse_adam=sparse, dist_grad_exchange=exchange)
 ctx = engine_dist.DistContext(n)
 table = ctx.create_shared_table()
 table.array[ctx.lo:ctx.hi] = g["sh"][ctx.lo:ctx.hi]
@@ -95,7 +96,8 @@ if rank == 0:
     if sparse:   # untouched rows are untouched on both sides
         unt = (ref.optimizer.cpu_adam.exp_avg_sq.numpy() == 0).all(1)
         ok &= bool(np.array_equal(sh_all[unt], np.asarray(g["sh"])[unt]))
-    print("DIST PARITY", "OK" if ok else "FAILED", "world", world, "sparse", sparse, "rows from peers' ranges",
+    print("DIST PARITY", "OK" if ok else "FAILED", "world", world, "sparse", sparse, "exchange",
+          "peer" if ctx.symm is not None else "nccl", "rows from peers' ranges",
           gm.last_batch_stats["rows_from_peers"])
 flag = torch.tensor([1 if ok else 0], device=dev)
 dist.broadcast(flag, src=0)

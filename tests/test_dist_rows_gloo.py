@@ -152,6 +152,11 @@ def _chunk_worker(rank, world, port, N, K, needs, tags, out_dir):
         dist.all_to_all_single(recv, grads[off:off + n_c].contiguous(), output_split_sizes=plan.recv_counts[c],
                                input_split_sizes=plan.send_counts[c])
         acc.index_add_(0, plan.dst_index[c], recv)
+        # peer-push mode: the requester already knows each row's slot in its owner's accumulator
+        slots = torch.empty(sum(plan.recv_counts[c]), dtype=torch.int64)
+        dist.all_to_all_single(slots, plan.remote_slot[off:off + n_c].contiguous(), output_split_sizes=plan.recv_counts[c],
+                               input_split_sizes=plan.send_counts[c])
+        assert torch.equal(slots, plan.dst_index[c])
         # nothing arrives for a row after its final chunk
         assert not bool(final_seen[plan.dst_index[c]].any()), "a contribution arrived after the row was declared final"
         final_seen[f_off:f_off + plan.final_counts[c]] = True

@@ -31,7 +31,8 @@ def test_dist_engine_world_1(extra):
     _run(1, extra)
 
 
-@pytest.mark.parametrize("extra", [[], ["--sparse"]], ids=["dense_adam", "sparse_adam"])
+@pytest.mark.parametrize("extra", [[], ["--sparse"], ["--nccl"], ["--sparse", "--nccl"]],
+                         ids=["dense_adam_peer", "sparse_adam_peer", "dense_adam_nccl", "sparse_adam_nccl"])
 def test_dist_engine_world_2(extra):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (run with gpurun --gpus 2); the world-of-1 test above covers the code path")
