@@ -20,10 +20,12 @@ ONE optimiser step per call.  Rank g owns the Gaussian range [g S, (g+1) S), S =
                   ascending-id = owner-major order); compute stream renders camera k, accumulates SH gradients
                   into a slot-shaped buffer and the dense gradients of the replicated attributes
                4. after each chunk of cameras, on a side stream: sparse reduce-scatter of the rows whose gradient
-                  is final on this rank -- NCCL all-to-all-v straight out of the slot buffer (slots are in
-                  (last chunk, id) order, so a chunk is one owner-major slice) -> owner sums with 16-byte vector
-                  atomics -> rows whose last contribution this was leave by DMA into a packed pinned staging
-                  buffer + one flag -> the owner's host Adam updates them while later cameras render
+                  is final on this rank (slots are in (last chunk, id) order, so a chunk is one owner-major slice):
+                  "peer" (default) -- the rows are added straight into the owners' accumulators, which live in
+                  symmetric memory mapped by every rank, with 16-byte vector atomics over NVLink, then a signal per
+                  owner; "nccl" -- all-to-all-v, then the owner accumulates out of the receive buffer.  Rows whose
+                  last contribution this was leave by DMA into a packed pinned staging buffer + one flag -> the
+                  owner's host Adam updates them while later cameras render
                5. NCCL reduce-scatter of the dense gradients -> owner Adam on its slice (moments sharded) ->
                   all-gather of the updated slices
                6. join host Adam; barrier (the next step reads rows other ranks just updated)
