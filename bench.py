@@ -447,9 +447,10 @@ def run_ours(a):
                                "%s_offload (48-float SH rows + Adam state in pinned host memory), %s Adam"
                                % (spec.name, N, W, H, batch, a.strategy, "sparse" if sparse_adam else "dense"),
                                parallelism=("dp%d over cameras, %s: %d cameras per GPU, global batch %d per optimiser step%s; SH "
-                                            "rows + host Adam + the Adam moments of the GPU-resident attributes sharded by "
-                                            "Gaussian id; NCCL all-to-all-v (rows, gradients), reduce-scatter + all-gather "
-                                            "(GPU-resident attributes)"
+                                            "table node-shared in host memory (every GPU reads its rows over its own host "
+                                            "link); host Adam + the Adam moments of the GPU-resident attributes sharded by "
+                                            "Gaussian id; SH gradients: accumulate into the owner's HBM over NVLink (peer "
+                                            "memory, chunked); GPU-resident attributes: NCCL reduce-scatter + all-gather"
                                             % (world, "strong scaling" if strong else "weak scaling", bsz, global_batch,
                                                "" if strong else " (counted as %d iterations of %d)" % (world, bsz)))
                                if world > 1 else "1 GPU",
