@@ -124,45 +124,51 @@ group_hist_kernel(const uint8_t *__restrict__ key, int64_t N, int nkeys, int32_t
     if (threadIdx.x < nkeys) counts[(int64_t)threadIdx.x * gridDim.x + blockIdx.x] = s[threadIdx.x];
 }
 
-// exclusive scan over the flattened [nkeys][nblocks] counts (int64 out), group totals -> group_counts
+// Block k: exclusive scan of counts[k][0..nblocks) -> offsets[k][.] (relative to the group's start), the group's total
+// -> group_counts[k].  One block per key (a single block walking all nkeys x nblocks entries took 6.6 ms at 102 M
+// Gaussians, twice per step, at the head of the step where nothing else can run yet).
 __global__ void __launch_bounds__(1024)
 group_scan_kernel(const int32_t *__restrict__ counts, int64_t nblocks, int nkeys, int64_t *__restrict__ offsets,
                   int64_t *__restrict__ group_counts) {
     __shared__ int64_t s_warp[33];
     __shared__ int64_t s_carry;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int k = blockIdx.x;
     int64_t carry = 0;
-    for (int k = 0; k < nkeys; ++k) {
-        int64_t group_start = carry;
-        for (int64_t base = 0; base < nblocks; base += 1024) {
-            int64_t j = base + threadIdx.x;
-            int64_t v = j < nblocks ? counts[(int64_t)k * nblocks + j] : 0, incl = v;
+    for (int64_t base = 0; base < nblocks; base += 1024) {
+        int64_t j = base + threadIdx.x;
+        int64_t v = j < nblocks ? counts[(int64_t)k * nblocks + j] : 0, incl = v;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { int64_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-            if (lane == 31) s_warp[warp] = incl;
-            __syncthreads();
-            if (warp == 0) {
-                int64_t w = s_warp[lane], wi = w;
+        for (int o = 1; o < 32; o <<= 1) { int64_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int64_t w = s_warp[lane], wi = w;
 #pragma unroll
-                for (int o = 1; o < 32; o <<= 1) { int64_t t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
-                s_warp[lane] = wi - w;
-                if (lane == 31) s_carry = wi;
-            }
-            __syncthreads();
-            if (j < nblocks) offsets[(int64_t)k * nblocks + j] = carry + s_warp[warp] + incl - v;
-            carry += s_carry;
-            __syncthreads();
+            for (int o = 1; o < 32; o <<= 1) { int64_t t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+            s_warp[lane] = wi - w;
+            if (lane == 31) s_carry = wi;
         }
-        if (threadIdx.x == 0) group_counts[k] = carry - group_start;
+        __syncthreads();
+        if (j < nblocks) offsets[(int64_t)k * nblocks + j] = carry + s_warp[warp] + incl - v;
+        carry += s_carry;
+        __syncthreads();
     }
+    if (threadIdx.x == 0) group_counts[k] = carry;
 }
 
 __global__ void __launch_bounds__(kGB)
-group_scatter_kernel(const uint8_t *__restrict__ key, int64_t N, const int64_t *__restrict__ offsets,
-                     int32_t *__restrict__ out_ids) {
+group_scatter_kernel(const uint8_t *__restrict__ key, int64_t N, int nkeys, const int64_t *__restrict__ offsets,
+                     const int64_t *__restrict__ group_counts, int32_t *__restrict__ out_ids) {
     __shared__ int s_wcnt[kGB / 32][kKeys];  // per-warp counts per key
+    __shared__ int64_t s_base[kKeys];        // start of every group = prefix of the group totals
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int e = threadIdx.x; e < (kGB / 32) * kKeys; e += kGB) (&s_wcnt[0][0])[e] = 0;
+    if (threadIdx.x < nkeys) {
+        int64_t b = 0;
+        for (int q = 0; q < (int)threadIdx.x; ++q) b += group_counts[q];
+        s_base[threadIdx.x] = b;
+    }
     __syncthreads();
     int64_t i = (int64_t)blockIdx.x * kGB + threadIdx.x;
     int k = i < N ? key[i] : -1;
@@ -173,7 +179,7 @@ group_scatter_kernel(const uint8_t *__restrict__ key, int64_t N, const int64_t *
     if (k < 0) return;
     int before = 0;
     for (int w = 0; w < warp; ++w) before += s_wcnt[w][k];
-    out_ids[offsets[(int64_t)k * gridDim.x + blockIdx.x] + before + rank_in_warp] = (int32_t)i;
+    out_ids[s_base[k] + offsets[(int64_t)k * gridDim.x + blockIdx.x] + before + rank_in_warp] = (int32_t)i;
 }
 
 }  // namespace
@@ -280,9 +286,9 @@ CLMGS_EXPORT int clmgs_group_by_ffs(const uint8_t *ffs, int64_t N, int bsz, int3
     int32_t *counts = (int32_t *)((char *)scratch + ((size_t)nblocks * kKeys * sizeof(int64_t) + 255) / 256 * 256);
     group_hist_kernel<<<(unsigned)nblocks, kGB, 0, st>>>(ffs, N, nkeys, counts);
     CLMGS_LAUNCH_OK();
-    group_scan_kernel<<<1, 1024, 0, st>>>(counts, nblocks, nkeys, offsets, group_counts);
+    group_scan_kernel<<<nkeys, 1024, 0, st>>>(counts, nblocks, nkeys, offsets, group_counts);
     CLMGS_LAUNCH_OK();
-    group_scatter_kernel<<<(unsigned)nblocks, kGB, 0, st>>>(ffs, N, offsets, out_ids);
+    group_scatter_kernel<<<(unsigned)nblocks, kGB, 0, st>>>(ffs, N, nkeys, offsets, group_counts, out_ids);
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }

@@ -45,8 +45,18 @@ for n, s, e in comp:
     prev_end = e
     if n == "activate_bwd_scatter":
         k += 1
-print("copy streams around the same time:")
+print("per-stage statistics over the step (ms): n, total, min, median, p90, max")
+import collections
+by = collections.defaultdict(list)
+for n, s_, e_ in tl:
+    by[n].append(e_ - s_)
+for n, v in sorted(by.items(), key=lambda kv: -sum(kv[1])):
+    v = np.array(v)
+    print("   %-22s %4d %9.2f %8.3f %8.3f %8.3f %8.3f" % (n, len(v), v.sum(), v.min(), np.median(v), np.percentile(v, 90), v.max()))
+slow = sorted([(e_ - s_, n, s_) for n, s_, e_ in tl if n == "raster_fwd"], reverse=True)[:8]
+print("slowest raster_fwd instances (ms, start):", [(round(a, 2), round(c, 1)) for a, _, c in slow])
+print("copy streams:")
 lo = min(s for (n, s, e), kk in zip(comp, range(len(comp))))
 for n, s, e in tl:
     if n in ("rows_load_first", "rows_prefetch", "grad_handoff"):
-        print("   %-16s %9.2f -> %9.2f (%6.2f ms)" % (n, s, e, e - s)) if first * 12 <= s <= (first + ncam + 2) * 14 or True else None
+        print("   %-16s %9.2f -> %9.2f (%6.2f ms)" % (n, s, e, e - s))
