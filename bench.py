@@ -315,7 +315,7 @@ def run_ours(a):
     # ---- per-stage device times (separate pass: event pairs around every stage, raster work counters) -------
     timer = engine.StageTimer(True)
     nprof = min(a.steps, 3)
-    gm.raster_work_counters = torch.zeros(3, dtype=torch.int64, device=dev)
+    gm.raster_work_counters = torch.zeros(64, 3, dtype=torch.int64, device=dev)
     host_stats = []
 
     def step_profiled(b):
@@ -326,7 +326,7 @@ def run_ours(a):
 
     timed(step_profiled, a.warmup, nprof)
     stats = dict(gm.last_batch_stats)
-    stats["raster_work"] = [int(x) // nprof for x in gm.raster_work_counters.tolist()]
+    stats["raster_work"] = [int(x) // nprof for x in gm.raster_work_counters.sum(0).tolist()]
     gm.raster_work_counters = None
     stage_ms = {k: v / nprof for k, v in timer.totals.items()}
     stage_n = {k: v / nprof for k, v in timer.counts.items()}

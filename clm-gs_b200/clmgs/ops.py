@@ -276,8 +276,8 @@ def isect_offset_encode(isect_ids, n_cameras, tile_width, tile_height):
 # --------------------------------------------------------------------------- S5
 def rasterize_fwd(means2d, conics, colors, opacities, width, height, tile_size, isect_offsets,
                   flatten_ids, backgrounds=None, work_counters=None):
-    """work_counters: optional int64[3] device tensor that P_f / evaluated / P_b are ACCUMULATED into
-    (clmgs_rasterize_fwd_counted; measurement only)."""
+    """work_counters: optional int64 [64, 3] device tensor whose column sums P_f / evaluated / P_b are ACCUMULATED
+    into (clmgs_rasterize_fwd_counted; measurement only)."""
     means2d, conics, colors, opacities = map(_f32c, (means2d, conics, colors, opacities))
     dev = means2d.device
     C, th, tw = isect_offsets.shape
@@ -287,7 +287,7 @@ def rasterize_fwd(means2d, conics, colors, opacities, width, height, tile_size, 
     last = torch.empty(C, height, width, dtype=torch.int32, device=dev)
     bg = None if backgrounds is None else _f32c(backgrounds)
     if work_counters is not None:
-        assert work_counters.dtype == torch.int64 and work_counters.numel() >= 3
+        assert work_counters.dtype == torch.int64 and work_counters.numel() == 192 and work_counters.is_contiguous()
         call("clmgs_rasterize_fwd_counted", C, N, flatten_ids.shape[0], means2d, conics, colors, opacities, bg,
              int(width), int(height), int(tile_size), tw, th, isect_offsets.contiguous(),
              flatten_ids.contiguous(), rc, ra, last, work_counters, _st())

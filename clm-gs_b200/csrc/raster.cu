@@ -195,10 +195,12 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
             n_eval += __shfl_xor_sync(0xffffffffu, n_eval, o);
             n_back += __shfl_xor_sync(0xffffffffu, n_back, o);
         }
+        // 64 partial sums per counter, picked by tile: thousands of warps adding to three words would serialise
         if ((tr & 31) == 0) {
-            atomicAdd(counters + 0, (unsigned long long)n_examined);
-            atomicAdd(counters + 1, (unsigned long long)n_eval);
-            atomicAdd(counters + 2, (unsigned long long)n_back);
+            unsigned long long *c = counters + 3 * ((tile_id + (tr >> 5)) & 63);
+            atomicAdd(c + 0, (unsigned long long)n_examined);
+            atomicAdd(c + 1, (unsigned long long)n_eval);
+            atomicAdd(c + 2, (unsigned long long)n_back);
         }
     }
 }
@@ -237,8 +239,8 @@ CLMGS_EXPORT int clmgs_rasterize_fwd(int C, int64_t N, int64_t n_isects, const f
                               nullptr, stream);
 }
 
-// Same outputs, plus work_counters[3] (device, uint64, ACCUMULATED into: the caller zeroes them) -- see the COUNT
-// note on the kernel.  Measurement only.
+// Same outputs, plus work_counters[64][3] (device, uint64, ACCUMULATED into: the caller zeroes them; the three totals
+// are the column sums) -- see the COUNT note on the kernel.  Measurement only.
 CLMGS_EXPORT int clmgs_rasterize_fwd_counted(int C, int64_t N, int64_t n_isects, const float *means2d,
                                              const float *conics, const float *colors, const float *opacities,
                                              const float *backgrounds, int width, int height, int tile_size,

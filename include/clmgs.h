@@ -215,7 +215,8 @@ int clmgs_rasterize_fwd(int C, int64_t N, int64_t n_isects, const float *means2d
                         const int32_t *flatten_ids, float *render_colors, float *render_alphas,
                         int32_t *last_ids, void *stream);
 /* Measurement variant of clmgs_rasterize_fwd (no counterpart in the reference): same outputs, and
- * work_counters[3] (device int64, accumulated into -- zero them first) receive
+ * work_counters[64][3] (device int64, accumulated into -- zero them first; 64 partial sums per counter so that
+ * the adds do not serialise: sum over the first index) receive
  *   [0] P_f: list entries the reference forward examines per pixel, summed (27 P_f FLOP),
  *   [1] entries this kernel evaluated per pixel after its tile-touch pruning, summed,
  *   [2] P_b: last blended entry - tile start + 1 per pixel, summed (75 P_b FLOP for the backward). */

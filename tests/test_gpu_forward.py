@@ -150,11 +150,11 @@ def test_rasterize_fwd_vs_oracle(W, H, n, bg):
     rc, ra, last = ops.rasterize_fwd(_t(means2d), _t(conics), _t(colors), _t(opacs), W, H, 16, _t(off), _t(flat),
                                      None if bgs is None else _t(bgs))
     # measurement variant: identical outputs + the work counters of the FLOP roofline
-    wc = torch.zeros(3, dtype=torch.int64, device=rc.device)
+    wc = torch.zeros(64, 3, dtype=torch.int64, device=rc.device)
     rc2, ra2, last2 = ops.rasterize_fwd(_t(means2d), _t(conics), _t(colors), _t(opacs), W, H, 16, _t(off), _t(flat),
                                         None if bgs is None else _t(bgs), work_counters=wc)
     assert torch.equal(rc, rc2) and torch.equal(ra, ra2) and torch.equal(last, last2)
-    p_f, n_eval, p_b = wc.tolist()
+    p_f, n_eval, p_b = wc.sum(0).tolist()
     assert abs(p_f - examined_r) <= 1e-4 * examined_r, (p_f, examined_r)   # threshold flips only
     assert 0 < n_eval <= p_f
     tile = (np.arange(H)[:, None] // 16) * tw + (np.arange(W)[None, :] // 16)
