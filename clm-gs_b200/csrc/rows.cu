@@ -37,6 +37,11 @@ inline int env_int(const char *name, int dflt) {
 }
 // tunables (read once): CTAs of kernels that LOAD from host / STORE to host
 inline int host_load_ctas() { static int v = env_int("CLMGS_HOST_LOAD_CTAS", 48); return v; }
+// threads per CTA of the host-LOADING kernels: the same bytes in flight from fewer, fatter CTAs disturb fewer SMs
+inline int host_load_threads() {
+    static int v = [] { int t = env_int("CLMGS_HOST_LOAD_THREADS", 256); return t < 64 ? 64 : (t > 1024 ? 1024 : (t / 32) * 32); }();
+    return v;
+}
 inline int host_store_ctas() { static int v = env_int("CLMGS_HOST_STORE_CTAS", 64); return v; }
 inline unsigned grid_for(int64_t n_rows, bool store = false) {
     int64_t work = ceil_div64(n_rows * kRowF4, (int64_t)kThreads * kUnroll);
@@ -46,11 +51,11 @@ inline unsigned grid_for(int64_t n_rows, bool store = false) {
 
 // dst[dst_row(r)] = src[src_row(r)] for r in [0,n); row maps are functors.
 template <typename SrcMap, typename DstMap>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(1024)
 copy_rows_kernel(float4 *__restrict__ dst, const float4 *__restrict__ src, int64_t n, SrcMap smap, DstMap dmap) {
     const int64_t total = n * kRowF4;
-    const int64_t stride = (int64_t)gridDim.x * kThreads;
-    for (int64_t e0 = (int64_t)blockIdx.x * kThreads + threadIdx.x; e0 < total; e0 += stride * kUnroll) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;   // block size is a launch parameter (host_load_threads)
+    for (int64_t e0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e0 < total; e0 += stride * kUnroll) {
         float4 v[kUnroll];
         int64_t d[kUnroll];
 #pragma unroll
@@ -309,7 +314,7 @@ CLMGS_EXPORT int clmgs_rows_gather_i64(float *d_rows, const float *h_rows, const
     if (n == 0) return CLMGS_OK;
     if (int rc = check_align(d_rows, "d_rows")) return rc;
     if (int rc = check_align(h_rows, "h_rows")) return rc;
-    copy_rows_kernel<<<grid_for(n), kThreads, 0, as_stream(stream)>>>(F4(d_rows), CF4(h_rows), n, Map64{ids}, Identity{});
+    copy_rows_kernel<<<grid_for(n), host_load_threads(), 0, as_stream(stream)>>>(F4(d_rows), CF4(h_rows), n, Map64{ids}, Identity{});
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }
@@ -480,8 +485,8 @@ CLMGS_EXPORT int clmgs_rows_gather_to_slots(float *d_rows, const float *h_rows, 
     if (n == 0) return CLMGS_OK;
     if (int rc = check_align(d_rows, "d_rows")) return rc;
     if (int rc = check_align(h_rows, "h_rows")) return rc;
-    copy_rows_kernel<<<grid_for(n), kThreads, 0, as_stream(stream)>>>(F4(d_rows), CF4(h_rows), n, Map32{ids},
-                                                                     Map32Via{ids, slot_of});
+    copy_rows_kernel<<<grid_for(n), host_load_threads(), 0, as_stream(stream)>>>(F4(d_rows), CF4(h_rows), n, Map32{ids},
+                                                                                Map32Via{ids, slot_of});
     CLMGS_LAUNCH_OK();
     return CLMGS_OK;
 }
