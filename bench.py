@@ -189,7 +189,7 @@ def run_ours(a):
     spec = S.CONFIGS[a.config]
     N = a.n_gaussians or spec.n_gaussians
     batch = a.bsz or spec.batch                      # cameras per optimiser step of the named config
-    strong = world > 1 and batch % world == 0 and batch // world >= 4
+    strong = world > 1 and batch % world == 0 and batch // world >= 4 and a.scaling != "weak"
     bsz = batch // world if strong else batch        # cameras per GPU per step
     global_batch = bsz * world
     sparse_adam = a.sparse_adam if a.sparse_adam is not None else (a.config in SPARSE_BY_DEFAULT)
@@ -613,6 +613,9 @@ def main():
     ap.add_argument("--config", default=DEFAULT_CONFIG)
     ap.add_argument("--n-gaussians", type=int, default=0, help="override the config's Gaussian count (debug)")
     ap.add_argument("--bsz", type=int, default=0)
+    ap.add_argument("--scaling", default="auto", choices=["auto", "weak"],
+                    help="auto: fixed global batch split over the GPUs where >= 4 cameras per GPU remain (strong scaling, "
+                         "SURVEY 8d); weak: the config's batch PER GPU, one optimiser step over N x batch cameras")
     ap.add_argument("--sparse-adam", dest="sparse_adam", action="store_true", default=None)
     ap.add_argument("--dense-adam", dest="sparse_adam", action="store_false")
     ap.add_argument("--cpu-threads", type=int, default=0)
