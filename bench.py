@@ -470,6 +470,9 @@ def run_ours(a):
                    gpu_launches=launches, clocks=clk, roofline=roof, raster=raster, stages=stages,
                    peaks={k: v for k, v in pk.items()})
         out["config"]["hbm_allocated_gb"] = round(torch.cuda.max_memory_allocated() / 1e9, 2)
+        if "grad_exchange" in stats:
+            out["config"]["grad_exchange"] = stats["grad_exchange"]
+            out["config"]["grad_chunks"] = stats.get("grad_chunks")
         out["config"]["host_huge_pages"] = hostmem.huge_page_stats()
         if pipelined:
             out["pipelined"] = pipelined

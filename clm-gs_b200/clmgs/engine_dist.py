@@ -84,11 +84,23 @@ def training_setup_dist(gaussians, args, ctx):
         # Owner-side gradient accumulators in SYMMETRIC memory: every rank maps every rank's buffer, so a renderer
         # adds its gradient rows straight into the owner's HBM over NVLink (vector atomics) -- the sparse
         # reduce-scatter is ONE kernel per (chunk, owner) with no send / receive buffers and no collective call.
-        import torch.distributed._symmetric_memory as symm_mem
-        ctx.acc_sym = symm_mem.empty(S * 48, dtype=torch.float32, device=dev)
-        ctx.acc_sym.zero_()
-        ctx.symm = symm_mem.rendezvous(ctx.acc_sym, ctx.group if ctx.group is not None else dist.group.WORLD)
-        ctx.peer_acc = [ctx.symm.get_buffer(r, (S, 48), torch.float32) for r in range(G)]
+        ok, err = 1, None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            ctx.acc_sym = symm_mem.empty(S * 48, dtype=torch.float32, device=dev)
+            ctx.acc_sym.zero_()
+            symm = symm_mem.rendezvous(ctx.acc_sym, ctx.group if ctx.group is not None else dist.group.WORLD)
+            peer_acc = [symm.get_buffer(r, (S, 48), torch.float32) for r in range(G)]
+        except Exception as e:   # no peer access on this box / torch build without symmetric memory
+            ok, err = 0, e
+        flag = torch.tensor([ok], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=ctx.group)   # all ranks take the same path
+        if int(flag.item()) == 1:
+            ctx.symm, ctx.peer_acc = symm, peer_acc
+        else:
+            import warnings
+            warnings.warn("clmgs.engine_dist: symmetric memory is not available (%r); the SH gradients return through "
+                          "NCCL all-to-all-v instead of peer-memory accumulation" % (err,))
     ctx.table.register_cuda()
     gaussians.shared_parameters = ctx.table.tensor
     torch.cuda.synchronize()
@@ -205,6 +217,7 @@ def clm_offload_train_one_batch_dist(gaussians, scene, local_cameras, parameters
     gaussians.last_batch_stats = dict(n_visible=[f.shape[0] for f in filters], n_isects=out["n_isects"], n_union=n_need,
                                       n_first=int(fe[1]), n_owner_rows=n_uniq, n_adam_rows=n_uniq,
                                       rows_from_peers=plan.rows_from_peers, grad_chunks=K,
+                                      grad_exchange="peer" if ctx.symm is not None else "nccl",
                                       cpu_adam_trailing_ms=join_ms, **worker_times)
     return out["losses"], ordered, sparsity
 
