@@ -634,7 +634,7 @@ def main():
     ap.add_argument("--pipeline", action="store_true",
                     help="opt-in engine mode: defer the host-Adam join to the next call (reported in the extra "
                          "`pipelined` object; the headline keeps the reference's call contract)")
-    ap.add_argument("--cpu-sample-gaussians", type=int, default=4_000_000)
+    ap.add_argument("--cpu-sample-gaussians", type=int, default=8_000_000)
     a = ap.parse_args()
     a.warmup = max(a.warmup, 0)
     if a.other_configs is None:   # the default run (north-star config, 1 GPU) also carries configs[1] and configs[2]
