@@ -32,7 +32,22 @@ void clmgs_set_error(const char *fmt, ...);
 
 namespace {
 
-constexpr int kPrefetchRows = 6;  // rows of a sparse list are random 192-byte accesses: no hardware prefetcher helps
+// Rows of a sparse list are random 192-byte accesses: no hardware prefetcher helps.  Each row is requested
+// kPrefetchRows ahead of its use; CLMGS_CPU_ADAM_PREFETCH=<rows>[,<level>] overrides the distance and the cache level
+// the lines are requested into (0 = L1, 1 = L2) for tuning on another host.
+constexpr int kPrefetchRows = 6;
+struct PrefetchCfg { int rows, level; };
+inline PrefetchCfg prefetch_cfg() {
+    static const PrefetchCfg v = [] {
+        PrefetchCfg c{kPrefetchRows, 0};
+        if (const char *e = getenv("CLMGS_CPU_ADAM_PREFETCH")) {
+            c.rows = std::max(0, atoi(e));
+            if (const char *k = strchr(e, ',')) c.level = atoi(k + 1);
+        }
+        return c;
+    }();
+    return v;
+}
 
 struct AdamConst {
     float b1, b2, eps, scale, inv_bc1, bc2_rsqrt;
@@ -122,15 +137,25 @@ inline bool use_avx512() {
     __attribute__((target(TARGET))) void NAME(float *param, float *grad, float *exp_avg, float *exp_avg_sq,          \
                                               const float *col_lr, int cols, const int32_t *rows, int64_t a,         \
                                               int64_t b, int64_t packed_base, const AdamConst &c) {                  \
+        const PrefetchCfg pf = prefetch_cfg();                                                                       \
         for (int64_t r = a; r < b; ++r) {                                                                            \
             const int64_t base = (int64_t)(rows ? rows[r] : r) * cols;                                               \
-            if (rows && r + kPrefetchRows < b) { /* every 64-byte line of the row that comes up kPrefetchRows later */ \
-                const int64_t nb = (int64_t)rows[r + kPrefetchRows] * cols;                                          \
-                for (int l = 0; l < cols; l += 16) {                                                                 \
-                    _mm_prefetch((const char *)(param + nb + l), _MM_HINT_T0);                                       \
-                    if (GMODE == G_TABLE) _mm_prefetch((const char *)(grad + nb + l), _MM_HINT_T0);                  \
-                    _mm_prefetch((const char *)(exp_avg + nb + l), _MM_HINT_T0);                                     \
-                    _mm_prefetch((const char *)(exp_avg_sq + nb + l), _MM_HINT_T0);                                  \
+            if (rows && pf.rows && r + pf.rows < b) { /* every 64-byte line of the row that comes up pf.rows later */ \
+                const int64_t nb = (int64_t)rows[r + pf.rows] * cols;                                                \
+                if (pf.level == 0) {                                                                                 \
+                    for (int l = 0; l < cols; l += 16) {                                                             \
+                        _mm_prefetch((const char *)(param + nb + l), _MM_HINT_T0);                                   \
+                        if (GMODE == G_TABLE) _mm_prefetch((const char *)(grad + nb + l), _MM_HINT_T0);              \
+                        _mm_prefetch((const char *)(exp_avg + nb + l), _MM_HINT_T0);                                 \
+                        _mm_prefetch((const char *)(exp_avg_sq + nb + l), _MM_HINT_T0);                              \
+                    }                                                                                                \
+                } else {                                                                                             \
+                    for (int l = 0; l < cols; l += 16) {                                                             \
+                        _mm_prefetch((const char *)(param + nb + l), _MM_HINT_T1);                                   \
+                        if (GMODE == G_TABLE) _mm_prefetch((const char *)(grad + nb + l), _MM_HINT_T1);              \
+                        _mm_prefetch((const char *)(exp_avg + nb + l), _MM_HINT_T1);                                 \
+                        _mm_prefetch((const char *)(exp_avg_sq + nb + l), _MM_HINT_T1);                              \
+                    }                                                                                                \
                 }                                                                                                    \
             }                                                                                                        \
             float *g = GMODE == G_PACKED ? grad + (r - packed_base) * cols : grad + base;                            \
