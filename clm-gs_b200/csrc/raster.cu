@@ -26,6 +26,11 @@
 
 constexpr int kTile = 16;
 constexpr int kBlock = kTile * kTile;
+// resident CTAs per SM the forward kernel is compiled for: 5 = 48 registers (4 would give 54 registers and a
+// slightly shorter loop; tools/raster_variants.sh builds and times both)
+#ifndef CLMGS_RASTER_FWD_MIN_BLOCKS
+#define CLMGS_RASTER_FWD_MIN_BLOCKS 5
+#endif
 
 struct RasterArgs {
     int C;
@@ -102,7 +107,7 @@ __device__ __forceinline__ int stage_compact(bool keep, int tr, int *s_wcnt, int
 //   [1] entries this kernel actually evaluated per pixel (after tile-touch pruning and row skipping)
 //   [2] P_b = sum over pixels of (last blended entry - tile start + 1): what the reference backward walks
 template <bool HAS_BG, bool COUNT>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, CLMGS_RASTER_FWD_MIN_BLOCKS)
 raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float *__restrict__ conics,
                   const float *__restrict__ colors, const float *__restrict__ opacities,
                   const float *__restrict__ backgrounds, const int32_t *__restrict__ tile_offsets,
@@ -154,11 +159,13 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
         const int batch_size = stage_compact(keep, tr, s_wcnt, slot);
         if (keep) { s_a[slot] = A; s_b[slot] = Bv; s_c[slot] = Cv; }
         __syncthreads();
-        for (int t = 0; t < batch_size && !done; ++t) {
-            const float4 Cc = s_c[t];
+        if (done) continue;
+        const float4 *pa = s_a, *pb = s_b, *pc = s_c;
+        for (int t = batch_size; t > 0; --t, ++pa, ++pb, ++pc) {
+            const float4 Cc = *pc;
             if (wy1 < Cc.y || wy0 > Cc.z) continue;  // cannot reach 1/255 on this warp's rows (warp-uniform)
-            const float4 A = s_a[t];
-            const float4 Bv = s_b[t];
+            const float4 A = *pa;
+            const float4 Bv = *pb;
             const float dx = A.x - px, dy = A.y - py;
             const float sigma = 0.5f * (A.z * dx * dx + Bv.x * dy * dy) + A.w * dx * dy;
             const float alpha = fminf(0.999f, Bv.y * __expf(-sigma));
@@ -327,7 +334,7 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
     const int64_t pix = inside ? ((int64_t)cam * a.height + i) * a.width + j : 0;
     const float T_final = inside ? 1.0f - render_alphas[pix] : 1.0f;
     float T = T_final;
-    float buf_r = 0.f, buf_g = 0.f, buf_b = 0.f;
+    float buf_v = 0.f;  // sum over the entries behind the current one of (colour . v_render) * alpha * T
     const int bin_final = inside ? last_ids[pix] : 0;
     float vr = 0.f, vg = 0.f, vb = 0.f, va = 0.f;
     if (inside) {
@@ -339,6 +346,7 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
         const float *bg = backgrounds + 3 * cam;
         bg_dot = bg[0] * vr + bg[1] * vg + bg[2] * vb;
     }
+    const float tf_va = T_final * (va - bg_dot);
     int warp_bin_final = bin_final;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) warp_bin_final = max(warp_bin_final, __shfl_xor_sync(0xffffffffu, warp_bin_final, o));
@@ -356,6 +364,24 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
     const float txmin = (float)(blockIdx.x * kTile) + 0.5f, txmax = (float)min(blockIdx.x * kTile + kTile - 1, a.width - 1) + 0.5f;
     const float tymin = (float)(blockIdx.y * kTile) + 0.5f, tymax = (float)min(blockIdx.y * kTile + kTile - 1, a.height - 1) + 0.5f;
     const float wy0 = (float)(blockIdx.y * kTile + 2 * (tr >> 5)) + 0.5f, wy1 = wy0 + 1.0f;
+
+    // Where this lane's warp sum goes (per-warp atomics, !TILE_ACC): after the butterfly, lanes 0,4,..,28 hold the
+    // eight sums (rgb, conic xyz, mean xy), lane 1 the opacity sum (, lanes 2 / 3 the |mean| sums); element of
+    // Gaussian g = lane_dst[g * lane_stride].  Fixed per lane, so the inner loop needs no address selection.
+    float *lane_dst = nullptr;
+    unsigned lane_stride = 0;
+    if (!TILE_ACC) {
+        const int k = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+        if ((lane & 3) == 0) {
+            if (k < 3) { lane_dst = v_colors + k; lane_stride = 3; }
+            else if (k < 6) { lane_dst = v_conics + (k - 3); lane_stride = 3; }
+            else { lane_dst = v_means2d + (k - 6); lane_stride = 2; }
+        } else if (lane == 1) {
+            lane_dst = v_opacities; lane_stride = 1;
+        } else if (ABSGRAD && (lane == 2 || lane == 3)) {
+            lane_dst = v_means2d_abs + (lane - 2); lane_stride = 2;
+        }
+    }
 
     for (int bt = first_batch; bt < num_batches; ++bt) {
         __syncthreads();
@@ -389,72 +415,62 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
             const float4 Cc = s_c[tc];
             const int t = __float_as_int(Cc.w);  // position in the (uncompacted) batch
             if (t < t_lo || wy1 < Cc.y || wy0 > Cc.z) continue;  // warp-uniform
-            bool valid = inside && (batch_end - t <= bin_final);
-            float alpha = 0.f, opac = 0.f, vis = 0.f, dx = 0.f, dy = 0.f;
-            float4 A, Bv;
-            if (valid) {
-                A = s_a[tc]; Bv = s_b[tc];
-                opac = Bv.y;
-                dx = A.x - px; dy = A.y - py;
-                const float sigma = 0.5f * (A.z * dx * dx + Bv.x * dy * dy) + A.w * dx * dy;
-                vis = __expf(-sigma);
-                alpha = fminf(0.999f, opac * vis);
-                if (sigma < 0.f || alpha < 1.f / 255.f) valid = false;
-            }
+            // Branch-free from here: every lane evaluates the Gaussian; a lane that does not blend it (outside the
+            // image, behind its last entry, sigma < 0, alpha < 1/255) carries alpha = vis = 0, which makes each of its
+            // terms below exactly zero and leaves its running state untouched.
+            const float4 A = s_a[tc], Bv = s_b[tc];
+            const float opac = Bv.y;
+            const float dx = A.x - px, dy = A.y - py;
+            const float sigma = 0.5f * (A.z * dx * dx + Bv.x * dy * dy) + A.w * dx * dy;
+            float vis = __expf(-sigma);
+            float alpha = fminf(0.999f, opac * vis);
+            const bool valid = inside && (batch_end - t <= bin_final) && !(sigma < 0.f || alpha < 1.f / 255.f);
             if (!__any_sync(0xffffffffu, valid)) continue;
-            float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // rgb, conic xyz, xy
-            float v_opa = 0.f, v_ax = 0.f, v_ay = 0.f;
-            if (valid) {
-                const float cb = Cc.x;
-                const float ra = 1.0f / (1.0f - alpha);
-                T *= ra;
-                const float fac = alpha * T;
-                v[0] = fac * vr; v[1] = fac * vg; v[2] = fac * vb;
-                float v_alpha = (Bv.z * T - buf_r * ra) * vr + (Bv.w * T - buf_g * ra) * vg + (cb * T - buf_b * ra) * vb;
-                v_alpha += T_final * ra * va;
-                if (HAS_BG) v_alpha += -T_final * ra * bg_dot;
-                if (opac * vis <= 0.999f) {
-                    const float v_sigma = -opac * vis * v_alpha;
-                    v[3] = 0.5f * v_sigma * dx * dx;
-                    v[4] = v_sigma * dx * dy;
-                    v[5] = 0.5f * v_sigma * dy * dy;
-                    v[6] = v_sigma * (A.z * dx + A.w * dy);
-                    v[7] = v_sigma * (A.w * dx + Bv.x * dy);
-                    if (ABSGRAD) { v_ax = fabsf(v[6]); v_ay = fabsf(v[7]); }
-                    v_opa = vis * v_alpha;
-                }
-                buf_r += Bv.z * fac; buf_g += Bv.w * fac; buf_b += cb * fac;
+            if (!valid) { alpha = 0.f; vis = 0.f; }
+            const float ra = 1.0f / (1.0f - alpha);
+            if (valid) T *= ra;
+            const float fac = alpha * T;
+            // sum_c (c_c T - buf_c ra) v_c + T_final ra (v_a - bg . v)  with  buf . v  kept as ONE running scalar
+            const float cv = Bv.z * vr + Bv.w * vg + Cc.x * vb;
+            const float v_alpha = T * cv + ra * (tf_va - buf_v);
+            buf_v += cv * fac;
+            const float v_opa_px = (opac * vis <= 0.999f) ? vis * v_alpha : 0.f;  // alpha clamped: no gradient through it
+            const float v_sigma = -opac * v_opa_px;
+            float v[8];  // rgb, then conic xyz + mean xy (TILE_ACC: their raw moments, combined once per tile at the flush)
+            v[0] = fac * vr; v[1] = fac * vg; v[2] = fac * vb;
+            const float sx = v_sigma * dx, sy = v_sigma * dy;
+            float v_ax = 0.f, v_ay = 0.f;
+            if (TILE_ACC) {
+                v[3] = sx * dx; v[4] = sx * dy; v[5] = sy * dy; v[6] = sx; v[7] = sy;
+                if (ABSGRAD) { v_ax = fabsf(A.z * sx + A.w * sy); v_ay = fabsf(A.w * sx + Bv.x * sy); }
+            } else {
+                v[3] = 0.5f * sx * dx; v[4] = sx * dy; v[5] = 0.5f * sy * dy;
+                v[6] = A.z * sx + A.w * sy; v[7] = A.w * sx + Bv.x * sy;
+                if (ABSGRAD) { v_ax = fabsf(v[6]); v_ay = fabsf(v[7]); }
             }
             const float red = butterfly8(v, lane);
-            v_opa = warp_sum(v_opa);
+            const float v_opa = warp_sum(v_opa_px);
             if (ABSGRAD) { v_ax = warp_sum(v_ax); v_ay = warp_sum(v_ay); }
             if (TILE_ACC) {
-                // value q of staged Gaussian tc lives at s_acc[q * kBlock + tc]
-                if ((lane & 3) == 0) {
-                    const int k = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-                    atomicAdd(&s_acc[k * kBlock + tc], red);
-                } else if (lane == 1) {
-                    atomicAdd(&s_acc[8 * kBlock + tc], v_opa);
-                    s_hit[tc] = 1;
-                } else if (ABSGRAD && lane == 2) {
-                    atomicAdd(&s_acc[9 * kBlock + tc], v_ax);
-                } else if (ABSGRAD && lane == 3) {
-                    atomicAdd(&s_acc[10 * kBlock + tc], v_ay);
-                }
+                // value q of staged Gaussian tc lives at s_acc[q * kBlock + tc].  Lanes 0,4,..,28 hold the eight
+                // butterfly sums, lane 1 the opacity sum (, lanes 2 / 3 the |mean| sums): ONE shared atomic for all of
+                // them (a float atomic on shared memory is a compare-and-swap loop; one loop, not one per lane group)
+                int q = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+                float val = red;
+                bool part = (lane & 3) == 0;
+                if (lane == 1) { q = 8; val = v_opa; part = true; }
+                if (ABSGRAD && lane == 2) { q = 9; val = v_ax; part = true; }
+                if (ABSGRAD && lane == 3) { q = 10; val = v_ay; part = true; }
+                if (part) atomicAdd(&s_acc[q * kBlock + tc], val);
+                if (lane == 1) s_hit[tc] = 1;
                 continue;
             }
-            const int64_t gid = s_id[tc];
-            if ((lane & 3) == 0) {
-                const int k = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-                float *dst = k < 3 ? v_colors + 3 * gid + k : (k < 6 ? v_conics + 3 * gid + (k - 3) : v_means2d + 2 * gid + (k - 6));
-                atomicAdd(dst, red);
-            } else if (lane == 1) {
-                atomicAdd(v_opacities + gid, v_opa);
-            } else if (ABSGRAD && lane == 2) {
-                atomicAdd(v_means2d_abs + 2 * gid, v_ax);
-            } else if (ABSGRAD && lane == 3) {
-                atomicAdd(v_means2d_abs + 2 * gid + 1, v_ay);
-            }
+            // one reduction instruction for the whole warp: every participating lane adds its sum to its own array
+            float val = red;
+            if (lane == 1) val = v_opa;
+            if (ABSGRAD && lane == 2) val = v_ax;
+            if (ABSGRAD && lane == 3) val = v_ay;
+            if (lane_dst) atomicAdd(lane_dst + (unsigned)s_id[tc] * lane_stride, val);  // 32-bit index: N < 2^32 / 3 (checked)
         }
         if (TILE_ACC) {
             __syncthreads();  // every warp's contribution to this batch is in s_acc
@@ -463,11 +479,14 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
                 atomicAdd(v_colors + 3 * gid, s_acc[0 * kBlock + tr]);
                 atomicAdd(v_colors + 3 * gid + 1, s_acc[1 * kBlock + tr]);
                 atomicAdd(v_colors + 3 * gid + 2, s_acc[2 * kBlock + tr]);
-                atomicAdd(v_conics + 3 * gid, s_acc[3 * kBlock + tr]);
+                // moments of v_sigma over the tile -> conic and mean gradients (conic a, b, c of staged Gaussian tr)
+                const float ca = s_a[tr].z, cb = s_a[tr].w, cc = s_b[tr].x;
+                const float m_x = s_acc[6 * kBlock + tr], m_y = s_acc[7 * kBlock + tr];
+                atomicAdd(v_conics + 3 * gid, 0.5f * s_acc[3 * kBlock + tr]);
                 atomicAdd(v_conics + 3 * gid + 1, s_acc[4 * kBlock + tr]);
-                atomicAdd(v_conics + 3 * gid + 2, s_acc[5 * kBlock + tr]);
-                atomicAdd(v_means2d + 2 * gid, s_acc[6 * kBlock + tr]);
-                atomicAdd(v_means2d + 2 * gid + 1, s_acc[7 * kBlock + tr]);
+                atomicAdd(v_conics + 3 * gid + 2, 0.5f * s_acc[5 * kBlock + tr]);
+                atomicAdd(v_means2d + 2 * gid, ca * m_x + cb * m_y);
+                atomicAdd(v_means2d + 2 * gid + 1, cb * m_x + cc * m_y);
                 atomicAdd(v_opacities + gid, s_acc[8 * kBlock + tr]);
                 if (ABSGRAD) {
                     atomicAdd(v_means2d_abs + 2 * gid, s_acc[9 * kBlock + tr]);
@@ -489,12 +508,14 @@ CLMGS_EXPORT int clmgs_rasterize_bwd(int C, int64_t N, int64_t n_isects, const f
     CLMGS_REQUIRE(tile_size == kTile, "rasterize: tile_size must be 16 (got %d)", tile_size);
     CLMGS_REQUIRE(tile_width * kTile >= width && tile_height * kTile >= height,
                   "rasterize: tile grid %dx%d does not cover %dx%d", tile_width, tile_height, width, height);
+    CLMGS_REQUIRE((int64_t)C * N < ((int64_t)1 << 32) / 3, "rasterize_bwd: C * N too large for 32-bit element indices");
     if (C == 0 || width == 0 || height == 0 || n_isects == 0) return CLMGS_OK;
     RasterArgs a{C, N, n_isects, width, height, tile_width, tile_height};
     dim3 grid(tile_width, tile_height, C), block(kTile, kTile, 1);
     cudaStream_t st = as_stream(stream);
-    // CLMGS_RASTER_BWD_TILE_ACC=0 selects the per-warp global atomics (kept for A/B measurements)
-    static const bool tile_acc = [] { const char *e = getenv("CLMGS_RASTER_BWD_TILE_ACC"); return !(e && e[0] == '0'); }();
+    // CLMGS_RASTER_BWD_TILE_ACC=1 selects the per-tile accumulation in shared memory (kept for A/B measurements:
+    // on B200 it is 10 % slower than the per-warp global reductions)
+    static const bool tile_acc = [] { const char *e = getenv("CLMGS_RASTER_BWD_TILE_ACC"); return e && e[0] == '1'; }();
 #define LAUNCH(BG, AB, TA)                                                                                          \
     raster_bwd_kernel<BG, AB, TA><<<grid, block, 0, st>>>(a, (const float2 *)means2d, conics, colors, opacities,     \
                                                           backgrounds, tile_offsets, flatten_ids, render_alphas,     \
