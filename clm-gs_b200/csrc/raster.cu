@@ -114,9 +114,9 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
                   const int32_t *__restrict__ flatten_ids, float *__restrict__ render_colors,
                   float *__restrict__ render_alphas, int32_t *__restrict__ last_ids,
                   unsigned long long *__restrict__ counters) {
-    __shared__ float4 s_a[kBlock];  // x, y, conic.x, conic.y
-    __shared__ float4 s_b[kBlock];  // conic.z, opacity, r, g
-    __shared__ float4 s_c[kBlock];  // b, first row, last row (pixel-centre y), position in the batch
+    // one staged Gaussian = 3 consecutive float4 (one pointer walks the batch):
+    //   [0] x, y, conic.x, conic.y   [1] conic.z, opacity, r, g   [2] b, first row, last row (pixel-centre y), position in the batch
+    __shared__ float4 s_g[3 * kBlock];
     __shared__ int s_wcnt[kBlock / 32];
     const int cam = blockIdx.z;
     const int tile_id = blockIdx.y * a.tile_width + blockIdx.x;
@@ -157,15 +157,15 @@ raster_fwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
         }
         int slot;
         const int batch_size = stage_compact(keep, tr, s_wcnt, slot);
-        if (keep) { s_a[slot] = A; s_b[slot] = Bv; s_c[slot] = Cv; }
+        if (keep) { float4 *d = s_g + 3 * slot; d[0] = A; d[1] = Bv; d[2] = Cv; }
         __syncthreads();
         if (done) continue;
-        const float4 *pa = s_a, *pb = s_b, *pc = s_c;
-        for (int t = batch_size; t > 0; --t, ++pa, ++pb, ++pc) {
-            const float4 Cc = *pc;
+        const float4 *pg = s_g;
+        for (int t = batch_size; t > 0; --t, pg += 3) {
+            const float4 Cc = pg[2];
             if (wy1 < Cc.y || wy0 > Cc.z) continue;  // cannot reach 1/255 on this warp's rows (warp-uniform)
-            const float4 A = *pa;
-            const float4 Bv = *pb;
+            const float4 A = pg[0];
+            const float4 Bv = pg[1];
             const float dx = A.x - px, dy = A.y - py;
             const float sigma = 0.5f * (A.z * dx * dx + Bv.x * dy * dy) + A.w * dx * dy;
             const float alpha = fminf(0.999f, Bv.y * __expf(-sigma));
@@ -311,10 +311,10 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
                   const float *__restrict__ v_render_alphas, float *__restrict__ v_means2d_abs,
                   float *__restrict__ v_means2d, float *__restrict__ v_conics, float *__restrict__ v_colors,
                   float *__restrict__ v_opacities) {
-    __shared__ int s_id[kBlock];
-    __shared__ float4 s_a[kBlock];  // x, y, conic.x, conic.y
-    __shared__ float4 s_b[kBlock];  // conic.z, opacity, r, g
-    __shared__ float4 s_c[kBlock];  // b, first row, last row (pixel-centre y), position in the batch
+    // one staged Gaussian = 4 consecutive float4 (one pointer walks the batch):
+    //   [0] x, y, conic.x, conic.y   [1] conic.z, opacity, r, g   [2] b, first row, last row (pixel-centre y), position in the batch
+    //   [3] .x = Gaussian id (int bits)
+    __shared__ float4 s_g[4 * kBlock];
     __shared__ int s_wcnt[kBlock / 32];
     constexpr int kAcc = ABSGRAD ? 11 : 9;  // rgb, conic xyz, mean xy, opacity (, |mean| xy)
     __shared__ float s_acc[TILE_ACC ? kBlock * kAcc : 1];
@@ -403,7 +403,7 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
         }
         int slot;
         const int batch_size = stage_compact(keep, tr, s_wcnt, slot);
-        if (keep) { s_id[slot] = gid_s; s_a[slot] = sA; s_b[slot] = sB; s_c[slot] = sC; }
+        if (keep) { float4 *d = s_g + 4 * slot; d[0] = sA; d[1] = sB; d[2] = sC; d[3].x = __int_as_float(gid_s); }
         if (TILE_ACC) {
 #pragma unroll
             for (int q = 0; q < kAcc; ++q) s_acc[q * kBlock + tr] = 0.f;
@@ -411,14 +411,15 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
         }
         __syncthreads();
         const int t_lo = batch_end - warp_bin_final;  // entries with a smaller position are behind every pixel's last
-        for (int tc = 0; tc < batch_size; ++tc) {
-            const float4 Cc = s_c[tc];
+        const float4 *pg = s_g;
+        for (int tc = 0; tc < batch_size; ++tc, pg += 4) {
+            const float4 Cc = pg[2];
             const int t = __float_as_int(Cc.w);  // position in the (uncompacted) batch
             if (t < t_lo || wy1 < Cc.y || wy0 > Cc.z) continue;  // warp-uniform
             // Branch-free from here: every lane evaluates the Gaussian; a lane that does not blend it (outside the
             // image, behind its last entry, sigma < 0, alpha < 1/255) carries alpha = vis = 0, which makes each of its
             // terms below exactly zero and leaves its running state untouched.
-            const float4 A = s_a[tc], Bv = s_b[tc];
+            const float4 A = pg[0], Bv = pg[1];
             const float opac = Bv.y;
             const float dx = A.x - px, dy = A.y - py;
             const float sigma = 0.5f * (A.z * dx * dx + Bv.x * dy * dy) + A.w * dx * dy;
@@ -470,17 +471,17 @@ raster_bwd_kernel(RasterArgs a, const float2 *__restrict__ means2d, const float 
             if (lane == 1) val = v_opa;
             if (ABSGRAD && lane == 2) val = v_ax;
             if (ABSGRAD && lane == 3) val = v_ay;
-            if (lane_dst) atomicAdd(lane_dst + (unsigned)s_id[tc] * lane_stride, val);  // 32-bit index: N < 2^32 / 3 (checked)
+            if (lane_dst) atomicAdd(lane_dst + (unsigned)__float_as_int(pg[3].x) * lane_stride, val);  // 32-bit index: N < 2^32 / 3 (checked)
         }
         if (TILE_ACC) {
             __syncthreads();  // every warp's contribution to this batch is in s_acc
             if (tr < batch_size && s_hit[tr]) {
-                const int64_t gid = s_id[tr];
+                const int64_t gid = __float_as_int(s_g[4 * tr + 3].x);
                 atomicAdd(v_colors + 3 * gid, s_acc[0 * kBlock + tr]);
                 atomicAdd(v_colors + 3 * gid + 1, s_acc[1 * kBlock + tr]);
                 atomicAdd(v_colors + 3 * gid + 2, s_acc[2 * kBlock + tr]);
                 // moments of v_sigma over the tile -> conic and mean gradients (conic a, b, c of staged Gaussian tr)
-                const float ca = s_a[tr].z, cb = s_a[tr].w, cc = s_b[tr].x;
+                const float ca = s_g[4 * tr].z, cb = s_g[4 * tr].w, cc = s_g[4 * tr + 1].x;
                 const float m_x = s_acc[6 * kBlock + tr], m_y = s_acc[7 * kBlock + tr];
                 atomicAdd(v_conics + 3 * gid, 0.5f * s_acc[3 * kBlock + tr]);
                 atomicAdd(v_conics + 3 * gid + 1, s_acc[4 * kBlock + tr]);

@@ -1,5 +1,5 @@
 """Rasterise fwd / bwd alone on one camera of a named config (kernel time, CUDA events, 10 repetitions).
-   CLMGS_RASTER_BWD_TILE_ACC=0|1 python tools/raster_bench.py [config] [n_gaussians]"""
+   CLMGS_RASTER_BWD_TILE_ACC=0|1 python tools/raster_bench.py [config] [n_gaussians]   (0, the default: per-warp global reductions)"""
 import json, math, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "clm-gs_b200")]
@@ -34,7 +34,7 @@ def timeit(fn, reps=10):
     return s.elapsed_time(e) / reps
 # pre-allocated outputs are not possible through ops (it zero-fills per call): subtract the zero-fill separately
 zf = timeit(lambda: [torch.zeros_like(m2), torch.zeros_like(con), torch.zeros_like(col), torch.zeros_like(opac)])
-out = dict(config=cfg, n_visible=int(ids.shape[0]), n_isects=int(n_is), tile_acc=os.environ.get("CLMGS_RASTER_BWD_TILE_ACC", "1"),
+out = dict(config=cfg, n_visible=int(ids.shape[0]), n_isects=int(n_is), tile_acc=os.environ.get("CLMGS_RASTER_BWD_TILE_ACC", "0"),
            fwd_ms=round(timeit(lambda: ops.rasterize_fwd(m2, con, col, opac, W, H, 16, off, flat)), 4),
            bwd_ms_incl_zero_fill=round(timeit(lambda: ops.rasterize_bwd(m2, con, col, opac, W, H, 16, off, flat, ra, last, v, None)), 4),
            zero_fill_ms=round(zf, 4),

@@ -11,7 +11,10 @@ for cfg in c2_bicycle_6m c4_bigcity_102m c3_rubble4k_28m; do
   python tools/raster_bench.py $cfg; CLMGS_RASTER_BWD_TILE_ACC=1 python tools/raster_bench.py $cfg
 done > gpurun_out/raster_ab2.jsonl 2>&1
 cut -c1-230 gpurun_out/raster_ab2.jsonl
-ncu --set full --clock-control none --import-source on -k regex:raster_ -c 6 -o /tmp/raster_prof python tools/raster_bench.py c2_bicycle_6m \
+ncu --set full --clock-control none --import-source on -k regex:raster_bwd -c 2 -o /tmp/raster_prof python tools/raster_bench.py c2_bicycle_6m \
   > gpurun_out/ncu_raster.log 2>&1
 ncu -i /tmp/raster_prof.ncu-rep --page raw --csv > gpurun_out/raster_prof_raw.csv 2>/dev/null
+ncu --set full --clock-control none --import-source on -k regex:raster_fwd -c 2 -o /tmp/raster_prof_f python tools/raster_bench.py c2_bicycle_6m \
+  >> gpurun_out/ncu_raster.log 2>&1
+ncu -i /tmp/raster_prof_f.ncu-rep --page raw --csv > gpurun_out/raster_fwd_prof_raw.csv 2>/dev/null
 ls -la gpurun_out/raster_prof_raw.csv

@@ -17,6 +17,6 @@ else
   done
   for cfg in c2_bicycle_6m c4_bigcity_102m; do
     echo "== $cfg forward compiled for 4 CTAs/SM"; CLMGS_LIB_PATH=$PWD/$V/libclmgs_fwd4.so python tools/raster_bench.py $cfg
-    echo "== $cfg per-warp global atomics in the backward"; CLMGS_RASTER_BWD_TILE_ACC=0 python tools/raster_bench.py $cfg
+    echo "== $cfg per-tile shared-memory accumulation in the backward"; CLMGS_RASTER_BWD_TILE_ACC=1 python tools/raster_bench.py $cfg
   done
 fi
