@@ -17,7 +17,7 @@
 //    ballot compaction in shared memory) and the survivors carry the image rows they can touch, which lets
 //    each warp (2 rows) skip the rest with one compare.  The test is conservative (tolerances cover the
 //    rounding of the per-pixel evaluation), so images, last_ids and gradients are unchanged;
-//  * backward: the 9 per-Gaussian partial gradients of a warp are reduced with
+//  * backward: branch-free inner loop, the 9 per-Gaussian partial gradients of a warp are reduced with
 //    a multi-value butterfly (14 shuffles instead of 45) and the 8 finished
 //    sums are added by 8 different lanes in parallel.
 #include "common.cuh"
