@@ -4,6 +4,7 @@
 // bit-exact against the oracle.
 #include "common.cuh"
 #include "gs_math.cuh"
+#include <stdlib.h>
 
 using namespace gsm;
 
@@ -56,38 +57,67 @@ __device__ __forceinline__ void load_gaussian(const float *means, const float *s
     if (smax2) { float m = fmaxf(fmaxf(fabsf(s[0]), fabsf(s[1])), fabsf(s[2])); *smax2 = m * m; }
 }
 
-// Cheap sufficient condition for project_one<true>() == false, evaluated before the covariance is carried
-// into the camera frame (most (camera, Gaussian) pairs of a large scene fail here: ~98 % at C4).  It rejects only
-// what the full test rejects: behind / beyond the planes (the same comparison on the same depth), or the disc
-// test with an upper bound R on the radius.  lambda_max(J cov_c J^T + eps I) <= |J|_F^2 smax^2 + eps, the packed
-// radius rule uses at most lambda_max + sqrt(0.1), radius = ceil(3 sqrt(.)) <= 3 sqrt(.) + 1; 2 % slack covers
-// rounding (the view rotation is assumed rigid up to a uniform scale).  mean2d is computed with the operations of project_one, so "mean2d + R <= 0" implies the full
-// test's "mean2d + radius <= 0".  Non-finite values fall through to the full test.
-__device__ __forceinline__ bool surely_culled(const float mean[3], float smax2, const Camera &cam, float lim_x,
-                                              float lim_y, float rs, int width, int height, float eps2d,
-                                              float near_plane, float far_plane) {
-    const float *R = cam.R;
-    float mc[3];
-#pragma unroll
-    for (int r = 0; r < 3; ++r)
-        mc[r] = ((R[r * 3 + 0] * mean[0] + R[r * 3 + 1] * mean[1]) + R[r * 3 + 2] * mean[2]) + cam.t[r];
-    if (mc[2] < near_plane || mc[2] > far_plane) return true;
-    const float fx = cam.fx, fy = cam.fy, x = mc[0], y = mc[1], z = mc[2];
-    const float rz = 1.f / z, rz2 = rz * rz;
-    const float tx = z * fminf(lim_x, fmaxf(-lim_x, x * rz));
-    const float ty = z * fminf(lim_y, fmaxf(-lim_y, y * rz));
-    const float J00 = fx * rz, J11 = fy * rz, J02 = (-fx * tx) * rz2, J12 = (-fy * ty) * rz2;
-    const float jf2 = (J00 * J00 + J11 * J11) + (J02 * J02 + J12 * J12);
-    // rs: world->camera rotation taken as a similarity (|R|_F^2 / 3 = its squared scale, 1 for a rigid camera)
-    const float Rb = 3.06f * sqrtf(jf2 * (smax2 * rs) + eps2d + 0.32f) + 1.02f;
-    const float mx = (fx * x) * rz + cam.cx, my = (fy * y) * rz + cam.cy;
-    if (!(Rb < 1e30f)) return false;
-    return mx + Rb <= 0.f || mx - Rb >= (float)width || my + Rb <= 0.f || my - Rb >= (float)height;
+// Cheap sufficient condition for project_one<true>() == false, evaluated before the covariance is carried into the
+// camera frame (most (camera, Gaussian) pairs of a large scene fail here: ~98 % at C4).  It only ever rejects what
+// the full test rejects, so the masks stay bit-exact; it is itself NOT exact arithmetic (approximate reciprocal /
+// square root, fused multiply-adds) and pays for that with explicit slack:
+//  * depth planes: the depth is computed with project_one's own operations, so the comparison is the same;
+//  * disc test with an upper bound on the radius.  lambda_max(J cov_c J^T + eps I) <= |J|_F^2 smax^2 + eps, and with
+//    |tx / z| <= lim_x:  |J|_F^2 <= (fx^2 (1 + lim_x^2) + fy^2 (1 + lim_y^2)) / z^2  -- a per-camera constant over z^2
+//    (the view rotation is taken as a similarity: |R|_F^2 / 3 = its squared scale).  The packed radius rule uses at
+//    most lambda_max + sqrt(0.1), radius = ceil(3 sqrt(.)) <= 3 sqrt(.) + 1; 2 % + 0.07 px cover the rounding;
+//  * the image position is one fused dot product per axis with the per-camera rows  fx R0 + cx R2,  fy R1 + cy R2
+//    divided by the depth.  It differs from project_one's mean2d by rounding only: at most
+//    2^-19 (f + |c|)(max|R| |mean|_1 + max|t|) / z  +  1e-5 |mean2d|, which is added to the radius bound.
+// Non-finite values make every comparison false and fall through to the full test.
+struct PreCam {      // 16 floats per camera in shared memory
+    float4 zrow;     // R[2][0..2], t[2]
+    float4 xrow;     // fx R[0] + cx R[2],  fx t[0] + cx t[2]
+    float4 yrow;     // fy R[1] + cy R[2],  fy t[1] + cy t[2]
+    float4 k;        // x: radius constant, y / z: rounding allowance per unit |mean|_1 / constant, w: unused
+};
+__device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float rsqrt_approx(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
+__device__ __forceinline__ void make_precam(const float *vm, const float *K, int width, int height, PreCam &o) {
+    const float fx = K[0], fy = K[4], cx = K[2], cy = K[5];
+    const float lim_x = 1.3f * (0.5f * (float)width / fx), lim_y = 1.3f * (0.5f * (float)height / fy);
+    float rs = 0.f, rmax = 0.f, tmax = 0.f;
+    for (int r = 0; r < 3; ++r) {
+        for (int k = 0; k < 3; ++k) { rs += vm[r * 4 + k] * vm[r * 4 + k]; rmax = fmaxf(rmax, fabsf(vm[r * 4 + k])); }
+        tmax = fmaxf(tmax, fabsf(vm[r * 4 + 3]));
+    }
+    o.zrow = make_float4(vm[8], vm[9], vm[10], vm[11]);
+    o.xrow = make_float4(fx * vm[0] + cx * vm[8], fx * vm[1] + cx * vm[9], fx * vm[2] + cx * vm[10], fx * vm[3] + cx * vm[11]);
+    o.yrow = make_float4(fy * vm[4] + cy * vm[8], fy * vm[5] + cy * vm[9], fy * vm[6] + cy * vm[10], fy * vm[7] + cy * vm[11]);
+    const float g = 1.9073486e-6f * (fmaxf(fabsf(fx), fabsf(fy)) + fmaxf(fabsf(cx), fabsf(cy)));  // 2^-19 (f + |c|)
+    o.k = make_float4(1.001f * (rs * (1.0f / 3.0f)) * (fx * fx * (1.f + lim_x * lim_x) + fy * fy * (1.f + lim_y * lim_y)),
+                      g * rmax, g * tmax, 0.f);
+}
+
+__device__ __forceinline__ bool surely_culled(const float mean[3], float smax2, float mean_l1, const PreCam *pc,
+                                              float fwidth, float fheight, float c0, float near_plane,
+                                              float far_plane) {
+    const float4 zr = pc->zrow;
+    const float z = ((zr.x * mean[0] + zr.y * mean[1]) + zr.z * mean[2]) + zr.w;  // = project_one's depth, same operations
+    if (z < near_plane || z > far_plane) return true;
+    const float4 xr = pc->xrow, yr = pc->yrow, k = pc->k;
+    const float rz = rcp_approx(z);
+    const float u = __fmaf_rn(k.x * smax2, rz * rz, c0);              // >= eps2d + 0.32 > 0
+    const float Rb = __fmaf_rn(3.06f, u * rsqrt_approx(u), 1.07f);
+    const float mx = __fmaf_rn(xr.x, mean[0], __fmaf_rn(xr.y, mean[1], __fmaf_rn(xr.z, mean[2], xr.w))) * rz;
+    const float my = __fmaf_rn(yr.x, mean[0], __fmaf_rn(yr.y, mean[1], __fmaf_rn(yr.z, mean[2], yr.w))) * rz;
+    const float Rr = __fmaf_rn(__fmaf_rn(mean_l1, k.y, k.z), rz, Rb);
+    const float Rx = __fmaf_rn(1e-5f, fabsf(mx), Rr), Ry = __fmaf_rn(1e-5f, fabsf(my), Rr);
+    return mx + Rx <= 0.f || mx - Rx >= fwidth || my + Ry <= 0.f || my - Ry >= fheight;
 }
 
 // ---------------------------------------------------------------------------
 // S1.  One thread per Gaussian, all B cameras: xyz/scale/quat are read once
 // (40 B/Gaussian) instead of 2*B times as in the reference's two-pass kernel.
+// PRETEST (B > 8): pass 1 runs the rejection above for every camera (no divergence) and leaves each lane a bit
+// list of candidate cameras; pass 2 runs the reference's full test on each lane's own candidates (pooling the
+// warp's candidates and dealing them out evenly was tried: 3 % faster at configs[3], 25 % slower on dense scenes).
 // ---------------------------------------------------------------------------
 template <typename W, bool PRETEST>
 __global__ void __launch_bounds__(kCullThreads)
@@ -95,36 +125,45 @@ cull_count_kernel(const float *__restrict__ means, const float *__restrict__ sca
                   const float *__restrict__ quats, int activated, int64_t N,
                   const float *__restrict__ viewmats, const float *__restrict__ Ks, int B, CullParams p,
                   W *__restrict__ bitmap, int32_t *__restrict__ block_counts /* [B][gridDim.x] */) {
-    __shared__ float s_cam[kMaxCams * 16];
+    __shared__ __align__(16) float s_cam[kMaxCams * 16];
     __shared__ int s_cnt[kMaxCams];
-    __shared__ float s_pre[kMaxCams * 4];  // per camera: 1.3 tan(fov/2) in x and y, squared scale of the rotation
+    __shared__ __align__(16) PreCam s_pre[PRETEST ? kMaxCams : 1];
     stage_cameras(s_cam, viewmats, Ks, B);
     if (threadIdx.x < kMaxCams) s_cnt[threadIdx.x] = 0;
-    if (threadIdx.x < B) {
-        const int c = threadIdx.x;
-        s_pre[4 * c] = 1.3f * (0.5f * (float)p.width / Ks[c * 9 + 0]);
-        s_pre[4 * c + 1] = 1.3f * (0.5f * (float)p.height / Ks[c * 9 + 4]);
-        float rs = 0.f;
-        for (int r = 0; r < 3; ++r)
-            for (int k = 0; k < 3; ++k) rs += viewmats[c * 16 + r * 4 + k] * viewmats[c * 16 + r * 4 + k];
-        s_pre[4 * c + 2] = rs * (1.0f / 3.0f);
-    }
+    if (PRETEST && threadIdx.x < B)
+        make_precam(viewmats + threadIdx.x * 16, Ks + threadIdx.x * 9, p.width, p.height, s_pre[threadIdx.x]);
     __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int64_t i = (int64_t)blockIdx.x * kCullThreads + threadIdx.x;
     uint64_t word = 0;
-    if (i < N) {
-        float mean[3], covar[9], smax2;
-        load_gaussian(means, scales, quats, activated, i, mean, covar, &smax2);
-        // Pass 1 (no divergence): cheap sufficient rejection for every camera.  Pass 2: the full test only for
-        // the candidates, each lane walking its OWN candidate list -- with a few per cent of the pairs surviving,
-        // running the full test whenever any lane of the warp survives would still execute it for half the pairs.
+    if (!PRETEST) {
+        if (i < N) {
+            float mean[3], covar[9];
+            load_gaussian(means, scales, quats, activated, i, mean, covar);
+            for (int c = 0; c < B; ++c) {
+                Camera cam;
+                camera_from_smem(s_cam + c * 16, cam);
+                Projected o;
+                bool ok = project_one<true>(mean, covar, cam, p.width, p.height, p.eps2d, p.near_plane,
+                                            p.far_plane, p.radius_clip, o);
+                word |= (uint64_t)ok << c;
+            }
+            bitmap[i] = (W)word;
+        }
+    } else {
+        float mean[3], covar[9], smax2 = 0.f;
         uint64_t cand = 0;
-        for (int c = 0; c < B; ++c) {
-            Camera cam;
-            camera_from_smem(s_cam + c * 16, cam);
-            if (!PRETEST || !surely_culled(mean, smax2, cam, s_pre[4 * c], s_pre[4 * c + 1], s_pre[4 * c + 2], p.width,
-                                           p.height, p.eps2d, p.near_plane, p.far_plane))
-                cand |= (uint64_t)1 << c;
+        if (i < N) {
+            load_gaussian(means, scales, quats, activated, i, mean, covar, &smax2);
+            const float l1 = (fabsf(mean[0]) + fabsf(mean[1])) + fabsf(mean[2]);
+            const float fw = (float)p.width, fh = (float)p.height, c0 = p.eps2d + 0.32f;
+            for (int cb = 0; cb < B; cb += 32) {   // 32 cameras per mask word: no 64-bit shifts in the loop
+                unsigned m = 0;
+                const int nb = min(32, B - cb);
+                for (int j = 0; j < nb; ++j)
+                    if (!surely_culled(mean, smax2, l1, &s_pre[cb + j], fw, fh, c0, p.near_plane, p.far_plane)) m |= 1u << j;
+                cand |= (uint64_t)m << cb;
+            }
         }
         while (cand) {
             const int c = __ffsll((long long)cand) - 1;
@@ -136,13 +175,16 @@ cull_count_kernel(const float *__restrict__ means, const float *__restrict__ sca
                                         p.far_plane, p.radius_clip, o);
             word |= (uint64_t)ok << c;
         }
-        bitmap[i] = (W)word;
+        if (i < N) bitmap[i] = (W)word;
     }
-    // per-camera block totals: warp ballot + one shared atomic per warp
-    int lane = threadIdx.x & 31;
-    for (int c = 0; c < B; ++c) {
-        unsigned m = __ballot_sync(0xffffffffu, (word >> c) & 1);
-        if (lane == 0 && m) atomicAdd(&s_cnt[c], __popc(m));
+    // per-camera block totals: warp ballot + one shared atomic per warp, only for the cameras some lane is visible to
+    unsigned any_lo = __reduce_or_sync(0xffffffffu, (unsigned)word), any_hi = __reduce_or_sync(0xffffffffu, (unsigned)(word >> 32));
+    while (any_lo | any_hi) {
+        int c;
+        if (any_lo) { c = __ffs(any_lo) - 1; any_lo &= any_lo - 1; }
+        else { c = 32 + __ffs(any_hi) - 1; any_hi &= any_hi - 1; }
+        const unsigned m = __ballot_sync(0xffffffffu, (word >> c) & 1);
+        if (lane == 0) atomicAdd(&s_cnt[c], __popc(m));
     }
     __syncthreads();
     if (threadIdx.x < B) block_counts[(int64_t)threadIdx.x * gridDim.x + blockIdx.x] = s_cnt[threadIdx.x];
@@ -198,6 +240,102 @@ cull_scan_kernel(int32_t *__restrict__ block_counts, int64_t nblocks, int64_t *_
     }
 }
 
+// s_base[c] = counts[0] + .. + counts[c-1] for c < kMaxCams, by the first two warps (one load per thread: a serial
+// loop in thread 0 is 64 dependent global loads at the head of every block).  Caller syncs before reading.
+__device__ __forceinline__ void camera_bases(const int64_t *__restrict__ counts, int B, int64_t *s_base) {
+    static_assert(kMaxCams == 64, "camera_bases: two warps");
+    __shared__ int64_t s_first_half;
+    const int t = threadIdx.x, lane = t & 31;
+    int64_t v = 0, incl = 0;
+    if (t < kMaxCams) {
+        v = t < B ? counts[t] : 0;
+        incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int64_t u = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += u;
+        }
+        if (t == 31) s_first_half = incl;
+    }
+    __syncthreads();
+    if (t < kMaxCams) s_base[t] = (incl - v) + (t >= 32 ? s_first_half : 0);
+}
+
+// Ids only (what the training engine asks for).  The block's bitmap words are transposed into per-(camera, warp)
+// ballots in shared memory (only for the cameras some lane of the warp is visible to).  Sparse blocks (large batches
+// over large scenes: 1-2 % of the pairs set): thread (camera c, word w) writes the ids of its 32-Gaussian word --
+// eight neighbouring threads fill one camera's consecutive positions -- instead of every warp walking all B cameras
+// twice.  Dense blocks (more than 4 cameras per Gaussian on average): every thread writes its own Gaussian's bits,
+// ranked by the same ballots.
+template <typename W>
+__global__ void __launch_bounds__(kCullThreads)
+cull_emit_ids_kernel(int64_t N, int B, const W *__restrict__ bitmap, const int32_t *__restrict__ block_offsets,
+                     const int64_t *__restrict__ counts, int64_t *__restrict__ gaussian_ids,
+                     int64_t *__restrict__ camera_ids) {
+    constexpr int kWarps = kCullThreads / 32;
+    static_assert(kWarps == 8, "cull_emit_ids: 8 ballot words per camera");
+    __shared__ int64_t s_base[kMaxCams];
+    __shared__ unsigned s_bal[kMaxCams][kWarps];
+    __shared__ int s_pref[kMaxCams][kWarps];   // dense path: set bits of camera c in the warps before w
+    __shared__ int s_total;
+    camera_bases(counts, B, s_base);   // syncs once
+    for (int k = threadIdx.x; k < kMaxCams * kWarps; k += kCullThreads) (&s_bal[0][0])[k] = 0;
+    if (threadIdx.x == 0) s_total = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t i = (int64_t)blockIdx.x * kCullThreads + threadIdx.x;
+    const uint64_t word = i < N ? (uint64_t)bitmap[i] : 0;
+    unsigned any_lo = __reduce_or_sync(0xffffffffu, (unsigned)word), any_hi = __reduce_or_sync(0xffffffffu, (unsigned)(word >> 32));
+    int warp_bits = 0;
+    while (any_lo | any_hi) {
+        int c;
+        if (any_lo) { c = __ffs(any_lo) - 1; any_lo &= any_lo - 1; }
+        else { c = 32 + __ffs(any_hi) - 1; any_hi &= any_hi - 1; }
+        const unsigned m = __ballot_sync(0xffffffffu, (word >> c) & 1);
+        if (lane == 0) { s_bal[c][warp] = m; warp_bits += __popc(m); }
+    }
+    if (lane == 0 && warp_bits) atomicAdd(&s_total, warp_bits);
+    __syncthreads();
+    const bool dense = s_total > 4 * kCullThreads;   // block-uniform
+    const int w = threadIdx.x & (kWarps - 1);
+    for (int cb = 0; cb < B; cb += kCullThreads / kWarps) {
+        const int c = cb + (threadIdx.x >> 3);
+        unsigned m = c < B ? s_bal[c][w] : 0;
+        // set bits of this camera's words before word w (prefix over the 8 lanes that share the camera)
+        const int n = __popc(m);
+        int incl = n;
+#pragma unroll
+        for (int d = 1; d < kWarps; d <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, incl, d, kWarps);
+            if (w >= d) incl += u;
+        }
+        if (dense) {
+            if (c < B) s_pref[c][w] = incl - n;
+            continue;
+        }
+        if (!m) continue;
+        int64_t pos = s_base[c] + block_offsets[(int64_t)c * gridDim.x + blockIdx.x] + (incl - n);
+        const int64_t id0 = (int64_t)blockIdx.x * kCullThreads + w * 32;
+        while (m) {
+            const int b = __ffs(m) - 1;
+            m &= m - 1;
+            gaussian_ids[pos] = id0 + b;
+            if (camera_ids) camera_ids[pos] = c;
+            ++pos;
+        }
+    }
+    if (!dense) return;
+    __syncthreads();
+    const unsigned lt_mask = (1u << lane) - 1u;
+    for (uint64_t wd = word; wd; wd &= wd - 1) {
+        const int c = __ffsll((long long)wd) - 1;
+        const int r = s_pref[c][warp] + __popc(s_bal[c][warp] & lt_mask);
+        const int64_t pos = s_base[c] + block_offsets[(int64_t)c * gridDim.x + blockIdx.x] + r;
+        gaussian_ids[pos] = i;
+        if (camera_ids) camera_ids[pos] = c;
+    }
+}
+
 // Compaction from the bitmap: camera c's ascending ids land at
 // [sum(counts[<c]) + block offset + rank in block).
 template <typename W>
@@ -214,10 +352,7 @@ cull_emit_kernel(const float *__restrict__ means, const float *__restrict__ scal
     __shared__ int s_wcnt[kMaxCams][kCullThreads / 32];
     const bool extra = radii != nullptr;
     if (extra) stage_cameras(s_cam, viewmats, Ks, B);
-    if (threadIdx.x == 0) {
-        int64_t acc = 0;
-        for (int c = 0; c < B; ++c) { s_base[c] = acc; acc += counts[c]; }
-    }
+    camera_bases(counts, B, s_base);
     int64_t i = (int64_t)blockIdx.x * kCullThreads + threadIdx.x;
     uint64_t word = i < N ? (uint64_t)bitmap[i] : 0;
     int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -333,9 +468,16 @@ CLMGS_EXPORT int clmgs_cull_emit(const float *means, const float *scales, const 
     const int64_t *head = (const int64_t *)scratch;
     const int32_t *blk = (const int32_t *)((const char *)scratch + kCullHead);
 #define LAUNCH(W)                                                                                              \
-    cull_emit_kernel<W><<<nblocks, kCullThreads, 0, st>>>(means, scales, quats, activated, N, viewmats, Ks, B, \
-                                                         p, (const W *)bitmap, blk, head, gaussian_ids,       \
-                                                         camera_ids, radii, means2d, depths, conics)
+    do {                                                                                                       \
+        if (radii == nullptr)                                                                                  \
+            cull_emit_ids_kernel<W><<<nblocks, kCullThreads, 0, st>>>(N, B, (const W *)bitmap, blk, head,      \
+                                                                     gaussian_ids, camera_ids);               \
+        else                                                                                                   \
+            cull_emit_kernel<W><<<nblocks, kCullThreads, 0, st>>>(means, scales, quats, activated, N, viewmats, \
+                                                                 Ks, B, p, (const W *)bitmap, blk, head,       \
+                                                                 gaussian_ids, camera_ids, radii, means2d,     \
+                                                                 depths, conics);                              \
+    } while (0)
     switch (word_bytes) {
         case 1: LAUNCH(uint8_t); break;
         case 2: LAUNCH(uint16_t); break;
