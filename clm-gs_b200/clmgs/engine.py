@@ -165,6 +165,18 @@ def wait_host_adam(gaussians):
             raise pend["err"][0]
 
 
+_SIDE_STREAMS = {}
+
+
+def _side_stream(dev):
+    """One extra stream per device for copies nobody on the compute stream waits for."""
+    key = torch.device(dev).index if torch.device(dev).index is not None else torch.cuda.current_device()
+    st = _SIDE_STREAMS.get(key)
+    if st is None:
+        st = _SIDE_STREAMS[key] = torch.cuda.Stream(device=dev)
+    return st
+
+
 def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, timer=_NULL_TIMER, parity=0,
                       host_rows=True):
     """engine.py:135-298: camera order (TSP over sampled visibility distance), ordered bitmap,
@@ -194,16 +206,26 @@ def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, tim
         sparsity = [f.shape[0] / float(n_gaussians) for f in filters]
         ordered_bitmap = ops.bitmap_permute(bitmap, bsz, ordered_cams)
         ffs = ops.extract_ffs(ordered_bitmap)
-        rows_dev = counts = rows_host = None
+        rows_dev = counts = rows_host = rows_ready = None
         if host_rows:
             rows_dev, counts = ops.group_by_ffs(ffs, bsz)
             rows_host = _pinned_rows_buffer(n_gaussians, parity)
-            rows_host.copy_(rows_dev, non_blocking=True)
+            # N x 4 bytes to the host (7 ms at 102 M): on a side stream, so that neither the read-backs below nor the
+            # first cameras wait for it; its readers (the host Adam thread first of all) wait on rows_ready
+            side = _side_stream(dev)
+            grouped = torch.cuda.Event()
+            grouped.record()
+            side.wait_event(grouped)
+            with torch.cuda.stream(side):
+                rows_host.copy_(rows_dev, non_blocking=True)
+                rows_ready = torch.cuda.Event()
+                rows_ready.record(side)
+            rows_dev.record_stream(side)
         # batch-resident rows: Gaussians grouped by the first camera that needs them; a Gaussian's slot in the
         # device row table is its position in that grouping (so each first-use group is a contiguous slot range)
         first = ops.extract_first_use(ordered_bitmap, bsz)
         first_rows_dev, first_counts = ops.group_by_ffs(first, bsz)
-        counts_h = counts.cpu().numpy() if host_rows else None  # sync: also completes the rows copy above (same stream)
+        counts_h = counts.cpu().numpy() if host_rows else None
         first_counts_h = first_counts.cpu().numpy()
         n_untouched = int(first_counts_h[0])
         union_ids = first_rows_dev[n_untouched:]
@@ -223,7 +245,8 @@ def order_calculation(filters, cull, n_gaussians, bsz, perm_generator, args, tim
         row_end = np.ascontiguousarray(offs[[k + 1 for k in keys]], dtype=np.int64)
     first_edges = np.concatenate([[0], np.cumsum(first_counts_h[1:])]).astype(np.int64)  # slots of first-use group k
     return dict(ordered_cams=ordered_cams, filters=filters, sparsity=sparsity, ordered_bitmap=ordered_bitmap,
-                visibility=ffs, rows_host=rows_host, rows_dev=rows_dev, row_begin=row_begin, row_end=row_end,
+                visibility=ffs, rows_host=rows_host, rows_ready=rows_ready, rows_dev=rows_dev, row_begin=row_begin,
+                row_end=row_end,
                 union_ids=union_ids, slot_of=slot_of, first_edges=first_edges)
 
 
@@ -356,6 +379,7 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
         ca = gaussians.optimizer.cpu_adam
         if not ca.lazy_pending:
             ca.last_step[:N] = ca.step_count
+        oc["rows_ready"].synchronize()
         ca.catch_up(oc["rows_host"][int(oc["row_end"][0]):N], include_this_step=True)
         ca.lazy_pending = True
 
@@ -407,6 +431,7 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
         try:
             if prev is not None and prev["err"]:
                 raise prev["err"][0]   # the previous batch's host update failed: do not update on top of it
+            oc["rows_ready"].synchronize()   # the row list is in pinned memory
             with nvtx_range("cpu_adam.sparse_step()"):  # engine.py:319
                 cpu_adam.batched_sparse_step(h_grad, oc["rows_host"], seg_begin, seg_end, seg_signal, signal, 1.0 / bsz,
                                              progress, [1 if (s_ == -1 and not args.sparse_adam and i_ == 0) else 0
@@ -423,6 +448,7 @@ def clm_offload_train_one_batch(gaussians, scene, batched_cameras, parameters_gr
                              signal, timer, worker, worker_err, chunk_edges, prev, pipe)
         if pipe:
             # ids at the ends of the final-flush pieces: the next call loads rows up to hi[c] once piece c is updated
+            oc["rows_ready"].synchronize()
             rows_host, g0 = oc["rows_host"], int(rb[bsz])
             hi = [int(rows_host[g0 + chunk_edges[j + 1] - 1]) for j in range(J)]
             gaussians._pending_adam = dict(worker=worker, progress=progress, chunk_hi=hi, n_seg=len(seg_begin), err=worker_err,
