@@ -3,8 +3,10 @@
     python clm-gs_b200/build.py [--force] [--verbose]
 
 Per-file flags: proj.cu is the decision-critical translation unit and is
-compiled with -fmad=false (see csrc/gs_math.cuh); everything else uses the
-default contraction rules and explicit fast intrinsics where wanted.
+compiled with -fmad=false (see csrc/gs_math.cuh); raster.cu is built with
+-use_fast_math like the reference's extension (its parity bar is a tolerance,
+not bit equality); everything else uses the default contraction rules and
+explicit fast intrinsics where wanted.
 """
 import argparse
 import concurrent.futures as cf
