@@ -215,6 +215,13 @@ def run_ours(a):
         sh_host = hostmem.pinned_tensor((hi - lo, 48), torch.float32)
     g = S.make_gaussians(spec, sh_out=sh_host.numpy(), sh_rows=(lo, hi),
                          workers=max(1, (os.cpu_count() or 1) // world))  # each rank generates only its SH shard
+    if a.spatial_order:
+        # opt-in, reported separately: the same Gaussians stored in Morton order.  The synthetic SH rows are i.i.d., so
+        # only the geometry is permuted (every rank computes the same permutation).
+        perm = S.morton_order(g["xyz"], device=dev)
+        for key in ("xyz", "log_scale", "raw_quat", "opacity_logit"):
+            g[key] = np.ascontiguousarray(g[key][perm])
+        del perm
     args = model.TrainArgs(bsz=global_batch, sparse_adam=sparse_adam, cpu_adam_threads=host_threads)
     gm = model.GaussianModelCLMOffload(3, dev).create_from_arrays(g["xyz"], g["log_scale"], g["raw_quat"],
                                                                  g["opacity_logit"], sh_host,
@@ -474,6 +481,8 @@ def run_ours(a):
             out["config"]["grad_exchange"] = stats["grad_exchange"]
             out["config"]["grad_chunks"] = stats.get("grad_chunks")
         out["config"]["host_huge_pages"] = hostmem.huge_page_stats()
+        if a.spatial_order:
+            out["config"]["spatial_order"] = "Gaussians stored in Morton order (opt-in; default is the generator's i.i.d. order)"
         if pipelined:
             out["pipelined"] = pipelined
         if lazy:
@@ -635,6 +644,9 @@ def main():
                     help="opt-in engine mode: defer the host-Adam join to the next call (reported in the extra "
                          "`pipelined` object; the headline keeps the reference's call contract)")
     ap.add_argument("--cpu-sample-gaussians", type=int, default=8_000_000)
+    ap.add_argument("--spatial-order", action="store_true",
+                    help="store the scene's Gaussians in Morton order (opt-in; changes the memory access pattern of the "
+                         "SH row transfers, not the training math; noted in config)")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 0)
     if a.other_configs is None:   # the default run (north-star config, 1 GPU) also carries configs[1] and configs[2]
