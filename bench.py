@@ -16,6 +16,8 @@ Gaussians, 1920x1080, batch 64, sparse Adam, no densification (release_scripts/b
 `--gpus N`: configs with a batch of >= 4 cameras per GPU keep the GLOBAL batch fixed and split the cameras
            (strong scaling: 64 -> 32/16/8 per GPU for configs[3]); smaller batches scale weakly.
 `other_configs` (N = 1, default run): configs[1] and configs[2] (clm vs naive) measured in child processes.
+Opt-in modes, never part of the default line: `--pipeline` / `--lazy-adam` (relaxed call contract),
+           `--spatial-order` (the scene's Gaussians stored in Morton order; noted in `config.spatial_order`).
 `--impl reference`: the reference's CPU path (oracle port: C restatement of gsplat's kernels + cpu-adam, all host
            threads) on a bounded sample of the same workload, extrapolated.
 """

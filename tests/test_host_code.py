@@ -276,3 +276,16 @@ def test_cpu_adam_packed_gradients_equal_table_gradients():
         ops.cpu_adam_batched_sparse_step(b[0], untouched_table, b[1], b[2], col_lr, rows, [0], [10], [-1], sig, 0.9, 0.999,
                                          1e-15, 4, 0.25, n_threads=1, seg_zero_grad=[0], grad_packed=g_packed,
                                          packed_base=n_unt)
+
+
+def test_morton_order_is_a_locality_improving_permutation():
+    """scene.morton_order (bench.py --spatial-order): a permutation; numpy and torch paths agree; neighbours in the
+    order are neighbours in space."""
+    from clmgs import scene as S
+    rng = np.random.default_rng(3)
+    p = (rng.random((50_000, 3)) * np.array([200.0, 200.0, 10.0])).astype(np.float32)
+    perm = S.morton_order(p)
+    assert np.array_equal(np.sort(perm), np.arange(len(p)))
+    assert np.array_equal(perm, S.morton_order(p, device="cpu"))
+    step = lambda a: np.linalg.norm(np.diff(a, axis=0), axis=1).mean()
+    assert step(p[perm]) < 0.1 * step(p)
