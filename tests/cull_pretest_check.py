@@ -1,7 +1,7 @@
 """CPU check of the cull kernel's rejection pass (csrc/proj.cu: make_precam / surely_culled): a float32 numpy
 restatement of it must never reject a (camera, Gaussian) pair that the oracle's full test keeps.
 
-    python tools/cull_pretest_check.py [n_gaussians=200000]
+    python tests/cull_pretest_check.py [n_gaussians=200000]
 
 Scenes: the three bench scene shapes plus adversarial sets (Gaussians next to the camera, on the frustum edges,
 very large / very anisotropic).  Prints the fraction of pairs the pass rejects next to the fraction the full test

@@ -1,5 +1,5 @@
 """The cull kernel's rejection pass (csrc/proj.cu: make_precam / surely_culled) may only reject what the reference's
-full test rejects.  A float32 numpy restatement of it (tools/cull_pretest_check.py) is checked against the oracle's
+full test rejects.  A float32 numpy restatement of it (tests/cull_pretest_check.py) is checked against the oracle's
 keep mask on the three bench scene shapes plus adversarial Gaussians (next to a camera, on the frustum edges, huge /
 anisotropic).  The kernel itself is pinned on the GPU: its masks must equal the oracle's bit for bit
 (tests/test_gpu_forward.py, tests/test_gpu_vs_reference_cuda.py)."""
@@ -7,7 +7,7 @@ import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path[:0] = [ROOT, os.path.join(ROOT, "tools")]
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
 
 
 def test_rejection_pass_never_rejects_a_kept_pair(monkeypatch, capsys):
