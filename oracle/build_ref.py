@@ -1,6 +1,6 @@
 """Build the REFERENCE's own CUDA extensions (gsplat.csrc and clm_kernels._C) for sm_100 from the
 sources where they lie under /root/reference, into oracle/_ref/ (git-ignored, travels to the GPU
-box).  Test infrastructure only: used by tests/test_gpu_vs_reference_cuda.py and tools/ref_gpu_compare.py on the GPU box to compare our
+box).  Test infrastructure only: used by tests/test_gpu_vs_reference_cuda.py and tests/ref_gpu_compare.py on the GPU box to compare our
 kernels against the reference's kernels on identical inputs and to time them.
 
 No reference source is copied; this script only points torch.utils.cpp_extension at the files.

@@ -3,7 +3,7 @@ parity half is tests/test_gpu_vs_reference_cuda.py; this script also TIMES every
 
 Needs oracle/_ref/ (built in the build container by `python oracle/build_ref.py` from the sources
 under /root/reference, compiled for sm_100 with the reference's flags incl. --use_fast_math).
-Run on the GPU box:   python tools/ref_gpu_compare.py [--n 6000000]
+Run on the GPU box:   python tests/ref_gpu_compare.py [--n 6000000]
 
 Reports (a) parity on identical inputs -- cull-mask / radii mismatch rates against a fast-math
 build, exactness of the integer stages given identical inputs, image and gradient differences --
